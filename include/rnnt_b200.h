@@ -1,0 +1,157 @@
+/* rnnt_b200 -- C ABI of the B200-native RNN-T joint + transducer-loss hot path.
+ *
+ * This is the drop-in boundary for the two adjacent calls the reference makes at
+ *   rnnt/model.py:68   logits = self.joint(enc_state, dec_state)
+ *   rnnt/model.py:70   loss   = self.crit(logits, targets.int(), inputs_length.int(), targets_length.int())
+ * and their backward (train.py:45). `self.crit` is warprnnt_pytorch.RNNTLoss
+ * (model.py:6,59), a third-party C++/CUDA extension that is not in the reference
+ * tree; the entry points below are what that extension's FFI would bind for this
+ * path. Plain pointers and sizes only: no torch types, no allocation inside, no host
+ * synchronisation, every launch on the caller's stream. All pointers are DEVICE
+ * pointers unless stated. Re-entrant: no global mutable state (the reference's
+ * nn.DataParallel, train.py:177, calls from one thread per GPU).
+ *
+ * Return value: 0 = ok; <0 = invalid argument (RNNT_B200_E_*); >0 = cudaError_t.
+ *
+ * Lattice "plane" layout (workspace owned by the caller): for utterance b the cell
+ * (t,u), 0<=t<T, 0<=u<U1 (U1 = U+1), lives at
+ *       b*D*U1 + (t+u)*U1 + u,          D = T + U1 - 1   (anti-diagonal major)
+ * so that one wavefront step reads one contiguous row. rnnt_b200_plane_elems()
+ * returns B*D*U1. Cells with t >= act_lens[b] or u > label_lens[b] are never read.
+ */
+#ifndef RNNT_B200_H_
+#define RNNT_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RNNT_B200_VERSION 100
+
+enum {
+  RNNT_B200_OK = 0,
+  RNNT_B200_E_NULL = -1,      /* a required pointer is NULL                      */
+  RNNT_B200_E_SHAPE = -2,     /* B,T,U1,V,H out of the supported range           */
+  RNNT_B200_E_BLANK = -3,     /* blank not in [0,V)                              */
+  RNNT_B200_E_ALIGN = -4,     /* pointer not aligned as documented               */
+  RNNT_B200_E_WORKSPACE = -5, /* workspace too small                             */
+  RNNT_B200_E_DRIVER = -6,    /* cuTensorMapEncodeTiled unavailable / failed     */
+  RNNT_B200_E_ARCH = -7       /* device is not sm_100                            */
+};
+
+int rnnt_b200_version(void);
+const char* rnnt_b200_status_string(int status);
+
+/* Number of elements of one lattice plane (see layout above). */
+size_t rnnt_b200_plane_elems(int B, int T, int U1);
+
+/* ---- Boundary 1: strict drop-in on materialised logits ---------------------------
+ * replaces warprnnt_pytorch.RNNTLoss.forward on `acts` (model.py:70).
+ * logits (B,T,U1,V) float32 contiguous RAW activations (the reference applies no
+ * softmax, model.py:61-72); labels (B,U1-1) int32 zero padded; act_lens, label_lens
+ * (B) int32. Lengths are clamped on device to [1,T] / [0,U1-1].
+ * Writes lse, lp_blank, lp_label planes (float32) for the valid cells. */
+int rnnt_b200_logits_to_planes(const float* logits, const int32_t* labels,
+                               const int32_t* act_lens, const int32_t* label_lens,
+                               int B, int T, int U1, int V, int blank,
+                               float* lse, float* lp_blank, float* lp_label,
+                               void* stream);
+
+/* alpha/beta wavefront over the two log-prob planes (float64 accumulators), then the
+ * occupation coefficients
+ *   c_blank[t,u] = exp(alpha[t,u] + lp_blank[t,u] + beta[t+1,u] - ll)
+ *   c_label[t,u] = exp(alpha[t,u] + lp_label[t,u] + beta[t,u+1] - ll)
+ * and loss[b] = -ll_b (float32) plus loss64[b] (float64, nullable).
+ * alpha, beta: float64 planes (workspace). U1 <= 1024. */
+int rnnt_b200_lattice(const float* lp_blank, const float* lp_label,
+                      const int32_t* act_lens, const int32_t* label_lens,
+                      int B, int T, int U1,
+                      double* alpha, double* beta,
+                      float* c_blank, float* c_label,
+                      float* loss, double* loss64, void* stream);
+
+/* d loss / d logits for boundary 1 (the autograd backward of model.py:70):
+ *   g[b,t,u,v] = scale[b] * ( exp(logit - lse)*(c_blank+c_label) - [v=blank] c_blank
+ *                             - [v=labels[b,u]] c_label ),   0 outside the valid window.
+ * scale (B) float32 on device = upstream grad * reduction factor. dlogits is fully
+ * written (zeros outside the valid window). */
+int rnnt_b200_planes_to_dlogits(const float* logits, const int32_t* labels,
+                                const int32_t* act_lens, const int32_t* label_lens,
+                                int B, int T, int U1, int V, int blank,
+                                const float* lse, const float* c_blank, const float* c_label,
+                                const float* scale, float* dlogits, void* stream);
+
+/* ---- Boundary 2: fused joint + loss, logits never materialised --------------------
+ * replaces model.py:68 + :70 together. The first joint layer is decomposed as
+ *   W1.cat(e,d)+b1 = P_enc[b,t,:] + P_dec[b,u,:]   (model.py:31-32; encoder columns first)
+ * and the caller supplies P_enc (B,T,H), P_dec (B,U1,H) float32 (two small library
+ * GEMMs). H multiple of 64, 64 <= H <= 512. */
+
+/* Lattice cells are flattened per utterance, row-major over the VALID window
+ * (cell = t*(U_b+1)+u), and cut into tiles of 128 consecutive cells. Upper bound of
+ * the tile count for given padded dims (what workspaces must be sized for): */
+int rnnt_b200_max_tiles(int B, int T, int U1);
+
+/* Builds the device tile table from the lengths (no host read-back):
+ *   tile_utt[i], tile_cell0[i] for i < n_tiles[0]; also clamped lengths. */
+int rnnt_b200_build_tiles(const int32_t* act_lens, const int32_t* label_lens,
+                          int B, int T, int U1,
+                          int32_t* tile_utt, int32_t* tile_cell0, int32_t* n_tiles,
+                          void* stream);
+
+/* W2 (V,H) float32 -> bf16 (Vpad,H) zero-padded rows; b2 (V) -> (Vpad) float32 scaled by
+ * log2(e) with -1e30 in the padding (masks padded vocabulary columns).
+ * Vpad = rnnt_b200_vocab_pad(V). */
+int rnnt_b200_vocab_pad(int V);
+int rnnt_b200_vocab_tile(int V);
+int rnnt_b200_pack_vocab(const float* w2, const float* b2, int V, int H,
+                         void* w2_bf16, float* b2_log2, void* stream);
+
+/* Row pitch (elements) of the stashed hidden activations h: H + 8. Column H holds 1.0
+ * for valid cells so that dS^T . h_ext yields d b2 in its last column block. */
+int rnnt_b200_h_pitch(int H);
+
+/* Fused forward: tcgen05/TMEM GEMM  tanh(P_enc[t]+P_dec[u]) . W2^T  with an online
+ * log-sum-exp epilogue; writes lse / lp_blank / lp_label planes only.
+ * h_stash: nullable bf16 (max_tiles*128, H+8) -- written when the backward is wanted. */
+int rnnt_b200_joint_fwd(const float* p_enc, const float* p_dec,
+                        const void* w2_bf16, const float* b2_log2,
+                        const int32_t* labels, const int32_t* act_lens, const int32_t* label_lens,
+                        const int32_t* tile_utt, const int32_t* tile_cell0, const int32_t* n_tiles,
+                        int B, int T, int U1, int V, int H, int blank,
+                        float* lse, float* lp_blank, float* lp_label,
+                        void* h_stash, void* stream);
+
+/* Fused backward, stage 1: recompute logits tiles from h_stash on the tensor cores and
+ * emit dS = scale_b*(softmax*(c_blank+c_label) - onehots) as bf16 for tiles
+ * [tile_lo, tile_hi) into ds (rows (tile_hi-tile_lo)*128, pitch Vpad). Rows of
+ * tiles >= n_tiles[0] and rows past an utterance's last cell are written as zeros. */
+int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, const float* b2_log2,
+                           const int32_t* labels, const int32_t* act_lens, const int32_t* label_lens,
+                           const int32_t* tile_utt, const int32_t* tile_cell0, const int32_t* n_tiles,
+                           const float* lse, const float* c_blank, const float* c_label,
+                           const float* scale,
+                           int B, int T, int U1, int V, int H, int blank,
+                           int tile_lo, int tile_hi, void* ds, void* stream);
+
+/* Fused backward, stage 2: dpre = dh * (1 - h^2) and its two reductions
+ *   dP_enc[b,t,:] += sum_u dpre,   dP_dec[b,u,:] += sum_t dpre     (float32, atomics)
+ * for tiles [tile_lo, tile_hi). dh: float32 rows (tile_hi-tile_lo)*128, pitch H. */
+int rnnt_b200_dh_reduce(const float* dh, const void* h_stash,
+                        const int32_t* act_lens, const int32_t* label_lens,
+                        const int32_t* tile_utt, const int32_t* tile_cell0, const int32_t* n_tiles,
+                        int B, int T, int U1, int H, int tile_lo, int tile_hi,
+                        float* dp_enc, float* dp_dec, void* stream);
+
+/* Plain bf16 tensor-core GEMM used to validate the tcgen05/TMA plumbing on its own:
+ * C (M,N) float32 = A (M,K) bf16 . B (N,K)^T bf16; M%128==0, N%64==0, K%64==0. */
+int rnnt_b200_selftest_gemm(const void* a_bf16, const void* b_bf16, float* c,
+                            int M, int N, int K, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RNNT_B200_H_ */

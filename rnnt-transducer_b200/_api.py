@@ -1,0 +1,342 @@
+"""Host-side mirror of the reference interface for the hot path.
+
+* ``RNNTLoss`` / ``rnnt_loss``   -- boundary 1: drop-in for ``warprnnt_pytorch.RNNTLoss`` as
+  constructed and called at /root/reference rnnt/model.py:59,70 (materialised logits).
+* ``JointNet``                   -- same parameters / state-dict keys as rnnt/model.py:9-37.
+* ``JointRNNTLoss`` / ``joint_rnnt_loss`` -- boundary 2: replaces model.py:68 + :70 in one
+  call; the (B,T,U+1,V) logits are never materialised.
+
+PyTorch is plumbing here (device memory, streams, autograd glue, two small library GEMMs
+for the first joint layer); all lattice / softmax / vocabulary-GEMM work runs in the
+hand-written sm_100a kernels behind include/rnnt_b200.h. There is no CPU fallback.
+"""
+from __future__ import annotations
+
+import os
+from typing import Optional
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import _lib
+
+__all__ = ["RNNTLoss", "rnnt_loss", "JointNet", "JointRNNTLoss", "joint_rnnt_loss",
+           "build_extension", "extension_path", "selftest_gemm"]
+
+
+def build_extension(verbose: bool = False) -> str:
+    return _lib.build(verbose)
+
+
+def extension_path() -> str:
+    return _lib.SO_PATH
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+# --------------------------------------------------------------------------- validation
+def _check_loss_args(acts_shape, acts_dtype, acts_device, labels, act_lens, label_lens, what):
+    """Argument checks of the loss boundary (the reference does none at model.py:70;
+    upstream warp-transducer checks dtype/rank/contiguity). Raises, never falls back."""
+    if len(acts_shape) != 4 and what == "acts":
+        raise ValueError(f"acts must be (B,T,U+1,V), got rank {len(acts_shape)}")
+    if acts_dtype != torch.float32:
+        raise ValueError(f"{what} must be float32, got {acts_dtype}")
+    for name, t in (("labels", labels), ("act_lens", act_lens), ("label_lens", label_lens)):
+        if t.dtype != torch.int32:
+            raise ValueError(f"{name} must be int32 (the reference casts with .int(), model.py:70), got {t.dtype}")
+        if not t.is_contiguous():
+            raise ValueError(f"{name} must be contiguous")
+        if t.device != acts_device:
+            raise ValueError(f"{name} is on {t.device}, expected {acts_device}")
+    if acts_device.type != "cuda":
+        raise RuntimeError("rnnt_b200 has no CPU path: tensors must live on a CUDA device (sm_100)")
+
+
+def _check_lens(B, T, U1, labels, act_lens, label_lens):
+    if labels.dim() != 2 or labels.shape[0] != B or labels.shape[1] != U1 - 1:
+        raise ValueError(f"labels must be (B,U)=({B},{U1 - 1}), got {tuple(labels.shape)}")
+    if act_lens.shape != (B,) or label_lens.shape != (B,):
+        raise ValueError("act_lens and label_lens must have shape (B,)")
+    if os.environ.get("RNNT_B200_VALIDATE", "0") == "1":  # opt-in: costs a device sync
+        if int(act_lens.max()) > T or int(act_lens.min()) < 1:
+            raise ValueError("act_lens out of range [1,T]")
+        if int(label_lens.max()) > U1 - 1 or int(label_lens.min()) < 0:
+            raise ValueError("label_lens out of range [0,U]")
+
+
+def _reduce(loss_b: torch.Tensor, reduction: str) -> torch.Tensor:
+    if reduction == "none":
+        return loss_b
+    if reduction == "sum":
+        return loss_b.sum().reshape(1)
+    if reduction == "mean":  # sum over the batch / batch size, one element (train.py:43,47)
+        return (loss_b.sum() / loss_b.shape[0]).reshape(1)
+    raise ValueError(f"unknown reduction {reduction!r}")
+
+
+def _lattice(lpb, lpl, act_lens, label_lens, B, T, U1):
+    """alpha/beta wavefront + coefficients on the caller's stream. Returns (loss_b, c_blank, c_label)."""
+    L = _lib.lib()
+    dev = lpb.device
+    n = L.rnnt_b200_plane_elems(B, T, U1)
+    alpha = torch.empty(n + B, dtype=torch.float64, device=dev)
+    beta = torch.empty(n + B, dtype=torch.float64, device=dev)
+    cb = torch.empty(n, dtype=torch.float32, device=dev)
+    cl = torch.empty(n, dtype=torch.float32, device=dev)
+    loss = torch.empty(B, dtype=torch.float32, device=dev)
+    _lib.check(L.rnnt_b200_lattice(_ptr(lpb), _ptr(lpl), _ptr(act_lens), _ptr(label_lens), B, T, U1,
+                                   _ptr(alpha), _ptr(beta), _ptr(cb), _ptr(cl), _ptr(loss), None,
+                                   _stream()), "rnnt_b200_lattice")
+    return loss, cb, cl
+
+
+# --------------------------------------------------------------------------- boundary 1
+class _RNNTLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, acts, labels, act_lens, label_lens, blank):
+        L = _lib.lib()
+        B, T, U1, V = acts.shape
+        dev = acts.device
+        with torch.cuda.device(dev):
+            n = L.rnnt_b200_plane_elems(B, T, U1)
+            lse = torch.empty(n, dtype=torch.float32, device=dev)
+            lpb = torch.empty(n, dtype=torch.float32, device=dev)
+            lpl = torch.empty(n, dtype=torch.float32, device=dev)
+            _lib.check(L.rnnt_b200_logits_to_planes(_ptr(acts), _ptr(labels), _ptr(act_lens),
+                                                    _ptr(label_lens), B, T, U1, V, blank, _ptr(lse),
+                                                    _ptr(lpb), _ptr(lpl), _stream()),
+                       "rnnt_b200_logits_to_planes")
+            loss, cb, cl = _lattice(lpb, lpl, act_lens, label_lens, B, T, U1)
+        ctx.save_for_backward(acts, labels, act_lens, label_lens, lse, cb, cl)
+        ctx.blank = blank
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        acts, labels, act_lens, label_lens, lse, cb, cl = ctx.saved_tensors
+        L = _lib.lib()
+        B, T, U1, V = acts.shape
+        with torch.cuda.device(acts.device):
+            scale = grad_out.to(torch.float32).contiguous()
+            dlogits = torch.empty_like(acts)
+            _lib.check(L.rnnt_b200_planes_to_dlogits(_ptr(acts), _ptr(labels), _ptr(act_lens),
+                                                     _ptr(label_lens), B, T, U1, V, ctx.blank,
+                                                     _ptr(lse), _ptr(cb), _ptr(cl), _ptr(scale),
+                                                     _ptr(dlogits), _stream()),
+                       "rnnt_b200_planes_to_dlogits")
+        return dlogits, None, None, None, None
+
+
+def rnnt_loss(acts, labels, act_lens, label_lens, blank: int = 0, reduction: str = "mean"):
+    """Functional form of ``RNNTLoss``. acts (B,T,U+1,V) float32 CUDA raw logits."""
+    _check_loss_args(tuple(acts.shape), acts.dtype, acts.device, labels, act_lens, label_lens, "acts")
+    if not acts.is_contiguous():
+        raise ValueError("acts must be contiguous")
+    B, T, U1, V = acts.shape
+    _check_lens(B, T, U1, labels, act_lens, label_lens)
+    if not 0 <= blank < V:
+        raise ValueError(f"blank {blank} not in [0,{V})")
+    if U1 > 1024:
+        raise ValueError("U+1 > 1024 is not supported by the lattice kernel")
+    return _reduce(_RNNTLossFn.apply(acts, labels, act_lens, label_lens, int(blank)), reduction)
+
+
+class RNNTLoss(nn.Module):
+    """Drop-in for ``warprnnt_pytorch.RNNTLoss`` (rnnt/model.py:6,59,70).
+
+    ``RNNTLoss()`` is no-arg constructible; ``crit(acts, labels, act_lens, label_lens)``
+    returns a 1-element float32 tensor on ``acts.device`` (``reduction='mean'`` = sum over the
+    batch / B; upstream's default could not be consulted offline -- SURVEY.md 9.1) carrying
+    autograd to ``acts``. blank = 0 is pinned by the reference (model.py:64, decoder.py:9).
+    """
+
+    def __init__(self, blank: int = 0, reduction: str = "mean"):
+        super().__init__()
+        if reduction not in ("mean", "sum", "none"):
+            raise ValueError(f"unknown reduction {reduction!r}")
+        self.blank = blank
+        self.reduction = reduction
+
+    def forward(self, acts, labels, act_lens, label_lens):
+        return rnnt_loss(acts, labels, act_lens, label_lens, self.blank, self.reduction)
+
+
+# --------------------------------------------------------------------------- boundary 2
+_DS_BUDGET_BYTES = int(os.environ.get("RNNT_B200_DS_BYTES", str(4 << 30)))
+
+
+class _JointLossFn(torch.autograd.Function):
+    """(P_enc, P_dec, W2, b2) -> per-utterance loss; logits never materialised."""
+
+    @staticmethod
+    def forward(ctx, pe, pd, w2, b2, labels, act_lens, label_lens, blank):
+        L = _lib.lib()
+        B, T, H = pe.shape
+        U1 = pd.shape[1]
+        V = w2.shape[0]
+        dev = pe.device
+        need_grad = any(ctx.needs_input_grad[:4])
+        with torch.cuda.device(dev):
+            st = _stream()
+            max_tiles = L.rnnt_b200_max_tiles(B, T, U1)
+            Vpad = L.rnnt_b200_vocab_pad(V)
+            tile_utt = torch.empty(max_tiles, dtype=torch.int32, device=dev)
+            tile_cell0 = torch.empty(max_tiles, dtype=torch.int32, device=dev)
+            n_tiles = torch.empty(1, dtype=torch.int32, device=dev)
+            _lib.check(L.rnnt_b200_build_tiles(_ptr(act_lens), _ptr(label_lens), B, T, U1, _ptr(tile_utt),
+                                               _ptr(tile_cell0), _ptr(n_tiles), st), "rnnt_b200_build_tiles")
+            w2q = torch.empty(Vpad, H, dtype=torch.bfloat16, device=dev)
+            b2l = torch.empty(Vpad, dtype=torch.float32, device=dev)
+            _lib.check(L.rnnt_b200_pack_vocab(_ptr(w2), _ptr(b2), V, H, _ptr(w2q), _ptr(b2l), st),
+                       "rnnt_b200_pack_vocab")
+            n = L.rnnt_b200_plane_elems(B, T, U1)
+            lse = torch.empty(n, dtype=torch.float32, device=dev)
+            lpb = torch.empty(n, dtype=torch.float32, device=dev)
+            lpl = torch.empty(n, dtype=torch.float32, device=dev)
+            h_stash = None
+            if need_grad:
+                h_stash = torch.empty(max_tiles * 128, L.rnnt_b200_h_pitch(H), dtype=torch.bfloat16, device=dev)
+            _lib.check(L.rnnt_b200_joint_fwd(_ptr(pe), _ptr(pd), _ptr(w2q), _ptr(b2l), _ptr(labels),
+                                             _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt),
+                                             _ptr(tile_cell0), _ptr(n_tiles), B, T, U1, V, H, blank,
+                                             _ptr(lse), _ptr(lpb), _ptr(lpl), _ptr(h_stash), st),
+                       "rnnt_b200_joint_fwd")
+            loss, cb, cl = _lattice(lpb, lpl, act_lens, label_lens, B, T, U1)
+        if need_grad:
+            ctx.save_for_backward(labels, act_lens, label_lens, tile_utt, tile_cell0, n_tiles, w2q, b2l,
+                                  lse, cb, cl, h_stash)
+        ctx.dims = (B, T, U1, V, H, Vpad, max_tiles, blank)
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (labels, act_lens, label_lens, tile_utt, tile_cell0, n_tiles, w2q, b2l, lse, cb, cl,
+         h_stash) = ctx.saved_tensors
+        B, T, U1, V, H, Vpad, max_tiles, blank = ctx.dims
+        L = _lib.lib()
+        dev = lse.device
+        with torch.cuda.device(dev):
+            st = _stream()
+            scale = grad_out.to(torch.float32).contiguous()
+            dpe = torch.zeros(B, T, H, dtype=torch.float32, device=dev)
+            dpd = torch.zeros(B, U1, H, dtype=torch.float32, device=dev)
+            dw2x = torch.zeros(Vpad, H + 8, dtype=torch.float32, device=dev)
+            chunk = max(1, min(max_tiles, _DS_BUDGET_BYTES // (128 * Vpad * 2)))
+            ds = torch.empty(chunk * 128, Vpad, dtype=torch.bfloat16, device=dev)
+            for lo in range(0, max_tiles, chunk):
+                hi = min(max_tiles, lo + chunk)
+                rows = (hi - lo) * 128
+                dsc = ds[:rows]
+                _lib.check(L.rnnt_b200_joint_bwd_ds(_ptr(h_stash), _ptr(w2q), _ptr(b2l), _ptr(labels),
+                                                    _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt),
+                                                    _ptr(tile_cell0), _ptr(n_tiles), _ptr(lse), _ptr(cb),
+                                                    _ptr(cl), _ptr(scale), B, T, U1, V, H, blank, lo, hi,
+                                                    _ptr(dsc), st), "rnnt_b200_joint_bwd_ds")
+                # two plain library GEMMs on the staged bf16 gradient tile (fp32 accumulate/out)
+                dh = torch.mm(dsc, w2q, out_dtype=torch.float32)                       # (rows, H)
+                dw2x += torch.mm(dsc.t(), h_stash[lo * 128: hi * 128], out_dtype=torch.float32)
+                _lib.check(L.rnnt_b200_dh_reduce(_ptr(dh), _ptr(h_stash), _ptr(act_lens), _ptr(label_lens),
+                                                 _ptr(tile_utt), _ptr(tile_cell0), _ptr(n_tiles), B, T, U1,
+                                                 H, lo, hi, _ptr(dpe), _ptr(dpd), st), "rnnt_b200_dh_reduce")
+            dw2 = dw2x[:V, :H].contiguous()
+            db2 = dw2x[:V, H].contiguous()
+        return dpe, dpd, dw2, db2, None, None, None, None
+
+
+def joint_rnnt_loss(enc_state, dec_state, w1, b1, w2, b2, labels, act_lens, label_lens,
+                    blank: int = 0, reduction: str = "mean"):
+    """Fused replacement of rnnt/model.py:68 + :70.
+
+    enc_state (B,T,E), dec_state (B,U+1,D) float32 CUDA; w1 (H,E+D) = forward_layer.weight
+    (encoder columns first, model.py:31), b1 (H), w2 (V,H) = project_layer.weight, b2 (V).
+    Autograd reaches enc_state, dec_state and all four joint parameters.
+    """
+    if enc_state.dim() != 3 or dec_state.dim() != 3:
+        raise ValueError("enc_state must be (B,T,E) and dec_state (B,U+1,D)")
+    _check_loss_args((), enc_state.dtype, enc_state.device, labels, act_lens, label_lens, "enc_state")
+    B, T, E = enc_state.shape
+    if dec_state.shape[0] != B:
+        raise ValueError("enc_state and dec_state disagree on the batch size")
+    U1, D = dec_state.shape[1], dec_state.shape[2]
+    H, V = w1.shape[0], w2.shape[0]
+    if w1.shape[1] != E + D:
+        raise ValueError(f"forward_layer.weight is (H,{w1.shape[1]}) but E+D = {E + D}")
+    if w2.shape[1] != H or b1.shape != (H,) or b2.shape != (V,):
+        raise ValueError("joint parameter shapes are inconsistent")
+    if H % 64 or not 64 <= H <= 512:
+        raise ValueError(f"joint inner size {H} unsupported: need a multiple of 64 in [64,512]")
+    _check_lens(B, T, U1, labels, act_lens, label_lens)
+    if not 0 <= blank < V:
+        raise ValueError(f"blank {blank} not in [0,{V})")
+    if U1 > 1024:
+        raise ValueError("U+1 > 1024 is not supported by the lattice kernel")
+    # first joint layer, decomposed (two small library GEMMs instead of one over B*T*(U+1) rows)
+    pe = F.linear(enc_state, w1[:, :E], b1).contiguous()
+    pd = F.linear(dec_state, w1[:, E:]).contiguous()
+    loss_b = _JointLossFn.apply(pe, pd, w2.contiguous(), b2.contiguous(), labels, act_lens, label_lens,
+                                int(blank))
+    return _reduce(loss_b, reduction)
+
+
+class JointNet(nn.Module):
+    """Same parameters, names and forward semantics as rnnt/model.py:9-37, so reference
+    checkpoints (utils.py:74-85, key 'joint') load unchanged. ``forward`` materialises logits
+    (needed by greedy decoding, model.py:90); training should use ``JointRNNTLoss``."""
+
+    def __init__(self, input_size: int, inner_dim: int, vocab_size: int):
+        super().__init__()
+        self.forward_layer = nn.Linear(input_size, inner_dim, bias=True)
+        self.tanh = nn.Tanh()
+        self.project_layer = nn.Linear(inner_dim, vocab_size, bias=True)
+
+    def forward(self, enc_state, dec_state):
+        if enc_state.dim() == 3 and dec_state.dim() == 3:
+            E = enc_state.shape[-1]
+            w1 = self.forward_layer.weight
+            pe = F.linear(enc_state, w1[:, :E], self.forward_layer.bias)
+            pd = F.linear(dec_state, w1[:, E:])
+            hidden = self.tanh(pe.unsqueeze(2) + pd.unsqueeze(1))
+        else:
+            assert enc_state.dim() == dec_state.dim()
+            hidden = self.tanh(self.forward_layer(torch.cat((enc_state, dec_state), dim=-1)))
+        return self.project_layer(hidden)
+
+
+class JointRNNTLoss(nn.Module):
+    """``JointRNNTLoss(joint)(enc_state, dec_state, labels, act_lens, label_lens) -> loss``.
+
+    ``joint`` is any module with ``forward_layer`` / ``project_layer`` Linear children (this
+    package's ``JointNet`` or the reference's). Weight tying with the decoder embedding
+    (model.py:55-57) works because gradients accumulate into whatever tensor
+    ``project_layer.weight`` is."""
+
+    def __init__(self, joint: nn.Module, blank: int = 0, reduction: str = "mean"):
+        super().__init__()
+        self.joint = joint
+        self.blank = blank
+        self.reduction = reduction
+
+    def forward(self, enc_state, dec_state, labels, act_lens, label_lens):
+        j = self.joint
+        return joint_rnnt_loss(enc_state, dec_state, j.forward_layer.weight, j.forward_layer.bias,
+                               j.project_layer.weight, j.project_layer.bias, labels, act_lens,
+                               label_lens, self.blank, self.reduction)
+
+
+def selftest_gemm(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """C = A . B^T through the bare tcgen05/TMA plumbing (bf16 in, fp32 out)."""
+    M, K = a.shape
+    N = b.shape[0]
+    c = torch.empty(M, N, dtype=torch.float32, device=a.device)
+    with torch.cuda.device(a.device):
+        _lib.check(_lib.lib().rnnt_b200_selftest_gemm(_ptr(a), _ptr(b), _ptr(c), M, N, K, _stream()),
+                   "rnnt_b200_selftest_gemm")
+    return c

@@ -1,0 +1,32 @@
+// Shared helpers for the rnnt_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/rnnt_b200.h"
+
+#define RNNT_TILE_M 128            // lattice cells per GEMM tile
+#define RNNT_LOG2E 1.4426950408889634f
+#define RNNT_LN2 0.6931471805599453f
+#define RNNT_NEG_BIG (-1.0e30f)    // bias of padded vocabulary columns (log2 domain)
+
+#define RNNT_CUDA_RETURN_IF_ERROR()                        \
+  do {                                                     \
+    cudaError_t e__ = cudaGetLastError();                  \
+    if (e__ != cudaSuccess) return (int)e__;               \
+  } while (0)
+
+// Anti-diagonal-major plane index of cell (t,u) of utterance b (see rnnt_b200.h).
+__host__ __device__ __forceinline__ size_t plane_index(int b, int t, int u, int T, int U1) {
+  return ((size_t)b * (size_t)(T + U1 - 1) + (size_t)(t + u)) * (size_t)U1 + (size_t)u;
+}
+
+__device__ __forceinline__ int clamp_int(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+// log(exp(a)+exp(b)) in float64 with -inf handling.
+__device__ __forceinline__ double log_add_exp(double a, double b) {
+  double m = fmax(a, b);
+  double d = -fabs(a - b);
+  // d is NaN only when both are -inf (inf-inf); then m = -inf is the answer.
+  if (!(d == d)) return m;
+  return m + log1p(exp(d));
+}

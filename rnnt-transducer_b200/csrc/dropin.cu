@@ -1,0 +1,198 @@
+// Boundary 1 (strict drop-in on materialised logits): the two HBM-streaming kernels
+// around the lattice.
+//
+//   logits_to_planes : replaces the log-softmax stage of warprnnt_pytorch.RNNTLoss
+//                      (/root/reference rnnt/model.py:70). Reads each
+//                      logit exactly once, emits 12 B per cell (lse, lp_blank, lp_label).
+//   planes_to_dlogits: the logit gradient (row a8), produced in the backward from the
+//                      occupation coefficients instead of being stashed in the forward.
+//
+// One warp per lattice cell; 16-byte vector loads/stores when V % 4 == 0; grid sized to a
+// multiple of the SM count with a grid-stride loop over cells.
+#include "common.cuh"
+
+namespace {
+
+constexpr int WARPS_PER_BLOCK = 8;
+
+__device__ __forceinline__ void online_merge(float& m, float& s, float m2, float s2) {
+  const float mn = fmaxf(m, m2);
+  // exp2f(-inf - finite) = 0; both -inf only before any element was seen.
+  const float a = (m == -INFINITY) ? 0.f : s * exp2f(m - mn);
+  const float b = (m2 == -INFINITY) ? 0.f : s2 * exp2f(m2 - mn);
+  m = mn;
+  s = a + b;
+}
+
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+logits_to_planes_kernel(const float* __restrict__ logits, const int32_t* __restrict__ labels,
+                        const int32_t* __restrict__ act_lens, const int32_t* __restrict__ label_lens,
+                        int B, int T, int U1, int V, int blank,
+                        float* __restrict__ lse_out, float* __restrict__ lpb_out,
+                        float* __restrict__ lpl_out) {
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = (long long)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  const long long nwarps = (long long)gridDim.x * WARPS_PER_BLOCK;
+  const long long ncell = (long long)B * T * U1;
+  const int U = U1 - 1;
+  for (long long cell = warp0; cell < ncell; cell += nwarps) {
+    const int b = (int)(cell / ((long long)T * U1));
+    const int r = (int)(cell - (long long)b * T * U1);
+    const int t = r / U1, u = r - t * U1;
+    const int Tb = clamp_int(act_lens[b], 1, T);
+    const int Ub = clamp_int(label_lens[b], 0, U);
+    if (t >= Tb || u > Ub) continue;  // warp-uniform
+    const float* x = logits + (size_t)cell * V;
+    // work in the log2 domain: z = x*log2(e)
+    float m = -INFINITY, s = 0.f;
+    if ((V & 3) == 0) {
+      const float4* x4 = reinterpret_cast<const float4*>(x);
+      const int n4 = V >> 2;
+      for (int i = lane; i < n4; i += 32) {
+        const float4 v = __ldcs(x4 + i);
+        const float z0 = v.x * RNNT_LOG2E, z1 = v.y * RNNT_LOG2E, z2 = v.z * RNNT_LOG2E, z3 = v.w * RNNT_LOG2E;
+        const float cm = fmaxf(fmaxf(z0, z1), fmaxf(z2, z3));
+        const float mn = fmaxf(m, cm);
+        s = s * exp2f(m - mn) + exp2f(z0 - mn) + exp2f(z1 - mn) + exp2f(z2 - mn) + exp2f(z3 - mn);
+        m = mn;
+      }
+    } else {
+      for (int i = lane; i < V; i += 32) {
+        const float z = __ldcs(x + i) * RNNT_LOG2E;
+        const float mn = fmaxf(m, z);
+        s = s * exp2f(m - mn) + exp2f(z - mn);
+        m = mn;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float m2 = __shfl_xor_sync(0xffffffffu, m, o);
+      const float s2 = __shfl_xor_sync(0xffffffffu, s, o);
+      online_merge(m, s, m2, s2);
+    }
+    if (lane == 0) {
+      const float lse = (m + log2f(s)) * RNNT_LN2;
+      const size_t idx = plane_index(b, t, u, T, U1);
+      lse_out[idx] = lse;
+      lpb_out[idx] = x[blank] - lse;
+      float ll = -INFINITY;
+      if (u < Ub) {
+        const int y = clamp_int(labels[(size_t)b * U + u], 0, V - 1);
+        ll = x[y] - lse;
+      }
+      lpl_out[idx] = ll;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+planes_to_dlogits_kernel(const float* __restrict__ logits, const int32_t* __restrict__ labels,
+                         const int32_t* __restrict__ act_lens, const int32_t* __restrict__ label_lens,
+                         int B, int T, int U1, int V, int blank,
+                         const float* __restrict__ lse_p, const float* __restrict__ cb_p,
+                         const float* __restrict__ cl_p, const float* __restrict__ scale,
+                         float* __restrict__ dlogits) {
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = (long long)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  const long long nwarps = (long long)gridDim.x * WARPS_PER_BLOCK;
+  const long long ncell = (long long)B * T * U1;
+  const int U = U1 - 1;
+  const bool vec = ((V & 3) == 0);
+  for (long long cell = warp0; cell < ncell; cell += nwarps) {
+    const int b = (int)(cell / ((long long)T * U1));
+    const int r = (int)(cell - (long long)b * T * U1);
+    const int t = r / U1, u = r - t * U1;
+    const int Tb = clamp_int(act_lens[b], 1, T);
+    const int Ub = clamp_int(label_lens[b], 0, U);
+    float* g = dlogits + (size_t)cell * V;
+    if (t >= Tb || u > Ub) {  // outside the valid window: exact zeros
+      if (vec) {
+        float4* g4 = reinterpret_cast<float4*>(g);
+        for (int i = lane; i < (V >> 2); i += 32) __stcs(g4 + i, make_float4(0.f, 0.f, 0.f, 0.f));
+      } else {
+        for (int i = lane; i < V; i += 32) __stcs(g + i, 0.f);
+      }
+      continue;
+    }
+    const float* x = logits + (size_t)cell * V;
+    const size_t idx = plane_index(b, t, u, T, U1);
+    const float sc = scale[b];
+    const float cb = cb_p[idx] * sc, cl = cl_p[idx] * sc;
+    const float c0 = cb + cl;
+    const float nl = -lse_p[idx] * RNNT_LOG2E;
+    const int y = (u < Ub) ? clamp_int(labels[(size_t)b * U + u], 0, V - 1) : -1;
+    if (vec) {
+      const float4* x4 = reinterpret_cast<const float4*>(x);
+      float4* g4 = reinterpret_cast<float4*>(g);
+      for (int i = lane; i < (V >> 2); i += 32) {
+        const float4 v = __ldcs(x4 + i);
+        float4 o;
+        o.x = exp2f(fmaf(v.x, RNNT_LOG2E, nl)) * c0;
+        o.y = exp2f(fmaf(v.y, RNNT_LOG2E, nl)) * c0;
+        o.z = exp2f(fmaf(v.z, RNNT_LOG2E, nl)) * c0;
+        o.w = exp2f(fmaf(v.w, RNNT_LOG2E, nl)) * c0;
+        const int v0 = i << 2;
+        if ((unsigned)(blank - v0) < 4u) {
+          const int k = blank - v0;
+          if (k == 0) o.x -= cb; else if (k == 1) o.y -= cb; else if (k == 2) o.z -= cb; else o.w -= cb;
+        }
+        if ((unsigned)(y - v0) < 4u) {
+          const int k = y - v0;
+          if (k == 0) o.x -= cl; else if (k == 1) o.y -= cl; else if (k == 2) o.z -= cl; else o.w -= cl;
+        }
+        __stcs(g4 + i, o);
+      }
+    } else {
+      for (int i = lane; i < V; i += 32) {
+        float o = exp2f(fmaf(__ldcs(x + i), RNNT_LOG2E, nl)) * c0;
+        if (i == blank) o -= cb;
+        if (i == y) o -= cl;
+        __stcs(g + i, o);
+      }
+    }
+  }
+}
+
+int grid_for_cells(long long ncell) {
+  long long blocks = (ncell + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK;
+  const long long cap = 148LL * 8 * 4;  // 4 waves of 8 resident CTAs per SM
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (int)blocks;
+}
+
+}  // namespace
+
+extern "C" int rnnt_b200_logits_to_planes(const float* logits, const int32_t* labels,
+                                          const int32_t* act_lens, const int32_t* label_lens,
+                                          int B, int T, int U1, int V, int blank, float* lse,
+                                          float* lp_blank, float* lp_label, void* stream) {
+  if (!logits || !act_lens || !label_lens || !lse || !lp_blank || !lp_label) return RNNT_B200_E_NULL;
+  if (U1 > 1 && !labels) return RNNT_B200_E_NULL;
+  if (B <= 0 || T <= 0 || U1 <= 0 || V <= 0) return RNNT_B200_E_SHAPE;
+  if (blank < 0 || blank >= V) return RNNT_B200_E_BLANK;
+  if ((V & 3) == 0 && ((uintptr_t)logits & 15)) return RNNT_B200_E_ALIGN;
+  const long long ncell = (long long)B * T * U1;
+  logits_to_planes_kernel<<<grid_for_cells(ncell), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
+      logits, labels, act_lens, label_lens, B, T, U1, V, blank, lse, lp_blank, lp_label);
+  RNNT_CUDA_RETURN_IF_ERROR();
+  return RNNT_B200_OK;
+}
+
+extern "C" int rnnt_b200_planes_to_dlogits(const float* logits, const int32_t* labels,
+                                           const int32_t* act_lens, const int32_t* label_lens,
+                                           int B, int T, int U1, int V, int blank, const float* lse,
+                                           const float* c_blank, const float* c_label,
+                                           const float* scale, float* dlogits, void* stream) {
+  if (!logits || !act_lens || !label_lens || !lse || !c_blank || !c_label || !scale || !dlogits)
+    return RNNT_B200_E_NULL;
+  if (U1 > 1 && !labels) return RNNT_B200_E_NULL;
+  if (B <= 0 || T <= 0 || U1 <= 0 || V <= 0) return RNNT_B200_E_SHAPE;
+  if (blank < 0 || blank >= V) return RNNT_B200_E_BLANK;
+  if ((V & 3) == 0 && (((uintptr_t)logits & 15) || ((uintptr_t)dlogits & 15))) return RNNT_B200_E_ALIGN;
+  const long long ncell = (long long)B * T * U1;
+  planes_to_dlogits_kernel<<<grid_for_cells(ncell), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
+      logits, labels, act_lens, label_lens, B, T, U1, V, blank, lse, c_blank, c_label, scale, dlogits);
+  RNNT_CUDA_RETURN_IF_ERROR();
+  return RNNT_B200_OK;
+}

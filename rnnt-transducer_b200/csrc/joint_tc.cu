@@ -1,0 +1,667 @@
+// Fused joint + log-softmax statistics on the 5th-gen tensor cores (tcgen05 / TMEM / TMA).
+//
+// Replaces, together, /root/reference rnnt/model.py:68 (JointNet.forward, model.py:18-37)
+// and the log-softmax stage of the loss call at model.py:70:
+//
+//   forward  : S[cell, v] = tanh(P_enc[b,t,:] + P_dec[b,u,:]) . W2[v,:] + b2[v]
+//              never leaves the SM: an online log-sum-exp epilogue reads the accumulators
+//              out of TMEM and emits 12 bytes per lattice cell (lse, lp_blank, lp_label).
+//   backward : the same GEMM is recomputed from the stashed bf16 hidden tile and the
+//              epilogue turns it into dS = scale*(softmax*(c_blank+c_label) - onehots), bf16.
+//
+// Work decomposition: lattice cells are flattened per utterance over the valid (t,u)
+// window and cut into tiles of 128 cells (the UMMA M). A persistent CTA per SM walks
+// tiles blockIdx.x, +gridDim.x, ...; for each tile it sweeps the vocabulary in BN-column
+// tiles with K = H. Warp roles (512 threads):
+//   warps 0-7   epilogue: TMEM -> registers; warp w owns TMEM lanes 32*(w&3)..+31 (one
+//               lattice cell per thread) and column half (w>>2) of the BN-wide tile
+//   warps 8-11  A producer (forward): tanh(P_enc+P_dec) -> bf16 -> 128B-swizzled smem tile
+//   warp 12     TMA producer: W2 tiles (and, backward, the stashed h tile)
+//   warp 13     MMA issuer (one elected thread)
+//   warp 14     TMEM allocator
+//   warp 15     TMA producer of the stashed h tile (backward)
+// Pipelines: W2 smem ring (full/empty mbarriers), A tile per 64-wide K block
+// (a_full/a_empty so the next tile's tanh overlaps the last vocabulary tile's MMAs), and a
+// double-buffered TMEM accumulator (acc_full/acc_empty) so the epilogue of vocabulary
+// tile j overlaps the MMAs of tile j+1.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include "common.cuh"
+#include "sm100_ptx.cuh"
+
+using namespace sm100;
+
+namespace {
+
+constexpr int kThreads = 512;
+constexpr int kEpiWarps = 8;
+constexpr int kProdThreads = 128;
+constexpr int kKBlock = 64;              // A tile K block (128-byte swizzle span of bf16)
+constexpr int kBK = 32;                  // W2 stage K extent (64-byte swizzle span of bf16)
+constexpr int kABlockBytes = RNNT_TILE_M * 128;
+constexpr int kMaxStages = 8;
+constexpr int kSmemLimit = 232448;       // 227 KB opt-in maximum per CTA
+
+struct TileInfo {  // per-row info shared inside the producer group
+  int pe_off;      // element offset of P_enc[b,t,0]; -1 = row past the utterance's last cell
+  int pd_off;
+};
+
+struct SharedCtl {
+  uint64_t a_full[8], a_empty[8];
+  uint64_t b_full[kMaxStages], b_empty[kMaxStages];
+  uint64_t acc_full[2], acc_empty[2];
+  uint32_t tmem_base;
+  uint32_t pad;
+  TileInfo info[RNNT_TILE_M];
+  float4 red[2][RNNT_TILE_M];
+};
+
+struct JointParams {
+  const float* pe;
+  const float* pd;
+  const float* b2l;
+  const int32_t* labels;
+  const int32_t* act_lens;
+  const int32_t* label_lens;
+  const int32_t* tile_utt;
+  const int32_t* tile_cell0;
+  const int32_t* n_tiles;
+  // forward outputs
+  float* lse;
+  float* lpb;
+  float* lpl;
+  __nv_bfloat16* h_stash;
+  // backward inputs/outputs
+  const float* cb;
+  const float* cl;
+  const float* scale;
+  __nv_bfloat16* ds;
+  int B, T, U1, V, Vpad, H, blank;
+  int tile_lo, tile_hi;  // tile range of this launch
+  int stages;
+};
+
+__host__ __device__ inline int smem_bytes_for(int H, int BN, int stages) {
+  return 1024 /*align slack*/ + (H / kKBlock) * kABlockBytes + stages * BN * 64 + (int)sizeof(SharedCtl);
+}
+
+__device__ __forceinline__ float tanh_accurate(float x) {
+  // tanh(x) = 1 - 2/(exp(2x)+1); two MUFU ops, |err| ~1e-7 absolute.
+  const float e = ex2_approx(x * (2.f * RNNT_LOG2E));
+  return 1.f - __fdividef(2.f, e + 1.f);
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// Locate row `r` of a tile: returns false when the row lies past the utterance's last cell.
+struct RowCoord {
+  int b, t, u, Ub;
+  bool valid;
+};
+__device__ __forceinline__ RowCoord locate_row(const JointParams& p, int tile, int r) {
+  RowCoord c;
+  c.b = p.tile_utt[tile];
+  const int cell = p.tile_cell0[tile] + r;
+  const int Tb = clamp_int(p.act_lens[c.b], 1, p.T);
+  c.Ub = clamp_int(p.label_lens[c.b], 0, p.U1 - 1);
+  const int w = c.Ub + 1;
+  c.valid = cell < Tb * w;
+  c.t = cell / w;
+  c.u = cell - c.t * w;
+  return c;
+}
+
+// ---------------------------------------------------------------------------------------
+// MODE 0 = forward (online LSE epilogue), MODE 1 = backward dS.
+// ---------------------------------------------------------------------------------------
+template <int BN, int MODE>
+__global__ void __launch_bounds__(kThreads, 1)
+joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__ CUtensorMap map_h,
+             const JointParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const int KB = p.H / kKBlock;      // A K-blocks of 64
+  const int KS = p.H / kBK;          // W2 stages per vocabulary tile (K steps of 32)
+  const int NV = p.Vpad / BN;        // vocabulary tiles
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + KB * kABlockBytes;
+  constexpr int kStageBytes = BN * 64;
+  SharedCtl* ctl = reinterpret_cast<SharedCtl*>(smem_b + p.stages * kStageBytes);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int n_tiles = min(p.n_tiles[0], p.tile_hi);
+
+  if (warp == 12 && lane == 0) {
+    tma_prefetch_desc(&map_w2);
+    if (MODE == 1) tma_prefetch_desc(&map_h);
+  }
+  if (warp == 13 && lane == 0) {
+    for (int i = 0; i < 8; ++i) {
+      mbar_init(&ctl->a_full[i], MODE == 0 ? kProdThreads : 1);
+      mbar_init(&ctl->a_empty[i], 1);
+    }
+    for (int i = 0; i < kMaxStages; ++i) {
+      mbar_init(&ctl->b_full[i], 1);
+      mbar_init(&ctl->b_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&ctl->acc_full[i], 1);
+      mbar_init(&ctl->acc_empty[i], kEpiWarps);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 14) {
+    tmem_alloc(&ctl->tmem_base, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = ctl->tmem_base;
+
+  if (warp < kEpiWarps) {
+    // =========================== EPILOGUE ===========================
+    const int q = warp & 3, half = warp >> 2;
+    const int row = q * 32 + lane;
+    constexpr int HALF = BN / 2;
+    constexpr int NCH = HALF / 32;
+    uint32_t acc_it = 0;
+    int it = 0;
+    for (int tile = p.tile_lo + blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const RowCoord rc = locate_row(p, tile, row);
+      int label = -1;
+      size_t pidx = 0;
+      if (rc.valid) {
+        pidx = plane_index(rc.b, rc.t, rc.u, p.T, p.U1);
+        if (rc.u < rc.Ub) label = clamp_int(p.labels[(size_t)rc.b * (p.U1 - 1) + rc.u], 0, p.V - 1);
+      }
+      // forward state
+      float m = -INFINITY, s = 0.f, zb = 0.f, zl = 0.f;
+      // backward per-row constants
+      float nlse2 = 0.f, c0 = 0.f, cbs = 0.f, cls = 0.f;
+      if (MODE == 1) {
+        nlse2 = RNNT_NEG_BIG;  // invalid rows: exp2(z + nlse2) == 0 exactly
+        if (rc.valid) {
+          const float sc = p.scale[rc.b];
+          cbs = p.cb[pidx] * sc;
+          cls = (rc.u < rc.Ub) ? p.cl[pidx] * sc : 0.f;
+          c0 = cbs + cls;
+          nlse2 = -p.lse[pidx] * RNNT_LOG2E;
+        }
+      }
+      for (int vt = 0; vt < NV; ++vt, ++acc_it) {
+        const uint32_t buf = acc_it & 1;
+        mbar_wait(&ctl->acc_full[buf], (acc_it >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          const int col0 = vt * BN + half * HALF + c * 32;
+          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN + half * HALF + c * 32;
+          float z[32];
+          tmem_ld_32x32(taddr, z);
+          tmem_ld_wait();
+          const float4* b4 = reinterpret_cast<const float4*>(p.b2l + col0);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 bb = __ldg(b4 + j);
+            z[4 * j + 0] = fmaf(z[4 * j + 0], RNNT_LOG2E, bb.x);
+            z[4 * j + 1] = fmaf(z[4 * j + 1], RNNT_LOG2E, bb.y);
+            z[4 * j + 2] = fmaf(z[4 * j + 2], RNNT_LOG2E, bb.z);
+            z[4 * j + 3] = fmaf(z[4 * j + 3], RNNT_LOG2E, bb.w);
+          }
+          if (MODE == 0) {
+            float cm = z[0];
+#pragma unroll
+            for (int j = 1; j < 32; ++j) cm = fmaxf(cm, z[j]);
+            const float mn = fmaxf(m, cm);
+            float acc = 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) acc += ex2_approx(z[j] - mn);
+            s = s * ex2_approx(m - mn) + acc;
+            m = mn;
+            if ((unsigned)(p.blank - col0) < 32u) {
+              const int k = p.blank - col0;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) zb = (j == k) ? z[j] : zb;
+            }
+            if ((unsigned)(label - col0) < 32u) {
+              const int k = label - col0;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) zl = (j == k) ? z[j] : zl;
+            }
+          } else {
+            float g[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) g[j] = ex2_approx(z[j] + nlse2) * c0;
+            if ((unsigned)(p.blank - col0) < 32u) {
+              const int k = p.blank - col0;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) g[j] -= (j == k) ? cbs : 0.f;
+            }
+            if ((unsigned)(label - col0) < 32u) {
+              const int k = label - col0;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) g[j] -= (j == k) ? cls : 0.f;
+            }
+            uint4* dst = reinterpret_cast<uint4*>(p.ds + ((size_t)(tile - p.tile_lo) * RNNT_TILE_M + row) * p.Vpad + col0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint4 o;
+              o.x = pack_bf16x2(g[8 * j + 0], g[8 * j + 1]);
+              o.y = pack_bf16x2(g[8 * j + 2], g[8 * j + 3]);
+              o.z = pack_bf16x2(g[8 * j + 4], g[8 * j + 5]);
+              o.w = pack_bf16x2(g[8 * j + 6], g[8 * j + 7]);
+              dst[j] = o;
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&ctl->acc_empty[buf]);
+      }
+      if (MODE == 0) {
+        const int slot = it & 1;
+        if (half == 1) ctl->red[slot][row] = make_float4(m, s, zb, zl);
+        named_bar_sync(1, kEpiWarps * 32);
+        if (half == 0 && rc.valid) {
+          const float4 o = ctl->red[slot][row];
+          const float mn = fmaxf(m, o.x);
+          const float st = s * ex2_approx(m - mn) + o.y * ex2_approx(o.x - mn);
+          const float lse2 = mn + log2f(st);
+          p.lse[pidx] = lse2 * RNNT_LN2;
+          p.lpb[pidx] = (zb + o.z - lse2) * RNNT_LN2;
+          p.lpl[pidx] = (label >= 0) ? (zl + o.w - lse2) * RNNT_LN2 : -INFINITY;
+        }
+      }
+    }
+    if (MODE == 1) {
+      // tiles of this launch past the end of the tile table: dS rows are defined as zero
+      const int first_dead = max(n_tiles, p.tile_lo);
+      const int epi_tid = threadIdx.x;  // 0..255
+      for (int tile = first_dead + blockIdx.x; tile < p.tile_hi; tile += gridDim.x) {
+        uint4* dst = reinterpret_cast<uint4*>(p.ds + (size_t)(tile - p.tile_lo) * RNNT_TILE_M * p.Vpad);
+        const size_t n16 = (size_t)RNNT_TILE_M * p.Vpad / 8;
+        for (size_t i = epi_tid; i < n16; i += kEpiWarps * 32) dst[i] = make_uint4(0, 0, 0, 0);
+      }
+    }
+  } else if (warp < 12) {
+    // =========================== A PRODUCER (forward only) ===========================
+    if (MODE == 0) {
+      const int ptid = threadIdx.x - kEpiWarps * 32;  // 0..127
+      const int chunk = ptid & 7;
+      const int row0 = ptid >> 3;
+      const int hp = p.H + 8;
+      int it = 0;
+      for (int tile = p.tile_lo + blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        {
+          const RowCoord rc = locate_row(p, tile, ptid);
+          TileInfo ti;
+          ti.pe_off = rc.valid ? (rc.b * p.T + rc.t) * p.H : -1;
+          ti.pd_off = rc.valid ? (rc.b * p.U1 + rc.u) * p.H : -1;
+          named_bar_sync(2, kProdThreads);  // previous tile's readers are done with info[]
+          ctl->info[ptid] = ti;
+          named_bar_sync(2, kProdThreads);
+          if (p.h_stash) {  // "ones" column block H..H+7 (column H = 1 for valid cells)
+            uint4 o = make_uint4(rc.valid ? 0x00003F80u : 0u, 0u, 0u, 0u);
+            *reinterpret_cast<uint4*>(p.h_stash + ((size_t)tile * RNNT_TILE_M + ptid) * hp + p.H) = o;
+          }
+        }
+        for (int kb = 0; kb < KB; ++kb) {
+          mbar_wait(&ctl->a_empty[kb], (it & 1) ^ 1);
+          uint8_t* ablk = smem_a + kb * kABlockBytes;
+          const int k0 = kb * kKBlock + chunk * 8;
+#pragma unroll 4
+          for (int i = 0; i < RNNT_TILE_M / 16; ++i) {
+            const int row = row0 + 16 * i;
+            const TileInfo ti = ctl->info[row];
+            uint4 o = make_uint4(0u, 0u, 0u, 0u);
+            if (ti.pe_off >= 0) {
+              const float4* e4 = reinterpret_cast<const float4*>(p.pe + ti.pe_off + k0);
+              const float4* d4 = reinterpret_cast<const float4*>(p.pd + ti.pd_off + k0);
+              const float4 e0 = __ldg(e4), e1 = __ldg(e4 + 1), d0 = __ldg(d4), d1 = __ldg(d4 + 1);
+              o.x = pack_bf16x2(tanh_accurate(e0.x + d0.x), tanh_accurate(e0.y + d0.y));
+              o.y = pack_bf16x2(tanh_accurate(e0.z + d0.z), tanh_accurate(e0.w + d0.w));
+              o.z = pack_bf16x2(tanh_accurate(e1.x + d1.x), tanh_accurate(e1.y + d1.y));
+              o.w = pack_bf16x2(tanh_accurate(e1.z + d1.z), tanh_accurate(e1.w + d1.w));
+            }
+            *reinterpret_cast<uint4*>(ablk + row * 128 + ((chunk ^ (row & 7)) << 4)) = o;
+            if (p.h_stash)
+              *reinterpret_cast<uint4*>(p.h_stash + ((size_t)tile * RNNT_TILE_M + row) * hp + k0) = o;
+          }
+          fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the MMA (async proxy)
+          mbar_arrive(&ctl->a_full[kb]);
+        }
+      }
+      if (p.h_stash) {
+        // rows of tiles past the end of the tile table must be finite (they meet dS = 0 in a GEMM)
+        const int first_dead = max(n_tiles, p.tile_lo);
+        for (int tile = first_dead + blockIdx.x; tile < p.tile_hi; tile += gridDim.x) {
+          uint4* dst = reinterpret_cast<uint4*>(p.h_stash + (size_t)tile * RNNT_TILE_M * hp);
+          const int n16 = RNNT_TILE_M * hp / 8;
+          for (int i = ptid; i < n16; i += kProdThreads) dst[i] = make_uint4(0, 0, 0, 0);
+        }
+      }
+    }
+  } else if (warp == 12) {
+    // =========================== TMA PRODUCER ===========================
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      int it = 0;
+      for (int tile = p.tile_lo + blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        for (int vt = 0; vt < NV; ++vt) {
+          for (int ks = 0; ks < KS; ++ks) {
+            mbar_wait(&ctl->b_empty[stage], phase ^ 1);
+            mbar_arrive_expect_tx(&ctl->b_full[stage], kStageBytes);
+            tma_load_2d(smem_b + stage * kStageBytes, &map_w2, &ctl->b_full[stage], ks * kBK, vt * BN);
+            if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 15) {
+    // =========================== A TILE TMA (backward only) ===========================
+    if (MODE == 1 && lane == 0) {
+      int it = 0;
+      for (int tile = p.tile_lo + blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        for (int kb = 0; kb < KB; ++kb) {
+          mbar_wait(&ctl->a_empty[kb], (it & 1) ^ 1);
+          mbar_arrive_expect_tx(&ctl->a_full[kb], kABlockBytes);
+          tma_load_2d(smem_a + kb * kABlockBytes, &map_h, &ctl->a_full[kb], kb * kKBlock,
+                      tile * RNNT_TILE_M);
+        }
+      }
+    }
+  } else if (warp == 13) {
+    // =========================== MMA ISSUER ===========================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(RNNT_TILE_M, BN);
+      uint32_t stage = 0, phase = 0, acc_it = 0;
+      int it = 0;
+      for (int tile = p.tile_lo + blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        for (int vt = 0; vt < NV; ++vt, ++acc_it) {
+          const uint32_t buf = acc_it & 1;
+          mbar_wait(&ctl->acc_empty[buf], ((acc_it >> 1) & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t tmem_d = tmem_base + buf * BN;
+          for (int ks = 0; ks < KS; ++ks) {
+            const int kb = ks >> 1;
+            if (vt == 0 && (ks & 1) == 0) mbar_wait(&ctl->a_full[kb], it & 1);
+            mbar_wait(&ctl->b_full[stage], phase);
+            tc_fence_after();
+            const uint64_t adesc =
+                umma_desc_kmajor<128>(smem_u32(smem_a + kb * kABlockBytes) + (ks & 1) * 64);
+            const uint64_t bdesc = umma_desc_kmajor<64>(smem_u32(smem_b + stage * kStageBytes));
+#pragma unroll
+            for (int k = 0; k < kBK / 16; ++k)
+              umma_bf16_ss(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | k) != 0);
+            umma_commit(&ctl->b_empty[stage]);
+            if (vt == NV - 1 && (ks & 1) == 1) umma_commit(&ctl->a_empty[kb]);
+            if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
+          }
+          umma_commit(&ctl->acc_full[buf]);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 14) tmem_dealloc(tmem_base, 512);
+}
+
+// ---------------------------------------------------------------------------------------
+// Plain C = A . B^T (bf16 in, fp32 out): exercises exactly the descriptors, swizzles, TMA
+// maps, TMEM addressing and barrier protocol used above, with nothing else in the way.
+// One CTA per 128 x BN output tile. 6 warps: 0 TMA, 1 MMA, 2-5 epilogue (+TMEM alloc).
+// ---------------------------------------------------------------------------------------
+template <int BN>
+__global__ void __launch_bounds__(192, 1)
+selftest_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                     float* __restrict__ C, int N, int K) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  constexpr int STAGES = 4;
+  constexpr int kAStage = RNNT_TILE_M * 128;  // 128 x 64 bf16, SW128
+  constexpr int kBStage = BN * 64;            // BN x 32 bf16, SW64 (two per A stage)
+  uint8_t* sa = smem;
+  uint8_t* sb = smem + STAGES * kAStage;
+  struct Ctl { uint64_t full[STAGES], empty[STAGES], acc; uint32_t tmem; };
+  Ctl* ctl = reinterpret_cast<Ctl*>(sb + STAGES * 2 * kBStage);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * RNNT_TILE_M, n0 = blockIdx.y * BN;
+  const int KBn = K / 64;
+  if (warp == 0 && lane == 0) {
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
+    mbar_init(&ctl->acc, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) { tmem_alloc(&ctl->tmem, 256); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = ctl->tmem;
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int kb = 0; kb < KBn; ++kb) {
+        mbar_wait(&ctl->empty[stage], phase ^ 1);
+        mbar_arrive_expect_tx(&ctl->full[stage], kAStage + 2 * kBStage);
+        tma_load_2d(sa + stage * kAStage, &map_a, &ctl->full[stage], kb * 64, m0);
+        tma_load_2d(sb + (stage * 2 + 0) * kBStage, &map_b, &ctl->full[stage], kb * 64, n0);
+        tma_load_2d(sb + (stage * 2 + 1) * kBStage, &map_b, &ctl->full[stage], kb * 64 + 32, n0);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(RNNT_TILE_M, BN);
+      uint32_t stage = 0, phase = 0;
+      for (int kb = 0; kb < KBn; ++kb) {
+        mbar_wait(&ctl->full[stage], phase);
+        tc_fence_after();
+        for (int h2 = 0; h2 < 2; ++h2) {
+          const uint64_t adesc = umma_desc_kmajor<128>(smem_u32(sa + stage * kAStage) + h2 * 64);
+          const uint64_t bdesc = umma_desc_kmajor<64>(smem_u32(sb + (stage * 2 + h2) * kBStage));
+          for (int k = 0; k < 2; ++k)
+            umma_bf16_ss(tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | h2 | k) != 0);
+        }
+        umma_commit(&ctl->empty[stage]);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      umma_commit(&ctl->acc);
+    }
+  } else {
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    mbar_wait(&ctl->acc, 0);
+    tc_fence_after();
+    for (int c = 0; c < BN / 32; ++c) {
+      float v[32];
+      tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + c * 32, v);
+      tmem_ld_wait();
+      float* dst = C + (size_t)(m0 + row) * N + n0 + c * 32;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) dst[j] = v[j];
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 256);
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;  // idempotent, benign race: same value written
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)ptr;
+  }
+  return fn;
+}
+
+// bf16 row-major matrix (rows x cols, row pitch in elements) -> 2-D tiled map with box
+// (box_cols x box_rows) and the given swizzle.
+int make_map_bf16(CUtensorMap* m, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_elems,
+                  uint32_t box_cols, uint32_t box_rows, CUtensorMapSwizzle sw) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return RNNT_B200_E_DRIVER;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {pitch_elems * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? RNNT_B200_OK : RNNT_B200_E_DRIVER;
+}
+
+int sm_count() {
+  int dev = 0, n = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  return n;
+}
+
+int pick_stages(int H, int BN) {
+  int s = kMaxStages;
+  while (s > 2 && smem_bytes_for(H, BN, s) > kSmemLimit) --s;
+  return s;
+}
+
+template <int BN, int MODE>
+int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, JointParams& p, cudaStream_t st) {
+  p.stages = pick_stages(p.H, BN);
+  const int smem = smem_bytes_for(p.H, BN, p.stages);
+  if (smem > kSmemLimit) return RNNT_B200_E_SHAPE;
+  cudaError_t e = cudaFuncSetAttribute(joint_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return (int)e;
+  int grid = sm_count();
+  const int ntile = p.tile_hi - p.tile_lo;
+  if (grid > ntile) grid = ntile;
+  if (grid < 1) return RNNT_B200_OK;
+  joint_kernel<BN, MODE><<<grid, kThreads, smem, st>>>(mw, mh, p);
+  RNNT_CUDA_RETURN_IF_ERROR();
+  return RNNT_B200_OK;
+}
+
+template <int MODE>
+int dispatch_joint(JointParams& p, const void* w2q, const void* h_stash, int max_tiles, cudaStream_t st) {
+  const int BN = rnnt_b200_vocab_tile(p.V);
+  CUtensorMap mw, mh;
+  int rc = make_map_bf16(&mw, w2q, p.Vpad, p.H, p.H, kBK, BN, CU_TENSOR_MAP_SWIZZLE_64B);
+  if (rc) return rc;
+  if (MODE == 1) {
+    rc = make_map_bf16(&mh, h_stash, (uint64_t)max_tiles * RNNT_TILE_M, p.H, p.H + 8, kKBlock, RNNT_TILE_M,
+                       CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+  } else {
+    mh = mw;
+  }
+  switch (BN) {
+    case 64: return launch_joint<64, MODE>(mw, mh, p, st);
+    case 128: return launch_joint<128, MODE>(mw, mh, p, st);
+    default: return launch_joint<256, MODE>(mw, mh, p, st);
+  }
+}
+
+int check_common(int B, int T, int U1, int V, int H, int blank) {
+  if (B <= 0 || T <= 0 || U1 <= 0 || V <= 0) return RNNT_B200_E_SHAPE;
+  if (H < 64 || H > 512 || (H & 63)) return RNNT_B200_E_SHAPE;
+  if (blank < 0 || blank >= V) return RNNT_B200_E_BLANK;
+  if ((long long)B * T * H > 0x7fffffffLL || (long long)B * U1 * H > 0x7fffffffLL) return RNNT_B200_E_SHAPE;
+  if (rnnt_b200_max_tiles(B, T, U1) < 0) return RNNT_B200_E_SHAPE;
+  return RNNT_B200_OK;
+}
+
+}  // namespace
+
+extern "C" int rnnt_b200_joint_fwd(const float* p_enc, const float* p_dec, const void* w2_bf16,
+                                   const float* b2_log2, const int32_t* labels, const int32_t* act_lens,
+                                   const int32_t* label_lens, const int32_t* tile_utt,
+                                   const int32_t* tile_cell0, const int32_t* n_tiles, int B, int T, int U1,
+                                   int V, int H, int blank, float* lse, float* lp_blank, float* lp_label,
+                                   void* h_stash, void* stream) {
+  if (!p_enc || !p_dec || !w2_bf16 || !b2_log2 || !act_lens || !label_lens || !tile_utt || !tile_cell0 ||
+      !n_tiles || !lse || !lp_blank || !lp_label)
+    return RNNT_B200_E_NULL;
+  if (U1 > 1 && !labels) return RNNT_B200_E_NULL;
+  int rc = check_common(B, T, U1, V, H, blank);
+  if (rc) return rc;
+  if (((uintptr_t)p_enc & 15) || ((uintptr_t)p_dec & 15) || ((uintptr_t)w2_bf16 & 127) ||
+      ((uintptr_t)b2_log2 & 15) || ((uintptr_t)h_stash & 15))
+    return RNNT_B200_E_ALIGN;
+  JointParams p = {};
+  p.pe = p_enc; p.pd = p_dec; p.b2l = b2_log2; p.labels = labels; p.act_lens = act_lens;
+  p.label_lens = label_lens; p.tile_utt = tile_utt; p.tile_cell0 = tile_cell0; p.n_tiles = n_tiles;
+  p.lse = lse; p.lpb = lp_blank; p.lpl = lp_label; p.h_stash = (__nv_bfloat16*)h_stash;
+  p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vpad = rnnt_b200_vocab_pad(V); p.H = H; p.blank = blank;
+  p.tile_lo = 0; p.tile_hi = rnnt_b200_max_tiles(B, T, U1);
+  return dispatch_joint<0>(p, w2_bf16, nullptr, p.tile_hi, (cudaStream_t)stream);
+}
+
+extern "C" int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, const float* b2_log2,
+                                      const int32_t* labels, const int32_t* act_lens,
+                                      const int32_t* label_lens, const int32_t* tile_utt,
+                                      const int32_t* tile_cell0, const int32_t* n_tiles, const float* lse,
+                                      const float* c_blank, const float* c_label, const float* scale, int B,
+                                      int T, int U1, int V, int H, int blank, int tile_lo, int tile_hi,
+                                      void* ds, void* stream) {
+  if (!h_stash || !w2_bf16 || !b2_log2 || !act_lens || !label_lens || !tile_utt || !tile_cell0 || !n_tiles ||
+      !lse || !c_blank || !c_label || !scale || !ds)
+    return RNNT_B200_E_NULL;
+  if (U1 > 1 && !labels) return RNNT_B200_E_NULL;
+  int rc = check_common(B, T, U1, V, H, blank);
+  if (rc) return rc;
+  const int max_tiles = rnnt_b200_max_tiles(B, T, U1);
+  if (tile_lo < 0 || tile_hi < tile_lo || tile_hi > max_tiles) return RNNT_B200_E_SHAPE;
+  if (((uintptr_t)h_stash & 127) || ((uintptr_t)w2_bf16 & 127) || ((uintptr_t)b2_log2 & 15) ||
+      ((uintptr_t)ds & 15))
+    return RNNT_B200_E_ALIGN;
+  if (tile_hi == tile_lo) return RNNT_B200_OK;
+  JointParams p = {};
+  p.b2l = b2_log2; p.labels = labels; p.act_lens = act_lens; p.label_lens = label_lens;
+  p.tile_utt = tile_utt; p.tile_cell0 = tile_cell0; p.n_tiles = n_tiles;
+  p.lse = const_cast<float*>(lse); p.cb = c_blank; p.cl = c_label; p.scale = scale;
+  p.ds = (__nv_bfloat16*)ds;
+  p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vpad = rnnt_b200_vocab_pad(V); p.H = H; p.blank = blank;
+  p.tile_lo = tile_lo; p.tile_hi = tile_hi;
+  return dispatch_joint<1>(p, w2_bf16, h_stash, max_tiles, (cudaStream_t)stream);
+}
+
+extern "C" int rnnt_b200_selftest_gemm(const void* a_bf16, const void* b_bf16, float* c, int M, int N,
+                                       int K, void* stream) {
+  if (!a_bf16 || !b_bf16 || !c) return RNNT_B200_E_NULL;
+  if (M <= 0 || N <= 0 || K <= 0 || (M % 128) || (N % 64) || (K % 64)) return RNNT_B200_E_SHAPE;
+  const int BN = (N % 256 == 0) ? 256 : 64;
+  CUtensorMap ma, mb;
+  int rc = make_map_bf16(&ma, a_bf16, M, K, K, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  rc = make_map_bf16(&mb, b_bf16, N, K, K, 32, BN, CU_TENSOR_MAP_SWIZZLE_64B);
+  if (rc) return rc;
+  const int smem = 1024 + 4 * (128 * 128) + 4 * 2 * BN * 64 + 256;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e;
+  if (BN == 256) {
+    e = cudaFuncSetAttribute(selftest_gemm_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+    selftest_gemm_kernel<256><<<dim3(M / 128, N / 256), 192, smem, st>>>(ma, mb, c, N, K);
+  } else {
+    e = cudaFuncSetAttribute(selftest_gemm_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+    selftest_gemm_kernel<64><<<dim3(M / 128, N / 64), 192, smem, st>>>(ma, mb, c, N, K);
+  }
+  RNNT_CUDA_RETURN_IF_ERROR();
+  return RNNT_B200_OK;
+}

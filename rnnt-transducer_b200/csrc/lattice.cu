@@ -1,0 +1,190 @@
+// alpha/beta anti-diagonal wavefront + occupation coefficients.
+//
+// Replaces the lattice stage of warprnnt_pytorch.RNNTLoss as called at
+// /root/reference rnnt/model.py:70. One CTA per
+// (utterance, direction): blockIdx.y = 0 runs alpha from (0,0), = 1 runs beta from
+// (T_b-1,U_b), concurrently on different SMs. Thread u owns lattice column u; a
+// wavefront step d handles the cells t+u = d. The planes are stored anti-diagonal
+// major (rnnt_b200.h), so each step reads one contiguous row of lp_blank/lp_label
+// (coalesced, prefetched PF steps ahead) and writes one contiguous row of alpha/beta.
+// Neighbour exchange goes through a double-buffered shared-memory diagonal.
+// Accumulators are float64: with V=4232 the per-utterance log-likelihood is ~1e3 nats
+// and fp32 alpha/beta miss the 1e-4 gradient tolerance.
+#include "common.cuh"
+
+namespace {
+
+constexpr int PF = 4;  // prefetch depth (wavefront steps)
+
+__global__ void __launch_bounds__(1024, 1)
+lattice_kernel(const float* __restrict__ lp_blank, const float* __restrict__ lp_label,
+               const int32_t* __restrict__ act_lens, const int32_t* __restrict__ label_lens,
+               int T, int U1, double* __restrict__ alpha, double* __restrict__ beta,
+               double* __restrict__ ll_alpha, double* __restrict__ ll_beta) {
+  __shared__ double xch[2][1024 + 2];
+  const int b = blockIdx.x;
+  const int u = threadIdx.x;
+  const int Tb = clamp_int(act_lens[b], 1, T);
+  const int Ub = clamp_int(label_lens[b], 0, U1 - 1);
+  const int nd = Tb + Ub;  // diagonals 0 .. nd-1
+  const size_t base = (size_t)b * (size_t)(T + U1 - 1) * (size_t)U1;
+  const float* pb = lp_blank + base;
+  const float* pl = lp_label + base;
+  const bool col_ok = (u <= Ub);
+  const double NEG = -INFINITY;
+  float rb[PF], rl[PF];
+
+  xch[0][u + 1] = NEG;
+  xch[1][u + 1] = NEG;
+  if (u == 0) { xch[0][0] = NEG; xch[1][0] = NEG; xch[0][blockDim.x + 1] = NEG; xch[1][blockDim.x + 1] = NEG; }
+  __syncthreads();
+
+  if (blockIdx.y == 0) {
+    // ---------------- alpha ----------------
+    double* out = alpha + base;
+#pragma unroll
+    for (int k = 0; k < PF; ++k) {
+      rb[k] = 0.f; rl[k] = 0.f;
+      if (k < nd && col_ok) { rb[k] = pb[(size_t)k * U1 + u]; rl[k] = pl[(size_t)k * U1 + u]; }
+    }
+    double up = NEG;  // alpha[t-1,u] + lp_blank[t-1,u]
+    for (int d0 = 0; d0 < nd; d0 += PF) {
+#pragma unroll
+      for (int k = 0; k < PF; ++k) {
+        const int d = d0 + k;
+        if (d < nd) {  // uniform across the block
+          const int t = d - u;
+          const bool valid = col_ok && t >= 0 && t < Tb;
+          const double left = xch[d & 1][u];  // slot u holds the message of thread u-1
+          double a = (d == 0 && u == 0) ? 0.0 : log_add_exp(up, left);
+          const float lpb = rb[k], lpl = rl[k];
+          if (d + PF < nd && col_ok) {
+            rb[k] = pb[(size_t)(d + PF) * U1 + u];
+            rl[k] = pl[(size_t)(d + PF) * U1 + u];
+          }
+          double right = NEG;
+          if (valid) {
+            out[(size_t)d * U1 + u] = a;
+            up = a + (double)lpb;
+            if (u < Ub) right = a + (double)lpl;
+          } else {
+            up = NEG;
+          }
+          xch[(d + 1) & 1][u + 1] = right;
+          __syncthreads();
+        }
+      }
+    }
+    if (u == Ub) ll_alpha[b] = up;  // alpha[Tb-1,Ub] + lp_blank[Tb-1,Ub]
+  } else {
+    // ---------------- beta ----------------
+    double* out = beta + base;
+#pragma unroll
+    for (int k = 0; k < PF; ++k) {
+      const int d = nd - 1 - k;
+      rb[k] = 0.f; rl[k] = 0.f;
+      if (d >= 0 && col_ok) { rb[k] = pb[(size_t)d * U1 + u]; rl[k] = pl[(size_t)d * U1 + u]; }
+    }
+    double own = NEG;  // beta[t+1,u]
+    for (int s0 = 0; s0 < nd; s0 += PF) {
+#pragma unroll
+      for (int k = 0; k < PF; ++k) {
+        const int s = s0 + k;  // step counter; diagonal d = nd-1-s
+        if (s < nd) {
+          const int d = nd - 1 - s;
+          const int t = d - u;
+          const bool valid = col_ok && t >= 0 && t < Tb;
+          const double right = xch[s & 1][u + 2];  // message of thread u+1 (beta[t,u+1])
+          const float lpb = rb[k], lpl = rl[k];
+          if (d - PF >= 0 && col_ok) {
+            rb[k] = pb[(size_t)(d - PF) * U1 + u];
+            rl[k] = pl[(size_t)(d - PF) * U1 + u];
+          }
+          double be = NEG;
+          if (valid) {
+            if (t == Tb - 1 && u == Ub) {
+              be = (double)lpb;
+            } else {
+              const double viab = own + (double)lpb;
+              const double vial = (u < Ub) ? right + (double)lpl : NEG;
+              be = log_add_exp(viab, vial);
+            }
+            out[(size_t)d * U1 + u] = be;
+          }
+          own = be;
+          xch[(s + 1) & 1][u + 1] = be;
+          __syncthreads();
+        }
+      }
+    }
+    if (u == 0) ll_beta[b] = own;  // beta[0,0]
+  }
+}
+
+// Elementwise over the valid cells of every utterance; one block row per (b, diagonal).
+__global__ void __launch_bounds__(256)
+coeff_kernel(const float* __restrict__ lp_blank, const float* __restrict__ lp_label,
+             const int32_t* __restrict__ act_lens, const int32_t* __restrict__ label_lens,
+             int T, int U1, const double* __restrict__ alpha, const double* __restrict__ beta,
+             const double* __restrict__ ll_beta,
+             float* __restrict__ c_blank, float* __restrict__ c_label,
+             float* __restrict__ loss, double* __restrict__ loss64) {
+  const int b = blockIdx.y;
+  const int Tb = clamp_int(act_lens[b], 1, T);
+  const int Ub = clamp_int(label_lens[b], 0, U1 - 1);
+  const int nd = Tb + Ub;
+  const double ll = ll_beta[b];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    loss[b] = (float)(-ll);
+    if (loss64) loss64[b] = -ll;
+  }
+  const size_t base = (size_t)b * (size_t)(T + U1 - 1) * (size_t)U1;
+  const long long n = (long long)nd * U1;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int d = (int)(i / U1);
+    const int u = (int)(i - (long long)d * U1);
+    const int t = d - u;
+    if (u > Ub || t < 0 || t >= Tb) continue;
+    const size_t idx = base + (size_t)i;
+    const double a = alpha[idx];
+    double cb = 0.0, cl = 0.0;
+    if (t + 1 < Tb) cb = exp(a + (double)lp_blank[idx] + beta[idx + U1] - ll);
+    else if (u == Ub) cb = exp(a + (double)lp_blank[idx] - ll);
+    if (u < Ub) cl = exp(a + (double)lp_label[idx] + beta[idx + U1 + 1] - ll);
+    c_blank[idx] = (float)cb;
+    c_label[idx] = (float)cl;
+  }
+}
+
+}  // namespace
+
+extern "C" int rnnt_b200_lattice(const float* lp_blank, const float* lp_label,
+                                 const int32_t* act_lens, const int32_t* label_lens,
+                                 int B, int T, int U1, double* alpha, double* beta,
+                                 float* c_blank, float* c_label, float* loss, double* loss64,
+                                 void* stream) {
+  if (!lp_blank || !lp_label || !act_lens || !label_lens || !alpha || !beta || !c_blank ||
+      !c_label || !loss)
+    return RNNT_B200_E_NULL;
+  if (B <= 0 || T <= 0 || U1 <= 0 || U1 > 1024) return RNNT_B200_E_SHAPE;
+  cudaStream_t st = (cudaStream_t)stream;
+  // ll scratch lives in the (never read) tail of the planes?  No: keep it explicit --
+  // the last diagonal row D-1 of utterance b is only used when T_b=T and U_b=U1-1, and
+  // then only its column U1-1; columns 0/1 of row 0 are taken. We instead reuse loss64
+  // when given, else the first two slots past the valid alpha/beta rows are not safe, so
+  // require a tiny scratch: alpha/beta planes are allocated with 2*B extra doubles.
+  double* ll_a = alpha + rnnt_b200_plane_elems(B, T, U1);
+  double* ll_b = beta + rnnt_b200_plane_elems(B, T, U1);
+  const int threads = ((U1 + 31) / 32) * 32;
+  lattice_kernel<<<dim3(B, 2), threads, 0, st>>>(lp_blank, lp_label, act_lens, label_lens, T, U1,
+                                                 alpha, beta, ll_a, ll_b);
+  RNNT_CUDA_RETURN_IF_ERROR();
+  const long long n = (long long)(T + U1 - 1) * U1;
+  int gx = (int)((n + 255) / 256);
+  if (gx > 592) gx = 592;
+  coeff_kernel<<<dim3(gx, B), 256, 0, st>>>(lp_blank, lp_label, act_lens, label_lens, T, U1, alpha,
+                                            beta, ll_b, c_blank, c_label, loss, loss64);
+  RNNT_CUDA_RETURN_IF_ERROR();
+  return RNNT_B200_OK;
+}

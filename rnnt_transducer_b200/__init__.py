@@ -1,0 +1,10 @@
+"""Importable alias of the package directory ``rnnt-transducer_b200/`` (a hyphen cannot
+appear in a Python module name). All code lives there; this file only extends the
+package search path and re-exports the public API."""
+import os as _os
+
+__path__.insert(0, _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))),
+                                 "rnnt-transducer_b200"))
+
+from ._api import *  # noqa: F401,F403,E402
+from ._api import __all__  # noqa: E402

@@ -1,0 +1,43 @@
+"""Shared test helpers: golden fixtures, synthetic inputs, error metrics."""
+import os
+
+import numpy as np
+import torch
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load_golden(name):
+    z = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    return {k: z[k] for k in z.files}
+
+
+def synth_lengths(B, T, U, mode, gen):
+    """mode: 'full' | 'ragged' (T_b ~ U{ceil(T/2)..T}, U_b ~ U{ceil(U/2)..U}, utterance 0 full)
+    | 'edge' (adds U_b=0 and T_b=1 utterances)."""
+    if mode == "full":
+        return torch.full((B,), T, dtype=torch.int32), torch.full((B,), U, dtype=torch.int32)
+    tl = torch.randint((T + 1) // 2, T + 1, (B,), generator=gen, dtype=torch.int32)
+    ul = torch.randint((U + 1) // 2, U + 1, (B,), generator=gen, dtype=torch.int32)
+    tl[0], ul[0] = T, U
+    if mode == "edge" and B >= 3:
+        ul[1] = 0
+        tl[2] = 1
+    return tl, ul
+
+
+def synth_labels(B, U, V, label_lens, gen):
+    y = torch.randint(1, V, (B, max(U, 0)), generator=gen, dtype=torch.int32)
+    for b in range(B):
+        y[b, int(label_lens[b]):] = 0
+    return y
+
+
+def rel_l2(a, b):
+    a, b = torch.as_tensor(a).detach().double().cpu(), torch.as_tensor(b).detach().double().cpu()
+    return float((a - b).norm() / b.norm().clamp_min(1e-300))
+
+
+def max_abs(a, b):
+    a, b = torch.as_tensor(a).detach().double().cpu(), torch.as_tensor(b).detach().double().cpu()
+    return float((a - b).abs().max())

@@ -1,0 +1,76 @@
+"""Boundary 1 (drop-in RNNTLoss on materialised fp32 logits) vs the float64 oracle.
+Tolerances are BASELINE.json's fp32-path figures: 1e-5 relative on per-utterance loss,
+1e-4 on gradients (max-abs over all logits)."""
+import pytest
+import torch
+
+from tests import gpu_checks as G
+
+pytestmark = pytest.mark.gpu
+
+LOSS_RTOL = 1e-5
+GRAD_ATOL = 1e-4
+
+
+@pytest.mark.parametrize("name", ["tiny", "timit_like", "aishell_like", "edge_u0_t1"])
+def test_golden(name):
+    m = G.dropin_golden(name)
+    assert m["loss_rel"] < LOSS_RTOL, m
+    assert m["grad_max_abs"] < GRAD_ATOL, m
+    assert m["grad_outside_window_max"] == 0.0, m
+    assert m["loss_rel_vs_torchaudio"] < 1e-5 and m["grad_max_abs_vs_torchaudio"] < 1e-4, m
+
+
+@pytest.mark.parametrize("shape,mode", [
+    ((2, 40, 10, 4232), "ragged"),     # AISHELL vocabulary, init-like logits (loss ~ 400 nats)
+    ((3, 30, 12, 49), "edge"),         # TIMIT vocabulary (V % 4 != 0 -> scalar path), U_b=0, T_b=1
+    ((1, 1, 0, 4232), "full"),         # T=1, U=0
+    ((2, 3, 40, 64), "full"),          # U+1 > 32: several warps per lattice CTA
+    ((1, 300, 200, 8), "ragged"),      # long lattice, tiny vocabulary
+])
+def test_synthetic(shape, mode):
+    m = G.dropin_synth(*shape, mode=mode)
+    assert m["loss_rel"] < LOSS_RTOL, m
+    assert m["grad_max_abs"] < GRAD_ATOL, m
+    assert m["grad_outside_window_max"] == 0.0, m
+
+
+def test_config1_shape_init_like_and_trained_like():
+    # BASELINE.json configs[0] lattice shape (B=8,T=200,U=30) at AISHELL V: the regime where an
+    # fp32 lattice misses 1e-4; float64 accumulators must pass it.
+    m = G.dropin_synth(2, 200, 30, 4232, mode="ragged")
+    assert m["loss_rel"] < LOSS_RTOL and m["grad_max_abs"] < GRAD_ATOL, m
+    m = G.dropin_synth(2, 200, 30, 4232, mode="ragged", trained_like=True)
+    assert m["loss_rel"] < LOSS_RTOL and m["grad_max_abs"] < GRAD_ATOL, m
+
+
+def test_reductions_and_grad_scaling():
+    import rnnt_transducer_b200 as R
+    gen = torch.Generator().manual_seed(5)
+    x = torch.randn(3, 6, 4, 10, generator=gen).cuda()
+    y = torch.randint(1, 10, (3, 3), generator=gen, dtype=torch.int32).cuda()
+    tl = torch.tensor([6, 5, 4], dtype=torch.int32).cuda()
+    ul = torch.tensor([3, 2, 3], dtype=torch.int32).cuda()
+    none = R.RNNTLoss(reduction="none")(x, y, tl, ul)
+    mean = R.RNNTLoss()(x, y, tl, ul)
+    assert mean.shape == (1,) and mean.dtype == torch.float32 and mean.device == x.device
+    assert abs(float(mean) - float(none.sum() / 3)) < 1e-5
+    xa = x.clone().requires_grad_(True)
+    R.RNNTLoss()(xa, y, tl, ul).backward()
+    xb = x.clone().requires_grad_(True)
+    R.RNNTLoss(reduction="sum")(xb, y, tl, ul).backward()
+    assert torch.allclose(xa.grad * 3, xb.grad, atol=1e-6)
+    # softmax-Jacobian property: every valid row of the gradient sums to zero
+    assert float(xb.grad.sum(-1).abs().max()) < 1e-5
+
+
+def test_uniform_logits_closed_form():
+    import rnnt_transducer_b200 as R
+    from oracle.rnnt_oracle import uniform_closed_form
+    for (T, U, V) in [(5, 3, 9), (50, 20, 4232), (7, 0, 4)]:
+        x = torch.zeros(1, T, U + 1, V, device="cuda")
+        y = torch.randint(1, V, (1, U), dtype=torch.int32, device="cuda")
+        l = R.RNNTLoss(reduction="none")(x, y, torch.tensor([T], dtype=torch.int32, device="cuda"),
+                                         torch.tensor([U], dtype=torch.int32, device="cuda"))
+        ref = uniform_closed_form(T, U, V)
+        assert abs(float(l) - ref) / ref < 1e-6

@@ -1,0 +1,100 @@
+"""CPU-side checks of the boundary: the C-ABI library loads and exports every symbol the
+header declares, pure shape helpers agree with their definition, and the Python mirror of
+the reference interface validates arguments and refuses to run without CUDA (no fallback)."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+import rnnt_transducer_b200 as R
+from rnnt_transducer_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _header_symbols():
+    src = open(os.path.join(ROOT, "include", "rnnt_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(rnnt_b200_\w+)\s*\(", src)))
+
+
+def test_library_exports_every_header_symbol():
+    assert os.path.exists(_lib.SO_PATH), "run __graft_entry__.build() first"
+    handle = ctypes.CDLL(_lib.SO_PATH)
+    syms = _header_symbols()
+    assert len(syms) >= 16
+    for s in syms:
+        assert hasattr(handle, s), f"{s} declared in include/rnnt_b200.h but not exported"
+    assert set(syms) == set(_lib.SIGNATURES), "ctypes signature table out of sync with the header"
+
+
+def test_shape_helpers_without_gpu():
+    L = _lib.lib()
+    assert L.rnnt_b200_version() == 100
+    assert L.rnnt_b200_plane_elems(2, 5, 4) == 2 * (5 + 4 - 1) * 4
+    assert L.rnnt_b200_max_tiles(32, 500, 101) == 32 * ((500 * 101 + 127) // 128)
+    assert L.rnnt_b200_vocab_tile(4232) == 256 and L.rnnt_b200_vocab_pad(4232) == 4352
+    assert L.rnnt_b200_vocab_tile(49) == 64 and L.rnnt_b200_vocab_pad(49) == 64
+    assert L.rnnt_b200_h_pitch(512) == 520
+    assert L.rnnt_b200_status_string(-3) == b"blank index not in [0,V)"
+
+
+def test_c_abi_rejects_bad_arguments_without_launching():
+    L = _lib.lib()
+    assert L.rnnt_b200_logits_to_planes(None, None, None, None, 1, 1, 1, 4, 0, None, None, None, None) == -1
+    one = ctypes.c_void_p(16)
+    assert L.rnnt_b200_logits_to_planes(one, one, one, one, 1, 1, 1, 4, 7, one, one, one, None) == -3
+    assert L.rnnt_b200_lattice(one, one, one, one, 1, 4, 2000, one, one, one, one, one, None, None) == -2
+    assert L.rnnt_b200_joint_fwd(one, one, one, one, one, one, one, one, one, one,
+                                 1, 4, 2, 10, 100, 0, one, one, one, None, None) == -2   # H % 64
+
+
+def test_rnntloss_is_dropin_constructible_and_validates():
+    crit = R.RNNTLoss()  # no-arg, like rnnt/model.py:59
+    assert crit.blank == 0 and crit.reduction == "mean"
+    acts = torch.zeros(1, 2, 2, 4)
+    y = torch.zeros(1, 1, dtype=torch.int32)
+    tl = torch.tensor([2], dtype=torch.int32)
+    ul = torch.tensor([1], dtype=torch.int32)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        crit(acts, y, tl, ul)
+    with pytest.raises(ValueError, match="int32"):
+        crit(acts, y.long(), tl, ul)
+    with pytest.raises(ValueError, match="float32"):
+        crit(acts.double(), y, tl, ul)
+    with pytest.raises(ValueError):
+        R.RNNTLoss(reduction="bogus")
+
+
+def test_warprnnt_pytorch_alias_resolves_to_this_package():
+    import warprnnt_pytorch
+    assert warprnnt_pytorch.RNNTLoss is R.RNNTLoss
+
+
+def test_jointnet_matches_reference_state_dict_layout_and_math():
+    from tests.helpers import load_golden, max_abs
+    g = load_golden("timit_like")
+    E, D = g["enc"].shape[-1], g["dec"].shape[-1]
+    H, V = g["w1"].shape[0], g["w2"].shape[0]
+    j = R.JointNet(E + D, H, V)
+    assert sorted(j.state_dict()) == ["forward_layer.bias", "forward_layer.weight",
+                                      "project_layer.bias", "project_layer.weight"]
+    j.load_state_dict({"forward_layer.weight": torch.from_numpy(g["w1"]), "forward_layer.bias": torch.from_numpy(g["b1"]),
+                       "project_layer.weight": torch.from_numpy(g["w2"]), "project_layer.bias": torch.from_numpy(g["b2"])})
+    out = j(torch.from_numpy(g["enc"]), torch.from_numpy(g["dec"]))
+    assert max_abs(out, g["ref_joint_logits"]) < 5e-6
+    # equal-rank branch used by greedy decoding (rnnt/model.py:28-29,90)
+    e1, d1 = torch.from_numpy(g["enc"])[0, 0], torch.from_numpy(g["dec"])[0, 0]
+    assert max_abs(j(e1, d1), g["ref_joint_logits"][0, 0, 0]) < 5e-6
+
+
+def test_fused_entry_validates_shapes_on_cpu():
+    j = R.JointNet(16, 100, 9)   # H = 100 is not a multiple of 64
+    f = R.JointRNNTLoss(j)
+    y = torch.zeros(1, 1, dtype=torch.int32)
+    tl = torch.tensor([2], dtype=torch.int32)
+    ul = torch.tensor([1], dtype=torch.int32)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        f(torch.zeros(1, 2, 8), torch.zeros(1, 2, 8), y, tl, ul)
