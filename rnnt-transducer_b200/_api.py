@@ -22,7 +22,7 @@ import torch.nn.functional as F
 from . import _lib
 
 __all__ = ["RNNTLoss", "rnnt_loss", "JointNet", "JointRNNTLoss", "joint_rnnt_loss",
-           "build_extension", "extension_path", "selftest_gemm"]
+           "build_extension", "extension_path", "selftest_gemm", "KernelTimer"]
 
 
 def build_extension(verbose: bool = False) -> str:
@@ -35,6 +35,73 @@ def extension_path() -> str:
 
 def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
+
+
+class KernelTimer:
+    """Optional per-launch CUDA-event timing of this package's own kernels (bench.py's
+    roofline numbers). ``with KernelTimer() as kt: ...; kt.summary()`` -> {name: [ms,...]}.
+    Events are recorded on the launching (current) stream; nothing synchronises until
+    ``summary()``."""
+    active = None
+    # kernels launched per C-ABI call
+    KERNELS = {"logits_to_planes": 1, "lattice": 2, "planes_to_dlogits": 1, "build_tiles": 1,
+               "pack_vocab": 1, "joint_fwd": 1, "joint_bwd_ds": 1, "dh_reduce": 1}
+
+    def __init__(self, events: bool = True):
+        self.events = events
+        self.records = []
+        self.launches = 0
+
+    def __enter__(self):
+        KernelTimer.active = self
+        return self
+
+    def __exit__(self, *exc):
+        KernelTimer.active = None
+
+    def summary(self):
+        torch.cuda.synchronize()
+        out = {}
+        for name, e0, e1 in self.records:
+            out.setdefault(name, []).append(e0.elapsed_time(e1))
+        return out
+
+
+def _call(name, fn, *args):
+    kt = KernelTimer.active
+    if kt is None:
+        _lib.check(fn(*args), "rnnt_b200_" + name)
+        return
+    kt.launches += KernelTimer.KERNELS[name]
+    if kt.events:
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _lib.check(fn(*args), "rnnt_b200_" + name)
+        e1.record()
+        kt.records.append((name, e0, e1))
+    else:
+        _lib.check(fn(*args), "rnnt_b200_" + name)
+
+
+class _region:
+    """Times a non-kernel region (library GEMMs) under an active KernelTimer; not a launch of ours."""
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        kt = KernelTimer.active
+        self.e0 = None
+        if kt is not None and kt.events:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+
+    def __exit__(self, *exc):
+        if self.e0 is not None and KernelTimer.active is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            KernelTimer.active.records.append((self.name, self.e0, e1))
 
 
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
@@ -92,9 +159,9 @@ def _lattice(lpb, lpl, act_lens, label_lens, B, T, U1):
     cb = torch.empty(n, dtype=torch.float32, device=dev)
     cl = torch.empty(n, dtype=torch.float32, device=dev)
     loss = torch.empty(B, dtype=torch.float32, device=dev)
-    _lib.check(L.rnnt_b200_lattice(_ptr(lpb), _ptr(lpl), _ptr(act_lens), _ptr(label_lens), B, T, U1,
+    _call("lattice", L.rnnt_b200_lattice, _ptr(lpb), _ptr(lpl), _ptr(act_lens), _ptr(label_lens), B, T, U1,
                                    _ptr(alpha), _ptr(beta), _ptr(cb), _ptr(cl), _ptr(loss), None,
-                                   _stream()), "rnnt_b200_lattice")
+                                   _stream())
     return loss, cb, cl
 
 
@@ -110,10 +177,9 @@ class _RNNTLossFn(torch.autograd.Function):
             lse = torch.empty(n, dtype=torch.float32, device=dev)
             lpb = torch.empty(n, dtype=torch.float32, device=dev)
             lpl = torch.empty(n, dtype=torch.float32, device=dev)
-            _lib.check(L.rnnt_b200_logits_to_planes(_ptr(acts), _ptr(labels), _ptr(act_lens),
+            _call("logits_to_planes", L.rnnt_b200_logits_to_planes, _ptr(acts), _ptr(labels), _ptr(act_lens),
                                                     _ptr(label_lens), B, T, U1, V, blank, _ptr(lse),
-                                                    _ptr(lpb), _ptr(lpl), _stream()),
-                       "rnnt_b200_logits_to_planes")
+                                                    _ptr(lpb), _ptr(lpl), _stream())
             loss, cb, cl = _lattice(lpb, lpl, act_lens, label_lens, B, T, U1)
         ctx.save_for_backward(acts, labels, act_lens, label_lens, lse, cb, cl)
         ctx.blank = blank
@@ -127,11 +193,10 @@ class _RNNTLossFn(torch.autograd.Function):
         with torch.cuda.device(acts.device):
             scale = grad_out.to(torch.float32).contiguous()
             dlogits = torch.empty_like(acts)
-            _lib.check(L.rnnt_b200_planes_to_dlogits(_ptr(acts), _ptr(labels), _ptr(act_lens),
+            _call("planes_to_dlogits", L.rnnt_b200_planes_to_dlogits, _ptr(acts), _ptr(labels), _ptr(act_lens),
                                                      _ptr(label_lens), B, T, U1, V, ctx.blank,
                                                      _ptr(lse), _ptr(cb), _ptr(cl), _ptr(scale),
-                                                     _ptr(dlogits), _stream()),
-                       "rnnt_b200_planes_to_dlogits")
+                                                     _ptr(dlogits), _stream())
         return dlogits, None, None, None, None
 
 
@@ -191,12 +256,11 @@ class _JointLossFn(torch.autograd.Function):
             tile_utt = torch.empty(max_tiles, dtype=torch.int32, device=dev)
             tile_cell0 = torch.empty(max_tiles, dtype=torch.int32, device=dev)
             n_tiles = torch.empty(1, dtype=torch.int32, device=dev)
-            _lib.check(L.rnnt_b200_build_tiles(_ptr(act_lens), _ptr(label_lens), B, T, U1, _ptr(tile_utt),
-                                               _ptr(tile_cell0), _ptr(n_tiles), st), "rnnt_b200_build_tiles")
+            _call("build_tiles", L.rnnt_b200_build_tiles, _ptr(act_lens), _ptr(label_lens), B, T, U1, _ptr(tile_utt),
+                                               _ptr(tile_cell0), _ptr(n_tiles), st)
             w2q = torch.empty(Vpad, H, dtype=torch.bfloat16, device=dev)
             b2l = torch.empty(Vpad, dtype=torch.float32, device=dev)
-            _lib.check(L.rnnt_b200_pack_vocab(_ptr(w2), _ptr(b2), V, H, _ptr(w2q), _ptr(b2l), st),
-                       "rnnt_b200_pack_vocab")
+            _call("pack_vocab", L.rnnt_b200_pack_vocab, _ptr(w2), _ptr(b2), V, H, _ptr(w2q), _ptr(b2l), st)
             n = L.rnnt_b200_plane_elems(B, T, U1)
             lse = torch.empty(n, dtype=torch.float32, device=dev)
             lpb = torch.empty(n, dtype=torch.float32, device=dev)
@@ -204,11 +268,10 @@ class _JointLossFn(torch.autograd.Function):
             h_stash = None
             if need_grad:
                 h_stash = torch.empty(max_tiles * 128, L.rnnt_b200_h_pitch(H), dtype=torch.bfloat16, device=dev)
-            _lib.check(L.rnnt_b200_joint_fwd(_ptr(pe), _ptr(pd), _ptr(w2q), _ptr(b2l), _ptr(labels),
+            _call("joint_fwd", L.rnnt_b200_joint_fwd, _ptr(pe), _ptr(pd), _ptr(w2q), _ptr(b2l), _ptr(labels),
                                              _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt),
                                              _ptr(tile_cell0), _ptr(n_tiles), B, T, U1, V, H, blank,
-                                             _ptr(lse), _ptr(lpb), _ptr(lpl), _ptr(h_stash), st),
-                       "rnnt_b200_joint_fwd")
+                                             _ptr(lse), _ptr(lpb), _ptr(lpl), _ptr(h_stash), st)
             loss, cb, cl = _lattice(lpb, lpl, act_lens, label_lens, B, T, U1)
         if need_grad:
             ctx.save_for_backward(labels, act_lens, label_lens, tile_utt, tile_cell0, n_tiles, w2q, b2l,
@@ -235,17 +298,19 @@ class _JointLossFn(torch.autograd.Function):
                 hi = min(max_tiles, lo + chunk)
                 rows = (hi - lo) * 128
                 dsc = ds[:rows]
-                _lib.check(L.rnnt_b200_joint_bwd_ds(_ptr(h_stash), _ptr(w2q), _ptr(b2l), _ptr(labels),
+                _call("joint_bwd_ds", L.rnnt_b200_joint_bwd_ds, _ptr(h_stash), _ptr(w2q), _ptr(b2l), _ptr(labels),
                                                     _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt),
                                                     _ptr(tile_cell0), _ptr(n_tiles), _ptr(lse), _ptr(cb),
                                                     _ptr(cl), _ptr(scale), B, T, U1, V, H, blank, lo, hi,
-                                                    _ptr(dsc), st), "rnnt_b200_joint_bwd_ds")
+                                                    _ptr(dsc), st)
                 # two plain library GEMMs on the staged bf16 gradient tile (fp32 accumulate/out)
-                dh = torch.mm(dsc, w2q, out_dtype=torch.float32)                       # (rows, H)
-                dw2x += torch.mm(dsc.t(), h_stash[lo * 128: hi * 128], out_dtype=torch.float32)
-                _lib.check(L.rnnt_b200_dh_reduce(_ptr(dh), _ptr(h_stash), _ptr(act_lens), _ptr(label_lens),
+                with _region("lib_gemm_dh"):
+                    dh = torch.mm(dsc, w2q, out_dtype=torch.float32)                   # (rows, H)
+                with _region("lib_gemm_dw2"):
+                    dw2x += torch.mm(dsc.t(), h_stash[lo * 128: hi * 128], out_dtype=torch.float32)
+                _call("dh_reduce", L.rnnt_b200_dh_reduce, _ptr(dh), _ptr(h_stash), _ptr(act_lens), _ptr(label_lens),
                                                  _ptr(tile_utt), _ptr(tile_cell0), _ptr(n_tiles), B, T, U1,
-                                                 H, lo, hi, _ptr(dpe), _ptr(dpd), st), "rnnt_b200_dh_reduce")
+                                                 H, lo, hi, _ptr(dpe), _ptr(dpd), st)
             dw2 = dw2x[:V, :H].contiguous()
             db2 = dw2x[:V, H].contiguous()
         return dpe, dpd, dw2, db2, None, None, None, None
