@@ -26,6 +26,7 @@
 // tile j overlaps the MMAs of tile j+1.
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <stdlib.h>
 #include "common.cuh"
 #include "sm100_ptx.cuh"
 
@@ -37,7 +38,7 @@ constexpr int kThreads = 512;
 constexpr int kEpiWarps = 8;
 constexpr int kProdThreads = 128;
 constexpr int kKBlock = 64;              // A tile K block (128-byte swizzle span of bf16)
-constexpr int kBK = 32;                  // W2 stage K extent (64-byte swizzle span of bf16)
+constexpr int kBK = 64;                  // W2 stage K extent (128-byte swizzle span of bf16)
 constexpr int kABlockBytes = RNNT_TILE_M * 128;
 constexpr int kMaxStages = 8;
 constexpr int kSmemLimit = 232448;       // 227 KB opt-in maximum per CTA
@@ -80,10 +81,11 @@ struct JointParams {
   int B, T, U1, V, Vpad, H, blank;
   int tile_lo, tile_hi;  // tile range of this launch
   int stages;
+  int debug;  // RNNT_B200_DEBUG bitmask (timing experiments only): 1 skip epilogue math, 2 skip producer math, 4 skip MMA issue
 };
 
 __host__ __device__ inline int smem_bytes_for(int H, int BN, int stages) {
-  return 1024 /*align slack*/ + (H / kKBlock) * kABlockBytes + stages * BN * 64 + (int)sizeof(SharedCtl);
+  return 1024 /*align slack*/ + (H / kKBlock) * kABlockBytes + stages * (BN / 2) * 128 + (int)sizeof(SharedCtl);
 }
 
 __device__ __forceinline__ float tanh_accurate(float x) {
@@ -102,8 +104,9 @@ struct RowCoord {
   int b, t, u, Ub;
   bool valid;
 };
-__device__ __forceinline__ RowCoord locate_row(const JointParams& p, int tile, int r) {
+__device__ __forceinline__ RowCoord locate_row(const JointParams& p, int tile, int r, bool dead) {
   RowCoord c;
+  if (dead) { c.b = 0; c.t = 0; c.u = 0; c.Ub = 0; c.valid = false; return c; }
   c.b = p.tile_utt[tile];
   const int cell = p.tile_cell0[tile] + r;
   const int Tb = clamp_int(p.act_lens[c.b], 1, p.T);
@@ -125,16 +128,21 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int KB = p.H / kKBlock;      // A K-blocks of 64
-  const int KS = p.H / kBK;          // W2 stages per vocabulary tile (K steps of 32)
+  const int KS = p.H / kBK;          // W2 stages per vocabulary tile (K steps of 64)
   const int NV = p.Vpad / BN;        // vocabulary tiles
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + KB * kABlockBytes;
-  constexpr int kStageBytes = BN * 64;
+  constexpr int kStageBytes = (BN / 2) * 128;  // this CTA's half of a W2 stage: BN/2 rows x 64 k
   SharedCtl* ctl = reinterpret_cast<SharedCtl*>(smem_b + p.stages * kStageBytes);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int n_tiles = min(p.n_tiles[0], p.tile_hi);
+  // CTA pair: the two CTAs of a cluster own tiles 2*pt and 2*pt+1 and sweep the vocabulary in
+  // lockstep; rank 0 (leader) issues the cta_group::2 MMAs for both.
+  const uint32_t rank = cluster_ctarank();
+  const int cid = blockIdx.x >> 1, ncl = gridDim.x >> 1;
+  const int n_pairs = (max(n_tiles - p.tile_lo, 0) + 1) >> 1;
 
   if (warp == 12 && lane == 0) {
     tma_prefetch_desc(&map_w2);
@@ -142,25 +150,27 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
   }
   if (warp == 13 && lane == 0) {
     for (int i = 0; i < 8; ++i) {
-      mbar_init(&ctl->a_full[i], MODE == 0 ? kProdThreads : 1);
+      mbar_init(&ctl->a_full[i], MODE == 0 ? 2 * (kProdThreads / 32) : 2);
       mbar_init(&ctl->a_empty[i], 1);
     }
     for (int i = 0; i < kMaxStages; ++i) {
-      mbar_init(&ctl->b_full[i], 1);
+      mbar_init(&ctl->b_full[i], 2);
       mbar_init(&ctl->b_empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&ctl->acc_full[i], 1);
-      mbar_init(&ctl->acc_empty[i], kEpiWarps);
+      mbar_init(&ctl->acc_empty[i], 2 * kEpiWarps);
     }
     fence_barrier_init();
   }
-  if (warp == 14) {
-    tmem_alloc(&ctl->tmem_base, 512);
-    tmem_relinquish();
+  __syncwarp();
+  cluster_sync_all();  // barrier inits visible to the peer before any remote arrive / multicast commit
+  if (warp == 13) {
+    tmem_alloc_pair(&ctl->tmem_base, 512);
+    tmem_relinquish_pair();
   }
   tc_fence_before();
-  __syncthreads();
+  cluster_sync_all();  // both CTAs' TMEM allocations exist before the leader's MMAs write them
   tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
 
@@ -172,8 +182,11 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
     constexpr int NCH = HALF / 32;
     uint32_t acc_it = 0;
     int it = 0;
-    for (int tile = p.tile_lo + blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-      const RowCoord rc = locate_row(p, tile, row);
+    for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
+      const int tile = p.tile_lo + 2 * pt + (int)rank;
+      const bool dead = tile >= n_tiles;  // odd tail: this CTA only keeps the pair's protocol going
+      (void)dead;
+      const RowCoord rc = locate_row(p, tile, row, dead);
       int label = -1;
       size_t pidx = 0;
       if (rc.valid) {
@@ -200,6 +213,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         tc_fence_after();
 #pragma unroll
         for (int c = 0; c < NCH; ++c) {
+          if (p.debug & 1) break;
           const int col0 = vt * BN + half * HALF + c * 32;
           const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN + half * HALF + c * 32;
           float z[32];
@@ -251,6 +265,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
             uint4* dst = reinterpret_cast<uint4*>(p.ds + ((size_t)(tile - p.tile_lo) * RNNT_TILE_M + row) * p.Vpad + col0);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
+              if (dead) break;
               uint4 o;
               o.x = pack_bf16x2(g[8 * j + 0], g[8 * j + 1]);
               o.y = pack_bf16x2(g[8 * j + 2], g[8 * j + 3]);
@@ -262,7 +277,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&ctl->acc_empty[buf]);
+        if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&ctl->acc_empty[buf]), 0));
       }
       if (MODE == 0) {
         const int slot = it & 1;
@@ -297,16 +312,19 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       const int row0 = ptid >> 3;
       const int hp = p.H + 8;
       int it = 0;
-      for (int tile = p.tile_lo + blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
+      const int tile = p.tile_lo + 2 * pt + (int)rank;
+      const bool dead = tile >= n_tiles;  // odd tail: this CTA only keeps the pair's protocol going
+      (void)dead;
         {
-          const RowCoord rc = locate_row(p, tile, ptid);
+          const RowCoord rc = locate_row(p, tile, ptid, dead);
           TileInfo ti;
           ti.pe_off = rc.valid ? (rc.b * p.T + rc.t) * p.H : -1;
           ti.pd_off = rc.valid ? (rc.b * p.U1 + rc.u) * p.H : -1;
           named_bar_sync(2, kProdThreads);  // previous tile's readers are done with info[]
           ctl->info[ptid] = ti;
           named_bar_sync(2, kProdThreads);
-          if (p.h_stash) {  // "ones" column block H..H+7 (column H = 1 for valid cells)
+          if (p.h_stash && !dead) {  // "ones" column block H..H+7 (column H = 1 for valid cells)
             uint4 o = make_uint4(rc.valid ? 0x00003F80u : 0u, 0u, 0u, 0u);
             *reinterpret_cast<uint4*>(p.h_stash + ((size_t)tile * RNNT_TILE_M + ptid) * hp + p.H) = o;
           }
@@ -320,7 +338,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
             const int row = row0 + 16 * i;
             const TileInfo ti = ctl->info[row];
             uint4 o = make_uint4(0u, 0u, 0u, 0u);
-            if (ti.pe_off >= 0) {
+            if (ti.pe_off >= 0 && !(p.debug & 2)) {
               const float4* e4 = reinterpret_cast<const float4*>(p.pe + ti.pe_off + k0);
               const float4* d4 = reinterpret_cast<const float4*>(p.pd + ti.pd_off + k0);
               const float4 e0 = __ldg(e4), e1 = __ldg(e4 + 1), d0 = __ldg(d4), d1 = __ldg(d4 + 1);
@@ -330,11 +348,12 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
               o.w = pack_bf16x2(tanh_accurate(e1.z + d1.z), tanh_accurate(e1.w + d1.w));
             }
             *reinterpret_cast<uint4*>(ablk + row * 128 + ((chunk ^ (row & 7)) << 4)) = o;
-            if (p.h_stash)
+            if (p.h_stash && !dead)
               *reinterpret_cast<uint4*>(p.h_stash + ((size_t)tile * RNNT_TILE_M + row) * hp + k0) = o;
           }
           fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the MMA (async proxy)
-          mbar_arrive(&ctl->a_full[kb]);
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&ctl->a_full[kb]), 0));
         }
       }
       if (p.h_stash) {
@@ -352,12 +371,18 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
       int it = 0;
-      for (int tile = p.tile_lo + blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
+      const int tile = p.tile_lo + 2 * pt + (int)rank;
+      const bool dead = tile >= n_tiles;  // odd tail: this CTA only keeps the pair's protocol going
+      (void)dead;
         for (int vt = 0; vt < NV; ++vt) {
           for (int ks = 0; ks < KS; ++ks) {
             mbar_wait(&ctl->b_empty[stage], phase ^ 1);
-            mbar_arrive_expect_tx(&ctl->b_full[stage], kStageBytes);
-            tma_load_2d(smem_b + stage * kStageBytes, &map_w2, &ctl->b_full[stage], ks * kBK, vt * BN);
+            const uint32_t full = mapa_u32(smem_u32(&ctl->b_full[stage]), 0);
+            if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[stage], 2 * kStageBytes);
+            else mbar_arrive_cluster(full);
+            tma_load_2d_pair(smem_b + stage * kStageBytes, &map_w2, full, ks * kBK,
+                             vt * BN + (int)rank * (BN / 2));
             if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
           }
         }
@@ -367,51 +392,58 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
     // =========================== A TILE TMA (backward only) ===========================
     if (MODE == 1 && lane == 0) {
       int it = 0;
-      for (int tile = p.tile_lo + blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
+      const int tile = p.tile_lo + 2 * pt + (int)rank;
+      const bool dead = tile >= n_tiles;  // odd tail: this CTA only keeps the pair's protocol going
+      (void)dead;
         for (int kb = 0; kb < KB; ++kb) {
           mbar_wait(&ctl->a_empty[kb], (it & 1) ^ 1);
-          mbar_arrive_expect_tx(&ctl->a_full[kb], kABlockBytes);
-          tma_load_2d(smem_a + kb * kABlockBytes, &map_h, &ctl->a_full[kb], kb * kKBlock,
-                      tile * RNNT_TILE_M);
+          const uint32_t full = mapa_u32(smem_u32(&ctl->a_full[kb]), 0);
+          if (rank == 0) mbar_arrive_expect_tx(&ctl->a_full[kb], 2 * kABlockBytes);
+          else mbar_arrive_cluster(full);
+          tma_load_2d_pair(smem_a + kb * kABlockBytes, &map_h, full, kb * kKBlock, tile * RNNT_TILE_M);
         }
       }
     }
   } else if (warp == 13) {
     // =========================== MMA ISSUER ===========================
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(RNNT_TILE_M, BN);
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(2 * RNNT_TILE_M, BN);
       uint32_t stage = 0, phase = 0, acc_it = 0;
       int it = 0;
-      for (int tile = p.tile_lo + blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
+      const int tile = p.tile_lo + 2 * pt + (int)rank;
+      const bool dead = tile >= n_tiles;  // odd tail: this CTA only keeps the pair's protocol going
+      (void)dead;
         for (int vt = 0; vt < NV; ++vt, ++acc_it) {
           const uint32_t buf = acc_it & 1;
           mbar_wait(&ctl->acc_empty[buf], ((acc_it >> 1) & 1) ^ 1);
           tc_fence_after();
           const uint32_t tmem_d = tmem_base + buf * BN;
           for (int ks = 0; ks < KS; ++ks) {
-            const int kb = ks >> 1;
-            if (vt == 0 && (ks & 1) == 0) mbar_wait(&ctl->a_full[kb], it & 1);
+            const int kb = ks;
+            if (vt == 0) mbar_wait(&ctl->a_full[kb], it & 1);
             mbar_wait(&ctl->b_full[stage], phase);
             tc_fence_after();
-            const uint64_t adesc =
-                umma_desc_kmajor<128>(smem_u32(smem_a + kb * kABlockBytes) + (ks & 1) * 64);
-            const uint64_t bdesc = umma_desc_kmajor<64>(smem_u32(smem_b + stage * kStageBytes));
+            const uint64_t adesc = umma_desc_kmajor<128>(smem_u32(smem_a + kb * kABlockBytes));
+            const uint64_t bdesc = umma_desc_kmajor<128>(smem_u32(smem_b + stage * kStageBytes));
 #pragma unroll
             for (int k = 0; k < kBK / 16; ++k)
-              umma_bf16_ss(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | k) != 0);
-            umma_commit(&ctl->b_empty[stage]);
-            if (vt == NV - 1 && (ks & 1) == 1) umma_commit(&ctl->a_empty[kb]);
+              if (!(p.debug & 4)) umma_bf16_ss_pair(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | k) != 0);
+            umma_commit_pair_mc(&ctl->b_empty[stage], 3);
+            if (vt == NV - 1) umma_commit_pair_mc(&ctl->a_empty[kb], 3);
             if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
           }
-          umma_commit(&ctl->acc_full[buf]);
+          umma_commit_pair_mc(&ctl->acc_full[buf], 3);
         }
       }
     }
   }
 
+  __syncwarp();  // single-lane roles: reconverge before the aligned cluster barrier
   tc_fence_before();
-  __syncthreads();
-  if (warp == 14) tmem_dealloc(tmem_base, 512);
+  cluster_sync_all();  // peer may still target this CTA's barriers / TMEM until here
+  if (warp == 13) tmem_dealloc_pair(tmem_base, 512);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -543,15 +575,34 @@ int pick_stages(int H, int BN) {
 template <int BN, int MODE>
 int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, JointParams& p, cudaStream_t st) {
   p.stages = pick_stages(p.H, BN);
+  {
+    const char* dbg = getenv("RNNT_B200_DEBUG");
+    p.debug = dbg ? atoi(dbg) : 0;
+    const char* stg = getenv("RNNT_B200_STAGES");
+    if (stg && atoi(stg) >= 2 && atoi(stg) < p.stages) p.stages = atoi(stg);
+  }
   const int smem = smem_bytes_for(p.H, BN, p.stages);
   if (smem > kSmemLimit) return RNNT_B200_E_SHAPE;
   cudaError_t e = cudaFuncSetAttribute(joint_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return (int)e;
-  int grid = sm_count();
+  int grid = sm_count() & ~1;
   const int ntile = p.tile_hi - p.tile_lo;
-  if (grid > ntile) grid = ntile;
-  if (grid < 1) return RNNT_B200_OK;
-  joint_kernel<BN, MODE><<<grid, kThreads, smem, st>>>(mw, mh, p);
+  if (ntile < 1) return RNNT_B200_OK;
+  if (grid > ((ntile + 1) & ~1)) grid = (ntile + 1) & ~1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  e = cudaLaunchKernelEx(&cfg, joint_kernel<BN, MODE>, mw, mh, p);
+  if (e != cudaSuccess) return (int)e;
   RNNT_CUDA_RETURN_IF_ERROR();
   return RNNT_B200_OK;
 }
@@ -560,7 +611,7 @@ template <int MODE>
 int dispatch_joint(JointParams& p, const void* w2q, const void* h_stash, int max_tiles, cudaStream_t st) {
   const int BN = rnnt_b200_vocab_tile(p.V);
   CUtensorMap mw, mh;
-  int rc = make_map_bf16(&mw, w2q, p.Vpad, p.H, p.H, kBK, BN, CU_TENSOR_MAP_SWIZZLE_64B);
+  int rc = make_map_bf16(&mw, w2q, p.Vpad, p.H, p.H, kBK, BN / 2, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
   if (MODE == 1) {
     rc = make_map_bf16(&mh, h_stash, (uint64_t)max_tiles * RNNT_TILE_M, p.H, p.H + 8, kKBlock, RNNT_TILE_M,
