@@ -116,7 +116,9 @@ int rnnt_b200_h_pitch(int H);
 
 /* Fused forward: tcgen05/TMEM GEMM  tanh(P_enc[t]+P_dec[u]) . W2^T  with an online
  * log-sum-exp epilogue; writes lse / lp_blank / lp_label planes only.
- * h_stash: nullable bf16 (max_tiles*128, H+8) -- written when the backward is wanted. */
+ * h_stash: bf16 workspace (max_tiles*128, H+8), 128-byte aligned: written first with
+ * h = tanh(P_enc[t]+P_dec[u]) by a streaming kernel, then read as the GEMM's A operand by TMA;
+ * the backward reads it again. */
 int rnnt_b200_joint_fwd(const float* p_enc, const float* p_dec,
                         const void* w2_bf16, const float* b2_log2,
                         const int32_t* labels, const int32_t* act_lens, const int32_t* label_lens,
@@ -128,7 +130,8 @@ int rnnt_b200_joint_fwd(const float* p_enc, const float* p_dec,
 /* Fused backward, stage 1: recompute logits tiles from h_stash on the tensor cores and
  * emit dS = scale_b*(softmax*(c_blank+c_label) - onehots) as bf16 for tiles
  * [tile_lo, tile_hi) into ds (rows (tile_hi-tile_lo)*128, pitch Vpad). Rows of
- * tiles >= n_tiles[0] and rows past an utterance's last cell are written as zeros. */
+ * tiles >= n_tiles[0] and rows past an utterance's last cell are written as zeros.
+ * ds must be 128-byte aligned. */
 int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, const float* b2_log2,
                            const int32_t* labels, const int32_t* act_lens, const int32_t* label_lens,
                            const int32_t* tile_utt, const int32_t* tile_cell0, const int32_t* n_tiles,

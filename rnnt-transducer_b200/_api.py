@@ -265,9 +265,8 @@ class _JointLossFn(torch.autograd.Function):
             lse = torch.empty(n, dtype=torch.float32, device=dev)
             lpb = torch.empty(n, dtype=torch.float32, device=dev)
             lpl = torch.empty(n, dtype=torch.float32, device=dev)
-            h_stash = None
-            if need_grad:
-                h_stash = torch.empty(max_tiles * 128, L.rnnt_b200_h_pitch(H), dtype=torch.bfloat16, device=dev)
+            # bf16 hidden activations, tile-packed (M x (H+8), never M x V): the GEMM's A operand
+            h_stash = torch.empty(max_tiles * 128, L.rnnt_b200_h_pitch(H), dtype=torch.bfloat16, device=dev)
             _call("joint_fwd", L.rnnt_b200_joint_fwd, _ptr(pe), _ptr(pd), _ptr(w2q), _ptr(b2l), _ptr(labels),
                                              _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt),
                                              _ptr(tile_cell0), _ptr(n_tiles), B, T, U1, V, H, blank,
@@ -291,8 +290,11 @@ class _JointLossFn(torch.autograd.Function):
             scale = grad_out.to(torch.float32).contiguous()
             dpe = torch.zeros(B, T, H, dtype=torch.float32, device=dev)
             dpd = torch.zeros(B, U1, H, dtype=torch.float32, device=dev)
-            dw2x = torch.zeros(Vpad, H + 8, dtype=torch.float32, device=dev)
-            chunk = max(1, min(max_tiles, _DS_BUDGET_BYTES // (128 * Vpad * 2)))
+            dw2x = torch.zeros(Vpad, H + 8, dtype=torch.float32, device=dev)  # [dW2 | db2 | 0..]
+            chunk = max(2, min(max_tiles, _DS_BUDGET_BYTES // (128 * Vpad * 2)))
+            nchunk = -(-max_tiles // chunk)
+            chunk = -(-max_tiles // nchunk)          # balanced chunks,
+            chunk += chunk & 1                       # whole CTA-pair tiles
             ds = torch.empty(chunk * 128, Vpad, dtype=torch.bfloat16, device=dev)
             for lo in range(0, max_tiles, chunk):
                 hi = min(max_tiles, lo + chunk)
@@ -307,7 +309,14 @@ class _JointLossFn(torch.autograd.Function):
                 with _region("lib_gemm_dh"):
                     dh = torch.mm(dsc, w2q, out_dtype=torch.float32)                   # (rows, H)
                 with _region("lib_gemm_dw2"):
-                    dw2x += torch.mm(dsc.t(), h_stash[lo * 128: hi * 128], out_dtype=torch.float32)
+                    # K = rows is huge and M x N = Vpad x (H+8) small: split K four ways (batched
+                    # GEMM). Column H of h_ext is 1 for valid cells, so column H of the product is db2.
+                    hc = h_stash[lo * 128: hi * 128]
+                    if rows % 4 == 0:
+                        dw2x += torch.bmm(dsc.view(4, rows // 4, Vpad).transpose(1, 2),
+                                          hc.view(4, rows // 4, H + 8), out_dtype=torch.float32).sum(0)
+                    else:
+                        dw2x += torch.mm(dsc.t(), hc, out_dtype=torch.float32)
                 _call("dh_reduce", L.rnnt_b200_dh_reduce, _ptr(dh), _ptr(h_stash), _ptr(act_lens), _ptr(label_lens),
                                                  _ptr(tile_utt), _ptr(tile_cell0), _ptr(n_tiles), B, T, U1,
                                                  H, lo, hi, _ptr(dpe), _ptr(dpd), st)

@@ -3,27 +3,32 @@
 // Replaces, together, /root/reference rnnt/model.py:68 (JointNet.forward, model.py:18-37)
 // and the log-softmax stage of the loss call at model.py:70:
 //
-//   forward  : S[cell, v] = tanh(P_enc[b,t,:] + P_dec[b,u,:]) . W2[v,:] + b2[v]
-//              never leaves the SM: an online log-sum-exp epilogue reads the accumulators
-//              out of TMEM and emits 12 bytes per lattice cell (lse, lp_blank, lp_label).
-//   backward : the same GEMM is recomputed from the stashed bf16 hidden tile and the
-//              epilogue turns it into dS = scale*(softmax*(c_blank+c_label) - onehots), bf16.
+//   hidden   : h[cell,:] = bf16(tanh(P_enc[b,t,:] + P_dec[b,u,:])) for the valid lattice cells,
+//              tile-packed (M x H, never M x V) -- one streaming pass (hidden_kernel).
+//   forward  : S[cell, v] = h[cell,:] . W2[v,:] + b2[v] never leaves the SM: an online
+//              log-sum-exp epilogue reads the accumulators out of TMEM and emits 12 bytes per
+//              lattice cell (lse, lp_blank, lp_label).
+//   backward : the same GEMM is recomputed from h and the epilogue turns it into
+//              dS = scale*(softmax*(c_blank+c_label) - onehots), bf16.
 //
-// Work decomposition: lattice cells are flattened per utterance over the valid (t,u)
-// window and cut into tiles of 128 cells (the UMMA M). A persistent CTA per SM walks
-// tiles blockIdx.x, +gridDim.x, ...; for each tile it sweeps the vocabulary in BN-column
-// tiles with K = H. Warp roles (512 threads):
+// Work decomposition: lattice cells are flattened per utterance over the valid (t,u) window
+// and cut into tiles of 128 cells. The GEMM kernel runs as CTA PAIRS (cluster of 2,
+// tcgen05 cta_group::2, UMMA M = 256): the two CTAs own tiles 2*pt and 2*pt+1 and sweep the
+// vocabulary in lockstep in BN-column tiles with K = H; each CTA TMA-loads only its half
+// (BN/2 rows) of every W2 stage, which halves the L2->SM traffic per SM -- the measured
+// limiter of the single-CTA version (profiles/r01_notes.md). Pairs are persistent: pair c
+// walks pair-tiles c, c+gridDim/2, ...  Warp roles (352 threads per CTA):
 //   warps 0-7   epilogue: TMEM -> registers; warp w owns TMEM lanes 32*(w&3)..+31 (one
 //               lattice cell per thread) and column half (w>>2) of the BN-wide tile
-//   warps 8-11  A producer (forward): tanh(P_enc+P_dec) -> bf16 -> 128B-swizzled smem tile
-//   warp 12     TMA producer: W2 tiles (and, backward, the stashed h tile)
-//   warp 13     MMA issuer (one elected thread)
-//   warp 14     TMEM allocator
-//   warp 15     TMA producer of the stashed h tile (backward)
-// Pipelines: W2 smem ring (full/empty mbarriers), A tile per 64-wide K block
-// (a_full/a_empty so the next tile's tanh overlaps the last vocabulary tile's MMAs), and a
-// double-buffered TMEM accumulator (acc_full/acc_empty) so the epilogue of vocabulary
-// tile j overlaps the MMAs of tile j+1.
+//   warp 8      TMA producer: this CTA's half of each W2 stage
+//   warp 9      TMEM allocator (both CTAs) and MMA issuer (leader CTA, one elected thread)
+//   warp 10     TMA producer of the h tile (A operand, eight 64-wide K blocks, resident
+//               for the whole vocabulary sweep)
+// Pipelines (mbarriers): W2 smem ring b_full (leader, fed by both CTAs' TMA) / b_empty
+// (multicast tcgen05.commit); A tile a_full/a_empty per K block so the next tile's loads
+// overlap the last vocabulary tile's MMAs; double-buffered TMEM accumulator acc_full
+// (multicast commit) / acc_empty (16 epilogue warps of the pair arrive on the leader) so the
+// epilogue of vocabulary tile j overlaps the MMAs of tile j+1.
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <stdlib.h>
@@ -34,19 +39,13 @@ using namespace sm100;
 
 namespace {
 
-constexpr int kThreads = 512;
+constexpr int kThreads = 352;  // 8 epilogue warps + W2 TMA + MMA + A TMA
 constexpr int kEpiWarps = 8;
-constexpr int kProdThreads = 128;
 constexpr int kKBlock = 64;              // A tile K block (128-byte swizzle span of bf16)
 constexpr int kBK = 64;                  // W2 stage K extent (128-byte swizzle span of bf16)
 constexpr int kABlockBytes = RNNT_TILE_M * 128;
 constexpr int kMaxStages = 8;
 constexpr int kSmemLimit = 232448;       // 227 KB opt-in maximum per CTA
-
-struct TileInfo {  // per-row info shared inside the producer group
-  int pe_off;      // element offset of P_enc[b,t,0]; -1 = row past the utterance's last cell
-  int pd_off;
-};
 
 struct SharedCtl {
   uint64_t a_full[8], a_empty[8];
@@ -54,7 +53,6 @@ struct SharedCtl {
   uint64_t acc_full[2], acc_empty[2];
   uint32_t tmem_base;
   uint32_t pad;
-  TileInfo info[RNNT_TILE_M];
   float4 red[2][RNNT_TILE_M];
 };
 
@@ -84,8 +82,9 @@ struct JointParams {
   int debug;  // RNNT_B200_DEBUG bitmask (timing experiments only): 1 skip epilogue math, 2 skip producer math, 4 skip MMA issue
 };
 
-__host__ __device__ inline int smem_bytes_for(int H, int BN, int stages) {
-  return 1024 /*align slack*/ + (H / kKBlock) * kABlockBytes + stages * (BN / 2) * 128 + (int)sizeof(SharedCtl);
+__host__ __device__ inline int smem_bytes_for(int H, int BN, int stages, int mode) {
+  return 1024 /*align slack*/ + (H / kKBlock) * kABlockBytes + stages * (BN / 2) * 128 +
+         (mode == 1 ? kEpiWarps * 2048 : 0) + (int)sizeof(SharedCtl);
 }
 
 __device__ __forceinline__ float tanh_accurate(float x) {
@@ -124,7 +123,7 @@ __device__ __forceinline__ RowCoord locate_row(const JointParams& p, int tile, i
 template <int BN, int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
 joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__ CUtensorMap map_h,
-             const JointParams p) {
+             const __grid_constant__ CUtensorMap map_ds, const JointParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int KB = p.H / kKBlock;      // A K-blocks of 64
@@ -133,7 +132,8 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + KB * kABlockBytes;
   constexpr int kStageBytes = (BN / 2) * 128;  // this CTA's half of a W2 stage: BN/2 rows x 64 k
-  SharedCtl* ctl = reinterpret_cast<SharedCtl*>(smem_b + p.stages * kStageBytes);
+  uint8_t* smem_ds = smem_b + p.stages * kStageBytes;  // MODE 1: 8 x 2 KB dS staging tiles
+  SharedCtl* ctl = reinterpret_cast<SharedCtl*>(smem_ds + (MODE == 1 ? kEpiWarps * 2048 : 0));
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -144,13 +144,13 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
   const int cid = blockIdx.x >> 1, ncl = gridDim.x >> 1;
   const int n_pairs = (max(n_tiles - p.tile_lo, 0) + 1) >> 1;
 
-  if (warp == 12 && lane == 0) {
+  if (warp == 8 && lane == 0) {
     tma_prefetch_desc(&map_w2);
-    if (MODE == 1) tma_prefetch_desc(&map_h);
+    tma_prefetch_desc(&map_h);
   }
-  if (warp == 13 && lane == 0) {
+  if (warp == 9 && lane == 0) {
     for (int i = 0; i < 8; ++i) {
-      mbar_init(&ctl->a_full[i], MODE == 0 ? 2 * (kProdThreads / 32) : 2);
+      mbar_init(&ctl->a_full[i], 2);
       mbar_init(&ctl->a_empty[i], 1);
     }
     for (int i = 0; i < kMaxStages; ++i) {
@@ -165,7 +165,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
   }
   __syncwarp();
   cluster_sync_all();  // barrier inits visible to the peer before any remote arrive / multicast commit
-  if (warp == 13) {
+  if (warp == 9) {
     tmem_alloc_pair(&ctl->tmem_base, 512);
     tmem_relinquish_pair();
   }
@@ -177,6 +177,8 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
   if (warp < kEpiWarps) {
     // =========================== EPILOGUE ===========================
     const int q = warp & 3, half = warp >> 2;
+    uint8_t* stage_w = smem_ds + warp * 2048;  // MODE 1: per-warp dS staging tile
+    (void)stage_w;
     const int row = q * 32 + lane;
     constexpr int HALF = BN / 2;
     constexpr int NCH = HALF / 32;
@@ -262,16 +264,25 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
 #pragma unroll
               for (int j = 0; j < 32; ++j) g[j] -= (j == k) ? cls : 0.f;
             }
-            uint4* dst = reinterpret_cast<uint4*>(p.ds + ((size_t)(tile - p.tile_lo) * RNNT_TILE_M + row) * p.Vpad + col0);
+            // 32 cells x 32 columns of bf16 -> this warp's 2 KB staging tile (64-byte rows,
+            // SWIZZLE_64B: conflict-free 16-byte stores) -> one TMA store (full-sector writes).
+            if (lane == 0) bulk_wait_group_read0();  // previous store has finished reading the tile
+            __syncwarp();
+            uint8_t* srow = stage_w + lane * 64;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              if (dead) break;
               uint4 o;
               o.x = pack_bf16x2(g[8 * j + 0], g[8 * j + 1]);
               o.y = pack_bf16x2(g[8 * j + 2], g[8 * j + 3]);
               o.z = pack_bf16x2(g[8 * j + 4], g[8 * j + 5]);
               o.w = pack_bf16x2(g[8 * j + 6], g[8 * j + 7]);
-              dst[j] = o;
+              *reinterpret_cast<uint4*>(srow + ((j ^ ((lane >> 1) & 3)) << 4)) = o;
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0 && !dead && !(p.debug & 16)) {
+              tma_store_2d(&map_ds, stage_w, col0, (tile - p.tile_lo) * RNNT_TILE_M + q * 32);
+              bulk_commit_group();
             }
           }
         }
@@ -295,6 +306,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       }
     }
     if (MODE == 1) {
+      if (lane == 0) bulk_wait_group0();  // all of this warp's dS stores have landed
       // tiles of this launch past the end of the tile table: dS rows are defined as zero
       const int first_dead = max(n_tiles, p.tile_lo);
       const int epi_tid = threadIdx.x;  // 0..255
@@ -304,70 +316,8 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         for (size_t i = epi_tid; i < n16; i += kEpiWarps * 32) dst[i] = make_uint4(0, 0, 0, 0);
       }
     }
-  } else if (warp < 12) {
-    // =========================== A PRODUCER (forward only) ===========================
-    if (MODE == 0) {
-      const int ptid = threadIdx.x - kEpiWarps * 32;  // 0..127
-      const int chunk = ptid & 7;
-      const int row0 = ptid >> 3;
-      const int hp = p.H + 8;
-      int it = 0;
-      for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
-      const int tile = p.tile_lo + 2 * pt + (int)rank;
-      const bool dead = tile >= n_tiles;  // odd tail: this CTA only keeps the pair's protocol going
-      (void)dead;
-        {
-          const RowCoord rc = locate_row(p, tile, ptid, dead);
-          TileInfo ti;
-          ti.pe_off = rc.valid ? (rc.b * p.T + rc.t) * p.H : -1;
-          ti.pd_off = rc.valid ? (rc.b * p.U1 + rc.u) * p.H : -1;
-          named_bar_sync(2, kProdThreads);  // previous tile's readers are done with info[]
-          ctl->info[ptid] = ti;
-          named_bar_sync(2, kProdThreads);
-          if (p.h_stash && !dead) {  // "ones" column block H..H+7 (column H = 1 for valid cells)
-            uint4 o = make_uint4(rc.valid ? 0x00003F80u : 0u, 0u, 0u, 0u);
-            *reinterpret_cast<uint4*>(p.h_stash + ((size_t)tile * RNNT_TILE_M + ptid) * hp + p.H) = o;
-          }
-        }
-        for (int kb = 0; kb < KB; ++kb) {
-          mbar_wait(&ctl->a_empty[kb], (it & 1) ^ 1);
-          uint8_t* ablk = smem_a + kb * kABlockBytes;
-          const int k0 = kb * kKBlock + chunk * 8;
-#pragma unroll 4
-          for (int i = 0; i < RNNT_TILE_M / 16; ++i) {
-            const int row = row0 + 16 * i;
-            const TileInfo ti = ctl->info[row];
-            uint4 o = make_uint4(0u, 0u, 0u, 0u);
-            if (ti.pe_off >= 0 && !(p.debug & 2)) {
-              const float4* e4 = reinterpret_cast<const float4*>(p.pe + ti.pe_off + k0);
-              const float4* d4 = reinterpret_cast<const float4*>(p.pd + ti.pd_off + k0);
-              const float4 e0 = __ldg(e4), e1 = __ldg(e4 + 1), d0 = __ldg(d4), d1 = __ldg(d4 + 1);
-              o.x = pack_bf16x2(tanh_accurate(e0.x + d0.x), tanh_accurate(e0.y + d0.y));
-              o.y = pack_bf16x2(tanh_accurate(e0.z + d0.z), tanh_accurate(e0.w + d0.w));
-              o.z = pack_bf16x2(tanh_accurate(e1.x + d1.x), tanh_accurate(e1.y + d1.y));
-              o.w = pack_bf16x2(tanh_accurate(e1.z + d1.z), tanh_accurate(e1.w + d1.w));
-            }
-            *reinterpret_cast<uint4*>(ablk + row * 128 + ((chunk ^ (row & 7)) << 4)) = o;
-            if (p.h_stash && !dead)
-              *reinterpret_cast<uint4*>(p.h_stash + ((size_t)tile * RNNT_TILE_M + row) * hp + k0) = o;
-          }
-          fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the MMA (async proxy)
-          __syncwarp();
-          if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&ctl->a_full[kb]), 0));
-        }
-      }
-      if (p.h_stash) {
-        // rows of tiles past the end of the tile table must be finite (they meet dS = 0 in a GEMM)
-        const int first_dead = max(n_tiles, p.tile_lo);
-        for (int tile = first_dead + blockIdx.x; tile < p.tile_hi; tile += gridDim.x) {
-          uint4* dst = reinterpret_cast<uint4*>(p.h_stash + (size_t)tile * RNNT_TILE_M * hp);
-          const int n16 = RNNT_TILE_M * hp / 8;
-          for (int i = ptid; i < n16; i += kProdThreads) dst[i] = make_uint4(0, 0, 0, 0);
-        }
-      }
-    }
-  } else if (warp == 12) {
-    // =========================== TMA PRODUCER ===========================
+  } else if (warp == 8) {
+    // =========================== TMA PRODUCER (W2) ===========================
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
       int it = 0;
@@ -388,9 +338,9 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         }
       }
     }
-  } else if (warp == 15) {
-    // =========================== A TILE TMA (backward only) ===========================
-    if (MODE == 1 && lane == 0) {
+  } else if (warp == 10) {
+    // =========================== A TILE TMA (stashed bf16 hidden tile) ===========================
+    if (lane == 0) {
       int it = 0;
       for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
       const int tile = p.tile_lo + 2 * pt + (int)rank;
@@ -405,7 +355,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         }
       }
     }
-  } else if (warp == 13) {
+  } else if (warp == 9) {
     // =========================== MMA ISSUER ===========================
     if (lane == 0 && rank == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(2 * RNNT_TILE_M, BN);
@@ -443,7 +393,52 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
   __syncwarp();  // single-lane roles: reconverge before the aligned cluster barrier
   tc_fence_before();
   cluster_sync_all();  // peer may still target this CTA's barriers / TMEM until here
-  if (warp == 13) tmem_dealloc_pair(tmem_base, 512);
+  if (warp == 9) tmem_dealloc_pair(tmem_base, 512);
+}
+
+// ---------------------------------------------------------------------------------------
+// h = bf16(tanh(P_enc[t] + P_dec[u])) for every tile row; the decomposed first joint layer
+// (model.py:26-34 without the repeat/cat). One CTA per tile, 64 threads per row (each 8
+// consecutive k: 2x16 B loads from each addend, one 16 B store), 4 rows in flight per pass.
+// Rows past an utterance's last cell and tiles past the table are written as zeros;
+// column H of the 8-wide tail is 1.0 for valid cells (the "ones" column that makes
+// dS^T.h_ext produce d b2).
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+hidden_kernel(const JointParams p, int max_tiles) {
+  const int n_tiles = min(p.n_tiles[0], max_tiles);
+  const int hp = p.H + 8;
+  const int cpr = p.H / 8;            // 16-byte chunks per row
+  const int rows_per_pass = 256 / cpr;  // H=512: 4 rows per pass
+  const int chunk = threadIdx.x % cpr;
+  const int rsub = threadIdx.x / cpr;
+  for (int tile = blockIdx.x; tile < max_tiles; tile += gridDim.x) {
+    const bool dead = tile >= n_tiles;
+    __nv_bfloat16* dst_tile = p.h_stash + (size_t)tile * RNNT_TILE_M * hp;
+    if (threadIdx.x < RNNT_TILE_M) {
+      const RowCoord rc = locate_row(p, tile, threadIdx.x, dead);
+      *reinterpret_cast<uint4*>(dst_tile + (size_t)threadIdx.x * hp + p.H) =
+          make_uint4(rc.valid ? 0x00003F80u : 0u, 0u, 0u, 0u);
+    }
+    if (rsub < rows_per_pass) {
+#pragma unroll 2
+      for (int r0 = 0; r0 < RNNT_TILE_M; r0 += rows_per_pass) {
+        const int row = r0 + rsub;
+        const RowCoord rc = locate_row(p, tile, row, dead);
+        uint4 o = make_uint4(0u, 0u, 0u, 0u);
+        if (rc.valid) {
+          const float4* e4 = reinterpret_cast<const float4*>(p.pe + ((size_t)rc.b * p.T + rc.t) * p.H) + chunk * 2;
+          const float4* d4 = reinterpret_cast<const float4*>(p.pd + ((size_t)rc.b * p.U1 + rc.u) * p.H) + chunk * 2;
+          const float4 e0 = __ldg(e4), e1 = __ldg(e4 + 1), d0 = __ldg(d4), d1 = __ldg(d4 + 1);
+          o.x = pack_bf16x2(tanh_accurate(e0.x + d0.x), tanh_accurate(e0.y + d0.y));
+          o.y = pack_bf16x2(tanh_accurate(e0.z + d0.z), tanh_accurate(e0.w + d0.w));
+          o.z = pack_bf16x2(tanh_accurate(e1.x + d1.x), tanh_accurate(e1.y + d1.y));
+          o.w = pack_bf16x2(tanh_accurate(e1.z + d1.z), tanh_accurate(e1.w + d1.w));
+        }
+        *reinterpret_cast<uint4*>(dst_tile + (size_t)row * hp + chunk * 8) = o;
+      }
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -566,22 +561,25 @@ int sm_count() {
   return n;
 }
 
-int pick_stages(int H, int BN) {
+int pick_stages(int H, int BN, int mode) {
   int s = kMaxStages;
-  while (s > 2 && smem_bytes_for(H, BN, s) > kSmemLimit) --s;
+  while (s > 2 && smem_bytes_for(H, BN, s, mode) > kSmemLimit) --s;
   return s;
 }
 
 template <int BN, int MODE>
-int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, JointParams& p, cudaStream_t st) {
-  p.stages = pick_stages(p.H, BN);
+int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap& md, JointParams& p,
+                 cudaStream_t st) {
+  p.stages = pick_stages(p.H, BN, MODE);
   {
     const char* dbg = getenv("RNNT_B200_DEBUG");
     p.debug = dbg ? atoi(dbg) : 0;
+    const char* dm = getenv("RNNT_B200_DEBUG_MODE");
+    if (dm && atoi(dm) != MODE) p.debug = 0;
     const char* stg = getenv("RNNT_B200_STAGES");
     if (stg && atoi(stg) >= 2 && atoi(stg) < p.stages) p.stages = atoi(stg);
   }
-  const int smem = smem_bytes_for(p.H, BN, p.stages);
+  const int smem = smem_bytes_for(p.H, BN, p.stages, MODE);
   if (smem > kSmemLimit) return RNNT_B200_E_SHAPE;
   cudaError_t e = cudaFuncSetAttribute(joint_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return (int)e;
@@ -601,7 +599,7 @@ int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, JointParams& p, c
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  e = cudaLaunchKernelEx(&cfg, joint_kernel<BN, MODE>, mw, mh, p);
+  e = cudaLaunchKernelEx(&cfg, joint_kernel<BN, MODE>, mw, mh, md, p);
   if (e != cudaSuccess) return (int)e;
   RNNT_CUDA_RETURN_IF_ERROR();
   return RNNT_B200_OK;
@@ -613,17 +611,19 @@ int dispatch_joint(JointParams& p, const void* w2q, const void* h_stash, int max
   CUtensorMap mw, mh;
   int rc = make_map_bf16(&mw, w2q, p.Vpad, p.H, p.H, kBK, BN / 2, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
-  if (MODE == 1) {
-    rc = make_map_bf16(&mh, h_stash, (uint64_t)max_tiles * RNNT_TILE_M, p.H, p.H + 8, kKBlock, RNNT_TILE_M,
-                       CU_TENSOR_MAP_SWIZZLE_128B);
+  rc = make_map_bf16(&mh, h_stash, (uint64_t)max_tiles * RNNT_TILE_M, p.H, p.H + 8, kKBlock, RNNT_TILE_M,
+                     CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  CUtensorMap md = mw;
+  if (MODE == 1) {  // dS chunk (rows x Vpad): 32 x 32 store boxes out of 64-byte-swizzled staging tiles
+    rc = make_map_bf16(&md, p.ds, (uint64_t)(p.tile_hi - p.tile_lo) * RNNT_TILE_M, p.Vpad, p.Vpad, 32, 32,
+                       CU_TENSOR_MAP_SWIZZLE_64B);
     if (rc) return rc;
-  } else {
-    mh = mw;
   }
   switch (BN) {
-    case 64: return launch_joint<64, MODE>(mw, mh, p, st);
-    case 128: return launch_joint<128, MODE>(mw, mh, p, st);
-    default: return launch_joint<256, MODE>(mw, mh, p, st);
+    case 64: return launch_joint<64, MODE>(mw, mh, md, p, st);
+    case 128: return launch_joint<128, MODE>(mw, mh, md, p, st);
+    default: return launch_joint<256, MODE>(mw, mh, md, p, st);
   }
 }
 
@@ -645,13 +645,13 @@ extern "C" int rnnt_b200_joint_fwd(const float* p_enc, const float* p_dec, const
                                    int V, int H, int blank, float* lse, float* lp_blank, float* lp_label,
                                    void* h_stash, void* stream) {
   if (!p_enc || !p_dec || !w2_bf16 || !b2_log2 || !act_lens || !label_lens || !tile_utt || !tile_cell0 ||
-      !n_tiles || !lse || !lp_blank || !lp_label)
+      !n_tiles || !lse || !lp_blank || !lp_label || !h_stash)
     return RNNT_B200_E_NULL;
   if (U1 > 1 && !labels) return RNNT_B200_E_NULL;
   int rc = check_common(B, T, U1, V, H, blank);
   if (rc) return rc;
   if (((uintptr_t)p_enc & 15) || ((uintptr_t)p_dec & 15) || ((uintptr_t)w2_bf16 & 127) ||
-      ((uintptr_t)b2_log2 & 15) || ((uintptr_t)h_stash & 15))
+      ((uintptr_t)b2_log2 & 15) || ((uintptr_t)h_stash & 127))
     return RNNT_B200_E_ALIGN;
   JointParams p = {};
   p.pe = p_enc; p.pd = p_dec; p.b2l = b2_log2; p.labels = labels; p.act_lens = act_lens;
@@ -659,7 +659,12 @@ extern "C" int rnnt_b200_joint_fwd(const float* p_enc, const float* p_dec, const
   p.lse = lse; p.lpb = lp_blank; p.lpl = lp_label; p.h_stash = (__nv_bfloat16*)h_stash;
   p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vpad = rnnt_b200_vocab_pad(V); p.H = H; p.blank = blank;
   p.tile_lo = 0; p.tile_hi = rnnt_b200_max_tiles(B, T, U1);
-  return dispatch_joint<0>(p, w2_bf16, nullptr, p.tile_hi, (cudaStream_t)stream);
+  {
+    int grid = p.tile_hi < 148 * 8 ? p.tile_hi : 148 * 8;
+    hidden_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p, p.tile_hi);
+    RNNT_CUDA_RETURN_IF_ERROR();
+  }
+  return dispatch_joint<0>(p, w2_bf16, h_stash, p.tile_hi, (cudaStream_t)stream);
 }
 
 extern "C" int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, const float* b2_log2,
