@@ -140,13 +140,14 @@ int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, const float
                            int B, int T, int U1, int V, int H, int blank,
                            int tile_lo, int tile_hi, void* ds, void* stream);
 
-/* Fused backward, stage 2: dpre = dh * (1 - h^2) and its two reductions
- *   dP_enc[b,t,:] += sum_u dpre,   dP_dec[b,u,:] += sum_t dpre     (float32, atomics)
- * for tiles [tile_lo, tile_hi). dh: float32 rows (tile_hi-tile_lo)*128, pitch H. */
-int rnnt_b200_dh_reduce(const float* dh, const void* h_stash,
+/* Fused backward, stage 2: dpre = dh_scale * dh * (1 - h^2) and its two reductions
+ *   dP_enc[b,t,:] += sum_u dpre,   dP_dec[b,u,:] += sum_t dpre     (float32, red.global.add)
+ * for the packed rows of tiles [tile_lo, tile_hi). dh: bf16 rows (tile_hi-tile_lo)*128, pitch H
+ * (the library GEMM dS . W2_bf16). dp_enc (B,T,H) and dp_dec (B,U1,H) must be zeroed by the
+ * caller before the first chunk. */
+int rnnt_b200_dh_reduce(const void* dh_bf16, const void* h_stash,
                         const int32_t* act_lens, const int32_t* label_lens,
-                        const int32_t* tile_utt, const int32_t* tile_cell0, const int32_t* n_tiles,
-                        int B, int T, int U1, int H, int tile_lo, int tile_hi,
+                        int B, int T, int U1, int H, int tile_lo, int tile_hi, float dh_scale,
                         float* dp_enc, float* dp_dec, void* stream);
 
 /* Plain bf16 tensor-core GEMM used to validate the tcgen05/TMA plumbing on its own:

@@ -20,9 +20,11 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from . import _lib
+from ._shard import allreduce_grads_and_loss, global_mean_loss, shard_batch
 
 __all__ = ["RNNTLoss", "rnnt_loss", "JointNet", "JointRNNTLoss", "joint_rnnt_loss",
-           "build_extension", "extension_path", "selftest_gemm", "KernelTimer"]
+           "build_extension", "extension_path", "selftest_gemm", "KernelTimer",
+           "shard_batch", "global_mean_loss", "allreduce_grads_and_loss"]
 
 
 def build_extension(verbose: bool = False) -> str:
@@ -307,7 +309,7 @@ class _JointLossFn(torch.autograd.Function):
                                                     _ptr(dsc), st)
                 # two plain library GEMMs on the staged bf16 gradient tile (fp32 accumulate/out)
                 with _region("lib_gemm_dh"):
-                    dh = torch.mm(dsc, w2q, out_dtype=torch.float32)                   # (rows, H)
+                    dh = torch.mm(dsc, w2q)                                            # (rows, H) bf16
                 with _region("lib_gemm_dw2"):
                     # K = rows is huge and M x N = Vpad x (H+8) small: split K four ways (batched
                     # GEMM). Column H of h_ext is 1 for valid cells, so column H of the product is db2.
@@ -318,8 +320,7 @@ class _JointLossFn(torch.autograd.Function):
                     else:
                         dw2x += torch.mm(dsc.t(), hc, out_dtype=torch.float32)
                 _call("dh_reduce", L.rnnt_b200_dh_reduce, _ptr(dh), _ptr(h_stash), _ptr(act_lens), _ptr(label_lens),
-                                                 _ptr(tile_utt), _ptr(tile_cell0), _ptr(n_tiles), B, T, U1,
-                                                 H, lo, hi, _ptr(dpe), _ptr(dpd), st)
+                      B, T, U1, H, lo, hi, 1.0, _ptr(dpe), _ptr(dpd), st)
             dw2 = dw2x[:V, :H].contiguous()
             db2 = dw2x[:V, H].contiguous()
         return dpe, dpd, dw2, db2, None, None, None, None

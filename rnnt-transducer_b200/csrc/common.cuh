@@ -22,11 +22,14 @@ __host__ __device__ __forceinline__ size_t plane_index(int b, int t, int u, int 
 
 __device__ __forceinline__ int clamp_int(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 
-// log(exp(a)+exp(b)) in float64 with -inf handling.
+// log(exp(a)+exp(b)): the running value and the difference a-b are float64 (alpha/beta reach
+// ~1e3..1e4 nats, where fp32 would lose the 1e-4 gradient tolerance -- SURVEY.md F7); the
+// increment log1p(exp(-|a-b|)) lies in [0, ln 2] and is evaluated in fp32 (absolute error
+// ~1e-7 per wavefront step), which takes the float64 transcendentals off the serial chain.
 __device__ __forceinline__ double log_add_exp(double a, double b) {
-  double m = fmax(a, b);
-  double d = -fabs(a - b);
+  const double m = fmax(a, b);
+  const float d = (float)(-fabs(a - b));
   // d is NaN only when both are -inf (inf-inf); then m = -inf is the answer.
   if (!(d == d)) return m;
-  return m + log1p(exp(d));
+  return m + (double)log1pf(__expf(d));
 }

@@ -37,40 +37,78 @@ pack_vocab_kernel(const float* __restrict__ w2, const float* __restrict__ b2, in
   }
 }
 
-// One CTA per tile, one thread per hidden column k. Rows of a tile are consecutive
-// cells (t,u) of one utterance: runs of equal t are pre-reduced in a register before
-// one atomic into dP_enc; dP_dec takes one coalesced red per row.
-__global__ void __launch_bounds__(512)
-dh_reduce_kernel(const float* __restrict__ dh, const __nv_bfloat16* __restrict__ h,
+// dpre = dh * (1 - h^2) and its two reductions. One CTA per (utterance b, block of TT lattice
+// rows t); thread k owns hidden columns 2k, 2k+1 (bf16x2 loads, 128 B per warp and row). The u
+// loop is outermost so that the sum over the block's t rows for dP_dec[b,u,:] lives in a
+// register and costs ONE float2 red per (CTA,u); the TT partial sums for dP_enc[b,t,:] stay in
+// registers for the whole sweep (the u range is additionally split DH_US ways over gridDim.z). Cells of an utterance are contiguous in the tile-packed row
+// order, so row(t,u) = first_tile_b*128 + t*(U_b+1) + u; a launch covers the packed rows of
+// tiles [tile_lo, tile_hi) only (the caller stages dS/dh in chunks), hence the atomics on dP_enc.
+constexpr int DH_TT = 8;
+constexpr int DH_US = 4;  // u range split over gridDim.z: the u loop is a serial latency chain
+
+__global__ void __launch_bounds__(256, 4)
+dh_reduce_kernel(const __nv_bfloat16* __restrict__ dh, const __nv_bfloat16* __restrict__ h,
                  const int32_t* __restrict__ act_lens, const int32_t* __restrict__ label_lens,
-                 const int32_t* __restrict__ tile_utt, const int32_t* __restrict__ tile_cell0,
-                 const int32_t* __restrict__ n_tiles, int T, int U1, int H, int tile_lo,
+                 int T, int U1, int H, int tile_lo, int tile_hi, float dh_scale,
                  float* __restrict__ dpe, float* __restrict__ dpd) {
-  const int tile = tile_lo + blockIdx.x;
-  if (tile >= n_tiles[0]) return;
-  const int k = threadIdx.x;
-  const int b = tile_utt[tile];
-  const int cell0 = tile_cell0[tile];
+  const int b = blockIdx.y;
   const int Tb = clamp_int(act_lens[b], 1, T);
-  const int Ub1 = clamp_int(label_lens[b], 0, U1 - 1) + 1;
-  const int ncell = Tb * Ub1;
-  const int rows = min(RNNT_TILE_M, ncell - cell0);
-  const int hp = H + 8;
-  const float* dhp = dh + (size_t)blockIdx.x * RNNT_TILE_M * H + k;
-  const __nv_bfloat16* hpn = h + (size_t)tile * RNNT_TILE_M * hp + k;
-  int t = cell0 / Ub1, u = cell0 - t * Ub1;
-  float acc_e = 0.f;
-  for (int r = 0; r < rows; ++r) {
-    const float hv = __bfloat162float(hpn[(size_t)r * hp]);
-    const float g = dhp[(size_t)r * H] * (1.f - hv * hv);
-    acc_e += g;
-    atomicAdd(dpd + ((size_t)b * U1 + u) * H + k, g);
-    if (++u == Ub1) {
-      atomicAdd(dpe + ((size_t)b * T + t) * H + k, acc_e);
-      acc_e = 0.f; u = 0; ++t;
-    }
+  const int w = clamp_int(label_lens[b], 0, U1 - 1) + 1;
+  const int t0 = blockIdx.x * DH_TT;
+  if (t0 >= Tb) return;
+  int first_tile = 0;  // tiles of the utterances before b
+  for (int i = 0; i < b; ++i) {
+    const int n = clamp_int(act_lens[i], 1, T) * (clamp_int(label_lens[i], 0, U1 - 1) + 1);
+    first_tile += (n + RNNT_TILE_M - 1) / RNNT_TILE_M;
   }
-  if (u != 0) atomicAdd(dpe + ((size_t)b * T + t) * H + k, acc_e);
+  // packed-row window of this launch, relative to the utterance's first cell
+  const long long lo = (long long)(tile_lo - first_tile) * RNNT_TILE_M;
+  const long long hi = (long long)(tile_hi - first_tile) * RNNT_TILE_M;
+  const int nt = min(DH_TT, Tb - t0);
+  const long long c_first = (long long)t0 * w, c_last = (long long)(t0 + nt) * w;
+  if (c_last <= lo || c_first >= hi) return;
+  const int k2 = threadIdx.x;  // column pair
+  const int hp = H + 8;
+  const __nv_bfloat162* dh2 = reinterpret_cast<const __nv_bfloat162*>(dh) + k2;
+  const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(h) + k2;
+  float2 acc_e[DH_TT];
+#pragma unroll
+  for (int i = 0; i < DH_TT; ++i) acc_e[i] = make_float2(0.f, 0.f);
+  const int u_per = (w + DH_US - 1) / DH_US;
+  const int u_lo = blockIdx.z * u_per, u_hi = min(w, u_lo + u_per);
+  // a row that is always inside the window (loads of masked-out cells are redirected to it so
+  // that all 2*DH_TT loads of an iteration are unconditional and issue back to back)
+  const long long c_safe = max(c_first, lo);
+  for (int u = u_lo; u < u_hi; ++u) {
+    __nv_bfloat162 g[DH_TT], hv[DH_TT];
+    bool ok[DH_TT];
+#pragma unroll
+    for (int i = 0; i < DH_TT; ++i) {
+      const long long c = (long long)(t0 + i) * w + u;
+      ok[i] = (i < nt) && c >= lo && c < hi;
+      const long long cc = ok[i] ? c : c_safe;
+      g[i] = dh2[(size_t)(cc - lo) * (H / 2)];
+      hv[i] = h2[((size_t)first_tile * RNNT_TILE_M + cc) * (hp / 2)];
+    }
+    float2 acc_d = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int i = 0; i < DH_TT; ++i) {
+      const float2 gf = __bfloat1622float2(g[i]), hf = __bfloat1622float2(hv[i]);
+      const float vx = ok[i] ? gf.x * (1.f - hf.x * hf.x) : 0.f;
+      const float vy = ok[i] ? gf.y * (1.f - hf.y * hf.y) : 0.f;
+      acc_d.x += vx; acc_d.y += vy;
+      acc_e[i].x += vx; acc_e[i].y += vy;
+    }
+    acc_d.x *= dh_scale; acc_d.y *= dh_scale;
+    atomicAdd(reinterpret_cast<float2*>(dpd + ((size_t)b * U1 + u) * H) + k2, acc_d);
+  }
+#pragma unroll
+  for (int i = 0; i < DH_TT; ++i)
+    if (i < nt) {
+      acc_e[i].x *= dh_scale; acc_e[i].y *= dh_scale;
+      atomicAdd(reinterpret_cast<float2*>(dpe + ((size_t)b * T + t0 + i) * H) + k2, acc_e[i]);
+    }
 }
 
 }  // namespace
@@ -114,20 +152,18 @@ extern "C" int rnnt_b200_pack_vocab(const float* w2, const float* b2, int V, int
   return RNNT_B200_OK;
 }
 
-extern "C" int rnnt_b200_dh_reduce(const float* dh, const void* h_stash, const int32_t* act_lens,
-                                   const int32_t* label_lens, const int32_t* tile_utt,
-                                   const int32_t* tile_cell0, const int32_t* n_tiles, int B, int T,
-                                   int U1, int H, int tile_lo, int tile_hi, float* dp_enc,
-                                   float* dp_dec, void* stream) {
-  if (!dh || !h_stash || !act_lens || !label_lens || !tile_utt || !tile_cell0 || !n_tiles || !dp_enc ||
-      !dp_dec)
-    return RNNT_B200_E_NULL;
-  if (B <= 0 || T <= 0 || U1 <= 0 || H < 64 || H > 512 || (H & 63) || tile_lo < 0 || tile_hi < tile_lo)
+extern "C" int rnnt_b200_dh_reduce(const void* dh_bf16, const void* h_stash, const int32_t* act_lens,
+                                   const int32_t* label_lens, int B, int T, int U1, int H, int tile_lo,
+                                   int tile_hi, float dh_scale, float* dp_enc, float* dp_dec,
+                                   void* stream) {
+  if (!dh_bf16 || !h_stash || !act_lens || !label_lens || !dp_enc || !dp_dec) return RNNT_B200_E_NULL;
+  if (B <= 0 || B > 65535 || T <= 0 || U1 <= 0 || H < 64 || H > 512 || (H & 63) || tile_lo < 0 ||
+      tile_hi < tile_lo)
     return RNNT_B200_E_SHAPE;
   if (tile_hi == tile_lo) return RNNT_B200_OK;
-  dh_reduce_kernel<<<tile_hi - tile_lo, H, 0, (cudaStream_t)stream>>>(
-      dh, (const __nv_bfloat16*)h_stash, act_lens, label_lens, tile_utt, tile_cell0, n_tiles, T, U1, H,
-      tile_lo, dp_enc, dp_dec);
+  dh_reduce_kernel<<<dim3((T + DH_TT - 1) / DH_TT, B, DH_US), H / 2, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)dh_bf16, (const __nv_bfloat16*)h_stash, act_lens, label_lens, T, U1, H, tile_lo,
+      tile_hi, dh_scale, dp_enc, dp_dec);
   RNNT_CUDA_RETURN_IF_ERROR();
   return RNNT_B200_OK;
 }
