@@ -31,6 +31,7 @@
 // epilogue of vocabulary tile j overlaps the MMAs of tile j+1.
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include "common.cuh"
 #include "sm100_ptx.cuh"
@@ -53,7 +54,7 @@ struct SharedCtl {
   uint64_t acc_full[2], acc_empty[2];
   uint32_t tmem_base;
   uint32_t pad;
-  float4 red[2][RNNT_TILE_M];
+  float4 red[RNNT_TILE_M];
 };
 
 struct JointParams {
@@ -79,11 +80,12 @@ struct JointParams {
   int B, T, U1, V, Vpad, H, blank;
   int tile_lo, tile_hi;  // tile range of this launch
   int stages;
+  long long* trace;  // RNNT_B200_TRACE: clock64 stamps of cluster 0 / rank 0 (debug only)
   int debug;  // RNNT_B200_DEBUG bitmask (timing experiments only): 1 skip epilogue math, 2 skip producer math, 4 skip MMA issue
 };
 
 __host__ __device__ inline int smem_bytes_for(int H, int BN, int stages, int mode) {
-  return 1024 /*align slack*/ + (H / kKBlock) * kABlockBytes + stages * (BN / 2) * 128 +
+  return (H / kKBlock) * kABlockBytes + stages * (BN / 2) * 128 +
          (mode == 1 ? kEpiWarps * 2048 : 0) + (int)sizeof(SharedCtl);
 }
 
@@ -124,8 +126,8 @@ template <int BN, int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
 joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__ CUtensorMap map_h,
              const __grid_constant__ CUtensorMap map_ds, const JointParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  extern __shared__ __align__(1024) uint8_t smem[];  // no static smem in this kernel: base is 1024-aligned
+  if ((smem_u32(smem) & 1023u) != 0) __trap();       // the 128B-swizzle atoms need it
   const int KB = p.H / kKBlock;      // A K-blocks of 64
   const int KS = p.H / kBK;          // W2 stages per vocabulary tile (K steps of 64)
   const int NV = p.Vpad / BN;        // vocabulary tiles
@@ -209,9 +211,14 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
           nlse2 = -p.lse[pidx] * RNNT_LOG2E;
         }
       }
-      for (int vt = 0; vt < NV; ++vt, ++acc_it) {
+      for (int vi = 0; vi < NV; ++vi, ++acc_it) {
+        // pairs sweep the vocabulary in rotated order so that the 74 pairs do not all pull the
+        // same W2 lines out of L2 at the same moment (the online LSE is order independent)
+        const int vt = (vi + cid) % NV;
         const uint32_t buf = acc_it & 1;
+        const long long tr0 = clock64();
         mbar_wait(&ctl->acc_full[buf], (acc_it >> 1) & 1);
+        const long long tr1 = clock64();
         tc_fence_after();
 #pragma unroll
         for (int c = 0; c < NCH; ++c) {
@@ -289,13 +296,16 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&ctl->acc_empty[buf]), 0));
+        if (p.trace && blockIdx.x == 0 && threadIdx.x == 0 && acc_it < 4096) {
+          long long* t = p.trace + 6 * 4096;
+          t[3 * acc_it + 0] = tr0; t[3 * acc_it + 1] = tr1; t[3 * acc_it + 2] = clock64();
+        }
       }
       if (MODE == 0) {
-        const int slot = it & 1;
-        if (half == 1) ctl->red[slot][row] = make_float4(m, s, zb, zl);
+        if (half == 1) ctl->red[row] = make_float4(m, s, zb, zl);
         named_bar_sync(1, kEpiWarps * 32);
         if (half == 0 && rc.valid) {
-          const float4 o = ctl->red[slot][row];
+          const float4 o = ctl->red[row];
           const float mn = fmaxf(m, o.x);
           const float st = s * ex2_approx(m - mn) + o.y * ex2_approx(o.x - mn);
           const float lse2 = mn + log2f(st);
@@ -303,6 +313,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
           p.lpb[pidx] = (zb + o.z - lse2) * RNNT_LN2;
           p.lpl[pidx] = (label >= 0) ? (zl + o.w - lse2) * RNNT_LN2 : -INFINITY;
         }
+        named_bar_sync(1, kEpiWarps * 32);  // red[] is free again
       }
     }
     if (MODE == 1) {
@@ -320,19 +331,27 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
     // =========================== TMA PRODUCER (W2) ===========================
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
-      int it = 0;
+      int it = 0, tr_n = 0;
       for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
       const int tile = p.tile_lo + 2 * pt + (int)rank;
       const bool dead = tile >= n_tiles;  // odd tail: this CTA only keeps the pair's protocol going
       (void)dead;
-        for (int vt = 0; vt < NV; ++vt) {
+        for (int vi = 0; vi < NV; ++vi) {
+          const int vt = (vi + cid) % NV;
           for (int ks = 0; ks < KS; ++ks) {
+            const long long tr0 = clock64();
             mbar_wait(&ctl->b_empty[stage], phase ^ 1);
+            const long long tr1 = clock64();
             const uint32_t full = mapa_u32(smem_u32(&ctl->b_full[stage]), 0);
             if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[stage], 2 * kStageBytes);
             else mbar_arrive_cluster(full);
             tma_load_2d_pair(smem_b + stage * kStageBytes, &map_w2, full, ks * kBK,
                              vt * BN + (int)rank * (BN / 2));
+            if (p.trace && blockIdx.x == 0 && tr_n < 4096) {
+              long long* t = p.trace + 3 * 4096;
+              t[3 * tr_n + 0] = tr0; t[3 * tr_n + 1] = tr1; t[3 * tr_n + 2] = clock64();
+              ++tr_n;
+            }
             if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
           }
         }
@@ -360,7 +379,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
     if (lane == 0 && rank == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(2 * RNNT_TILE_M, BN);
       uint32_t stage = 0, phase = 0, acc_it = 0;
-      int it = 0;
+      int it = 0, tr_n = 0;
       for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
       const int tile = p.tile_lo + 2 * pt + (int)rank;
       const bool dead = tile >= n_tiles;  // odd tail: this CTA only keeps the pair's protocol going
@@ -373,7 +392,9 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
           for (int ks = 0; ks < KS; ++ks) {
             const int kb = ks;
             if (vt == 0) mbar_wait(&ctl->a_full[kb], it & 1);
+            const long long tr0 = clock64();
             mbar_wait(&ctl->b_full[stage], phase);
+            const long long tr1 = clock64();
             tc_fence_after();
             const uint64_t adesc = umma_desc_kmajor<128>(smem_u32(smem_a + kb * kABlockBytes));
             const uint64_t bdesc = umma_desc_kmajor<128>(smem_u32(smem_b + stage * kStageBytes));
@@ -382,6 +403,10 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
               if (!(p.debug & 4)) umma_bf16_ss_pair(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | k) != 0);
             umma_commit_pair_mc(&ctl->b_empty[stage], 3);
             if (vt == NV - 1) umma_commit_pair_mc(&ctl->a_empty[kb], 3);
+            if (p.trace && blockIdx.x == 0 && tr_n < 4096) {
+              p.trace[3 * tr_n + 0] = tr0; p.trace[3 * tr_n + 1] = tr1; p.trace[3 * tr_n + 2] = clock64();
+              ++tr_n;
+            }
             if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
           }
           umma_commit_pair_mc(&ctl->acc_full[buf], 3);
@@ -587,6 +612,10 @@ int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap
   const int ntile = p.tile_hi - p.tile_lo;
   if (ntile < 1) return RNNT_B200_OK;
   if (grid > ((ntile + 1) & ~1)) grid = (ntile + 1) & ~1;
+  {
+    const char* g = getenv("RNNT_B200_GRID");  // timing experiments only
+    if (g && atoi(g) >= 2 && atoi(g) < grid) grid = atoi(g) & ~1;
+  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(kThreads);
@@ -599,8 +628,26 @@ int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  const char* trace_path = getenv("RNNT_B200_TRACE");  // debug only: synchronises and writes a file
+  const char* trace_mode = getenv("RNNT_B200_DEBUG_MODE");
+  if (trace_path && trace_mode && atoi(trace_mode) != MODE) trace_path = nullptr;
+  p.trace = nullptr;
+  const size_t trace_bytes = 9 * 4096 * sizeof(long long);
+  if (trace_path) {
+    if (cudaMalloc(&p.trace, trace_bytes) != cudaSuccess) p.trace = nullptr;
+    else cudaMemsetAsync(p.trace, 0, trace_bytes, st);
+  }
   e = cudaLaunchKernelEx(&cfg, joint_kernel<BN, MODE>, mw, mh, md, p);
   if (e != cudaSuccess) return (int)e;
+  if (p.trace) {
+    long long* host = (long long*)malloc(trace_bytes);
+    cudaStreamSynchronize(st);
+    cudaMemcpy(host, p.trace, trace_bytes, cudaMemcpyDeviceToHost);
+    FILE* f = fopen(trace_path, "wb");
+    if (f) { fwrite(host, 1, trace_bytes, f); fclose(f); }
+    free(host);
+    cudaFree(p.trace);
+  }
   RNNT_CUDA_RETURN_IF_ERROR();
   return RNNT_B200_OK;
 }
