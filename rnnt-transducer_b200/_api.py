@@ -311,14 +311,12 @@ class _JointLossFn(torch.autograd.Function):
                 with _region("lib_gemm_dh"):
                     dh = torch.mm(dsc, w2q)                                            # (rows, H) bf16
                 with _region("lib_gemm_dw2"):
-                    # K = rows is huge and M x N = Vpad x (H+8) small: split K four ways (batched
-                    # GEMM). Column H of h_ext is 1 for valid cells, so column H of the product is db2.
+                    # K = rows is huge and M x N = Vpad x (H+8) small: split K two ways (batched GEMM;
+                    # measured best for N = H+8, profiles/r01_notes.md). Column H of h_ext is 1 for
+                    # valid cells, so column H of the product is db2.
                     hc = h_stash[lo * 128: hi * 128]
-                    if rows % 4 == 0:
-                        dw2x += torch.bmm(dsc.view(4, rows // 4, Vpad).transpose(1, 2),
-                                          hc.view(4, rows // 4, H + 8), out_dtype=torch.float32).sum(0)
-                    else:
-                        dw2x += torch.mm(dsc.t(), hc, out_dtype=torch.float32)
+                    dw2x += torch.bmm(dsc.view(2, rows // 2, Vpad).transpose(1, 2),
+                                      hc.view(2, rows // 2, H + 8), out_dtype=torch.float32).sum(0)
                 _call("dh_reduce", L.rnnt_b200_dh_reduce, _ptr(dh), _ptr(h_stash), _ptr(act_lens), _ptr(label_lens),
                       B, T, U1, H, lo, hi, 1.0, _ptr(dpe), _ptr(dpd), st)
             dw2 = dw2x[:V, :H].contiguous()

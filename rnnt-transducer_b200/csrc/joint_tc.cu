@@ -216,36 +216,48 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         // same W2 lines out of L2 at the same moment (the online LSE is order independent)
         const int vt = (vi + cid) % NV;
         const uint32_t buf = acc_it & 1;
-        const long long tr0 = clock64();
+        const long long tr0 = p.trace ? clock64() : 0;
         mbar_wait(&ctl->acc_full[buf], (acc_it >> 1) & 1);
-        const long long tr1 = clock64();
+        const long long tr1 = p.trace ? clock64() : 0;
         tc_fence_after();
+        // Software pipeline over the NCH 32-column chunks of this warp's half tile: the TMEM load
+        // of chunk c+1 is in flight while chunk c is reduced; the bias loads of chunk c are
+        // issued before the wait on its accumulators.
+        const uint32_t taddr0 = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN + half * HALF;
+        float zz[2][32];
+        if (!(p.debug & 1)) tmem_ld_32x32(taddr0, zz[0]);
 #pragma unroll
         for (int c = 0; c < NCH; ++c) {
           if (p.debug & 1) break;
+          float* z = zz[c & 1];
           const int col0 = vt * BN + half * HALF + c * 32;
-          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN + half * HALF + c * 32;
-          float z[32];
-          tmem_ld_32x32(taddr, z);
-          tmem_ld_wait();
           const float4* b4 = reinterpret_cast<const float4*>(p.b2l + col0);
+          float4 bb[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) bb[j] = __ldg(b4 + j);
+          tmem_ld_wait();
+          if (c + 1 < NCH) tmem_ld_32x32(taddr0 + (c + 1) * 32, zz[(c + 1) & 1]);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const float4 bb = __ldg(b4 + j);
-            z[4 * j + 0] = fmaf(z[4 * j + 0], RNNT_LOG2E, bb.x);
-            z[4 * j + 1] = fmaf(z[4 * j + 1], RNNT_LOG2E, bb.y);
-            z[4 * j + 2] = fmaf(z[4 * j + 2], RNNT_LOG2E, bb.z);
-            z[4 * j + 3] = fmaf(z[4 * j + 3], RNNT_LOG2E, bb.w);
+            z[4 * j + 0] = fmaf(z[4 * j + 0], RNNT_LOG2E, bb[j].x);
+            z[4 * j + 1] = fmaf(z[4 * j + 1], RNNT_LOG2E, bb[j].y);
+            z[4 * j + 2] = fmaf(z[4 * j + 2], RNNT_LOG2E, bb[j].z);
+            z[4 * j + 3] = fmaf(z[4 * j + 3], RNNT_LOG2E, bb[j].w);
           }
           if (MODE == 0) {
-            float cm = z[0];
+            float m0 = z[0], m1 = z[1], m2 = z[2], m3 = z[3];  // four independent max chains
 #pragma unroll
-            for (int j = 1; j < 32; ++j) cm = fmaxf(cm, z[j]);
-            const float mn = fmaxf(m, cm);
-            float acc = 0.f;
+            for (int j = 4; j < 32; j += 4) {
+              m0 = fmaxf(m0, z[j]); m1 = fmaxf(m1, z[j + 1]); m2 = fmaxf(m2, z[j + 2]); m3 = fmaxf(m3, z[j + 3]);
+            }
+            const float mn = fmaxf(m, fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;      // four independent sum chains
 #pragma unroll
-            for (int j = 0; j < 32; ++j) acc += ex2_approx(z[j] - mn);
-            s = s * ex2_approx(m - mn) + acc;
+            for (int j = 0; j < 32; j += 4) {
+              a0 += ex2_approx(z[j] - mn); a1 += ex2_approx(z[j + 1] - mn);
+              a2 += ex2_approx(z[j + 2] - mn); a3 += ex2_approx(z[j + 3] - mn);
+            }
+            s = s * ex2_approx(m - mn) + ((a0 + a1) + (a2 + a3));
             m = mn;
             if ((unsigned)(p.blank - col0) < 32u) {
               const int k = p.blank - col0;
@@ -339,9 +351,9 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         for (int vi = 0; vi < NV; ++vi) {
           const int vt = (vi + cid) % NV;
           for (int ks = 0; ks < KS; ++ks) {
-            const long long tr0 = clock64();
+            const long long tr0 = p.trace ? clock64() : 0;
             mbar_wait(&ctl->b_empty[stage], phase ^ 1);
-            const long long tr1 = clock64();
+            const long long tr1 = p.trace ? clock64() : 0;
             const uint32_t full = mapa_u32(smem_u32(&ctl->b_full[stage]), 0);
             if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[stage], 2 * kStageBytes);
             else mbar_arrive_cluster(full);
@@ -376,40 +388,45 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
     }
   } else if (warp == 9) {
     // =========================== MMA ISSUER ===========================
-    if (lane == 0 && rank == 0) {
+    // The whole warp walks the loop with warp-uniform control flow (cheap uniform-datapath
+    // descriptor arithmetic, no single-lane waterfall code); one elected lane issues.
+    if (rank == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(2 * RNNT_TILE_M, BN);
       uint32_t stage = 0, phase = 0, acc_it = 0;
       int it = 0, tr_n = 0;
+      const uint32_t a0 = smem_u32(smem_a), b0 = smem_u32(smem_b);
+      const bool tracing = p.trace != nullptr && blockIdx.x == 0;
       for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
-      const int tile = p.tile_lo + 2 * pt + (int)rank;
-      const bool dead = tile >= n_tiles;  // odd tail: this CTA only keeps the pair's protocol going
-      (void)dead;
         for (int vt = 0; vt < NV; ++vt, ++acc_it) {
           const uint32_t buf = acc_it & 1;
           mbar_wait(&ctl->acc_empty[buf], ((acc_it >> 1) & 1) ^ 1);
           tc_fence_after();
           const uint32_t tmem_d = tmem_base + buf * BN;
           for (int ks = 0; ks < KS; ++ks) {
-            const int kb = ks;
-            if (vt == 0) mbar_wait(&ctl->a_full[kb], it & 1);
-            const long long tr0 = clock64();
+            if (vt == 0) mbar_wait(&ctl->a_full[ks], it & 1);
+            const long long tr0 = tracing ? clock64() : 0;
             mbar_wait(&ctl->b_full[stage], phase);
-            const long long tr1 = clock64();
+            const long long tr1 = tracing ? clock64() : 0;
             tc_fence_after();
-            const uint64_t adesc = umma_desc_kmajor<128>(smem_u32(smem_a + kb * kABlockBytes));
-            const uint64_t bdesc = umma_desc_kmajor<128>(smem_u32(smem_b + stage * kStageBytes));
+            if (elect_one_sync()) {
+              const uint64_t adesc = umma_desc_kmajor<128>(a0 + ks * kABlockBytes);
+              const uint64_t bdesc = umma_desc_kmajor<128>(b0 + stage * kStageBytes);
+              if (!(p.debug & 4)) {
 #pragma unroll
-            for (int k = 0; k < kBK / 16; ++k)
-              if (!(p.debug & 4)) umma_bf16_ss_pair(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | k) != 0);
-            umma_commit_pair_mc(&ctl->b_empty[stage], 3);
-            if (vt == NV - 1) umma_commit_pair_mc(&ctl->a_empty[kb], 3);
-            if (p.trace && blockIdx.x == 0 && tr_n < 4096) {
+                for (int k = 0; k < kBK / 16; ++k)
+                  umma_bf16_ss_pair(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | k) != 0);
+              }
+              umma_commit_pair_mc(&ctl->b_empty[stage], 3);
+              if (vt == NV - 1) umma_commit_pair_mc(&ctl->a_empty[ks], 3);
+              if (ks == KS - 1) umma_commit_pair_mc(&ctl->acc_full[buf], 3);
+            }
+            __syncwarp();
+            if (tracing && lane == 0 && tr_n < 4096) {
               p.trace[3 * tr_n + 0] = tr0; p.trace[3 * tr_n + 1] = tr1; p.trace[3 * tr_n + 2] = clock64();
               ++tr_n;
             }
             if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
           }
-          umma_commit_pair_mc(&ctl->acc_full[buf], 3);
         }
       }
     }

@@ -18,7 +18,7 @@ with torch.no_grad():
     s=kt.summary()
 print("RESULT", os.environ.get("RNNT_B200_DEBUG","0"), os.environ.get("RNNT_B200_STAGES","-"), os.environ.get("RNNT_B200_GRID","-"), ["%%.3f"%%x for x in s["joint_fwd"]], "lattice", ["%%.3f"%%x for x in s["lattice"]])
 ''' % ROOT
-for dbg, stg, grd in [("37","3","148"),("37","4","148"),("37","6","148"),("33","3","148"),("33","6","148"),("32","3","148"),("32","6","148")]:
+for dbg, stg, grd in [("0","","148"),("1","","148"),("4","","148"),("5","","148")]:
     env = dict(os.environ, RNNT_B200_DEBUG=dbg, RNNT_B200_GRID=grd)
     if stg: env["RNNT_B200_STAGES"] = stg
     p = subprocess.run([sys.executable, "-c", CODE], env=env, capture_output=True, text=True, timeout=300)
