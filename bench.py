@@ -103,6 +103,8 @@ def run_reference(args, wl, rank, world):
     float64 loss with OpenMP). Rank 0 alone runs; each step is a bounded sample of the workload."""
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1; the CPU arm uses every host core (stated in `cores`)
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     from oracle import c_oracle, cpu_path
     c_oracle.build()
     n_utts = 1
@@ -148,6 +150,11 @@ def main():
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # Anything a library prints on stdout (NCCL prints its version there on first use) would
+    # break the one-JSON-line contract: route fd 1 to stderr until the result line is printed.
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -183,7 +190,7 @@ def main():
         dec.requires_grad_(True)
         for p_ in params:
             p_.grad = None
-        loss_b = fused_none(enc, dec, yy, tll, ull)
+        loss_b = fused_none(enc, dec, yy, tll, ull, host_lens=(tl, ul))
         loss_sum = loss_b.sum()
         (loss_sum / (B * world)).backward()
         if world > 1:
@@ -294,6 +301,8 @@ def main():
         line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
                                 "sample": f"1 of {B} utterances (B=1,T={T},U={U}), median of 2 passes; "
                                           "torch-CPU joint as model.py:18-37 + oracle/rnnt_oracle.c (OpenMP)"}
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:

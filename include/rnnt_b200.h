@@ -118,12 +118,16 @@ int rnnt_b200_h_pitch(int H);
  * log-sum-exp epilogue; writes lse / lp_blank / lp_label planes only.
  * h_stash: bf16 workspace (max_tiles*128, H+8), 128-byte aligned: written first with
  * h = tanh(P_enc[t]+P_dec[u]) by a streaming kernel, then read as the GEMM's A operand by TMA;
- * the backward reads it again. */
+ * the backward reads it again.
+ * tile_cap: number of tiles the tile-indexed workspaces (h_stash, tile table) are sized for;
+ * rnnt_b200_max_tiles(B,T,U1) when the lengths are only known on the device, or the exact
+ * sum_b ceil(T_b*(U_b+1)/128) when the caller also has them on the host (skips all padded work).
+ * It must not be smaller than the number of tiles actually present. */
 int rnnt_b200_joint_fwd(const float* p_enc, const float* p_dec,
                         const void* w2_bf16, const float* b2_log2,
                         const int32_t* labels, const int32_t* act_lens, const int32_t* label_lens,
                         const int32_t* tile_utt, const int32_t* tile_cell0, const int32_t* n_tiles,
-                        int B, int T, int U1, int V, int H, int blank,
+                        int B, int T, int U1, int V, int H, int blank, int tile_cap,
                         float* lse, float* lp_blank, float* lp_label,
                         void* h_stash, void* stream);
 
@@ -137,7 +141,7 @@ int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, const float
                            const int32_t* tile_utt, const int32_t* tile_cell0, const int32_t* n_tiles,
                            const float* lse, const float* c_blank, const float* c_label,
                            const float* scale,
-                           int B, int T, int U1, int V, int H, int blank,
+                           int B, int T, int U1, int V, int H, int blank, int tile_cap,
                            int tile_lo, int tile_hi, void* ds, void* stream);
 
 /* Fused backward, stage 2: dpre = dh_scale * dh * (1 - h^2) and its two reductions

@@ -244,7 +244,7 @@ class _JointLossFn(torch.autograd.Function):
     """(P_enc, P_dec, W2, b2) -> per-utterance loss; logits never materialised."""
 
     @staticmethod
-    def forward(ctx, pe, pd, w2, b2, labels, act_lens, label_lens, blank):
+    def forward(ctx, pe, pd, w2, b2, labels, act_lens, label_lens, blank, tile_cap):
         L = _lib.lib()
         B, T, H = pe.shape
         U1 = pd.shape[1]
@@ -254,6 +254,8 @@ class _JointLossFn(torch.autograd.Function):
         with torch.cuda.device(dev):
             st = _stream()
             max_tiles = L.rnnt_b200_max_tiles(B, T, U1)
+            if tile_cap is not None:   # exact tile count from host-side lengths: no padded work
+                max_tiles = max(1, min(max_tiles, int(tile_cap)))
             Vpad = L.rnnt_b200_vocab_pad(V)
             tile_utt = torch.empty(max_tiles, dtype=torch.int32, device=dev)
             tile_cell0 = torch.empty(max_tiles, dtype=torch.int32, device=dev)
@@ -271,7 +273,7 @@ class _JointLossFn(torch.autograd.Function):
             h_stash = torch.empty(max_tiles * 128, L.rnnt_b200_h_pitch(H), dtype=torch.bfloat16, device=dev)
             _call("joint_fwd", L.rnnt_b200_joint_fwd, _ptr(pe), _ptr(pd), _ptr(w2q), _ptr(b2l), _ptr(labels),
                                              _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt),
-                                             _ptr(tile_cell0), _ptr(n_tiles), B, T, U1, V, H, blank,
+                                             _ptr(tile_cell0), _ptr(n_tiles), B, T, U1, V, H, blank, max_tiles,
                                              _ptr(lse), _ptr(lpb), _ptr(lpl), _ptr(h_stash), st)
             loss, cb, cl = _lattice(lpb, lpl, act_lens, label_lens, B, T, U1)
         if need_grad:
@@ -305,7 +307,7 @@ class _JointLossFn(torch.autograd.Function):
                 _call("joint_bwd_ds", L.rnnt_b200_joint_bwd_ds, _ptr(h_stash), _ptr(w2q), _ptr(b2l), _ptr(labels),
                                                     _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt),
                                                     _ptr(tile_cell0), _ptr(n_tiles), _ptr(lse), _ptr(cb),
-                                                    _ptr(cl), _ptr(scale), B, T, U1, V, H, blank, lo, hi,
+                                                    _ptr(cl), _ptr(scale), B, T, U1, V, H, blank, max_tiles, lo, hi,
                                                     _ptr(dsc), st)
                 # two plain library GEMMs on the staged bf16 gradient tile (fp32 accumulate/out)
                 with _region("lib_gemm_dh"):
@@ -321,16 +323,26 @@ class _JointLossFn(torch.autograd.Function):
                       B, T, U1, H, lo, hi, 1.0, _ptr(dpe), _ptr(dpd), st)
             dw2 = dw2x[:V, :H].contiguous()
             db2 = dw2x[:V, H].contiguous()
-        return dpe, dpd, dw2, db2, None, None, None, None
+        return dpe, dpd, dw2, db2, None, None, None, None, None
+
+
+def _tile_count(host_lens) -> Optional[int]:
+    if host_lens is None:
+        return None
+    tl, ul = host_lens
+    return int(sum((int(t) * (int(u) + 1) + 127) // 128 for t, u in zip(tl, ul)))
 
 
 def joint_rnnt_loss(enc_state, dec_state, w1, b1, w2, b2, labels, act_lens, label_lens,
-                    blank: int = 0, reduction: str = "mean"):
+                    blank: int = 0, reduction: str = "mean", host_lens=None):
     """Fused replacement of rnnt/model.py:68 + :70.
 
     enc_state (B,T,E), dec_state (B,U+1,D) float32 CUDA; w1 (H,E+D) = forward_layer.weight
     (encoder columns first, model.py:31), b1 (H), w2 (V,H) = project_layer.weight, b2 (V).
     Autograd reaches enc_state, dec_state and all four joint parameters.
+    ``host_lens=(act_lens_cpu, label_lens_cpu)`` (optional, e.g. straight from the DataLoader as in
+    train.py:24-31) lets the op size its tile loops exactly instead of for the padded (B,T,U+1)
+    bound -- no device read-back is ever made to obtain it.
     """
     if enc_state.dim() != 3 or dec_state.dim() != 3:
         raise ValueError("enc_state must be (B,T,E) and dec_state (B,U+1,D)")
@@ -355,7 +367,7 @@ def joint_rnnt_loss(enc_state, dec_state, w1, b1, w2, b2, labels, act_lens, labe
     pe = F.linear(enc_state, w1[:, :E], b1).contiguous()
     pd = F.linear(dec_state, w1[:, E:]).contiguous()
     loss_b = _JointLossFn.apply(pe, pd, w2.contiguous(), b2.contiguous(), labels, act_lens, label_lens,
-                                int(blank))
+                                int(blank), _tile_count(host_lens))
     return _reduce(loss_b, reduction)
 
 
@@ -397,11 +409,11 @@ class JointRNNTLoss(nn.Module):
         self.blank = blank
         self.reduction = reduction
 
-    def forward(self, enc_state, dec_state, labels, act_lens, label_lens):
+    def forward(self, enc_state, dec_state, labels, act_lens, label_lens, host_lens=None):
         j = self.joint
         return joint_rnnt_loss(enc_state, dec_state, j.forward_layer.weight, j.forward_layer.bias,
                                j.project_layer.weight, j.project_layer.bias, labels, act_lens,
-                               label_lens, self.blank, self.reduction)
+                               label_lens, self.blank, self.reduction, host_lens)
 
 
 def selftest_gemm(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:

@@ -706,8 +706,8 @@ extern "C" int rnnt_b200_joint_fwd(const float* p_enc, const float* p_dec, const
                                    const float* b2_log2, const int32_t* labels, const int32_t* act_lens,
                                    const int32_t* label_lens, const int32_t* tile_utt,
                                    const int32_t* tile_cell0, const int32_t* n_tiles, int B, int T, int U1,
-                                   int V, int H, int blank, float* lse, float* lp_blank, float* lp_label,
-                                   void* h_stash, void* stream) {
+                                   int V, int H, int blank, int tile_cap, float* lse, float* lp_blank,
+                                   float* lp_label, void* h_stash, void* stream) {
   if (!p_enc || !p_dec || !w2_bf16 || !b2_log2 || !act_lens || !label_lens || !tile_utt || !tile_cell0 ||
       !n_tiles || !lse || !lp_blank || !lp_label || !h_stash)
     return RNNT_B200_E_NULL;
@@ -722,7 +722,8 @@ extern "C" int rnnt_b200_joint_fwd(const float* p_enc, const float* p_dec, const
   p.label_lens = label_lens; p.tile_utt = tile_utt; p.tile_cell0 = tile_cell0; p.n_tiles = n_tiles;
   p.lse = lse; p.lpb = lp_blank; p.lpl = lp_label; p.h_stash = (__nv_bfloat16*)h_stash;
   p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vpad = rnnt_b200_vocab_pad(V); p.H = H; p.blank = blank;
-  p.tile_lo = 0; p.tile_hi = rnnt_b200_max_tiles(B, T, U1);
+  if (tile_cap < 1 || tile_cap > rnnt_b200_max_tiles(B, T, U1)) return RNNT_B200_E_SHAPE;
+  p.tile_lo = 0; p.tile_hi = tile_cap;
   {
     int grid = p.tile_hi < 148 * 8 ? p.tile_hi : 148 * 8;
     hidden_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p, p.tile_hi);
@@ -736,15 +737,16 @@ extern "C" int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, 
                                       const int32_t* label_lens, const int32_t* tile_utt,
                                       const int32_t* tile_cell0, const int32_t* n_tiles, const float* lse,
                                       const float* c_blank, const float* c_label, const float* scale, int B,
-                                      int T, int U1, int V, int H, int blank, int tile_lo, int tile_hi,
-                                      void* ds, void* stream) {
+                                      int T, int U1, int V, int H, int blank, int tile_cap, int tile_lo,
+                                      int tile_hi, void* ds, void* stream) {
   if (!h_stash || !w2_bf16 || !b2_log2 || !act_lens || !label_lens || !tile_utt || !tile_cell0 || !n_tiles ||
       !lse || !c_blank || !c_label || !scale || !ds)
     return RNNT_B200_E_NULL;
   if (U1 > 1 && !labels) return RNNT_B200_E_NULL;
   int rc = check_common(B, T, U1, V, H, blank);
   if (rc) return rc;
-  const int max_tiles = rnnt_b200_max_tiles(B, T, U1);
+  if (tile_cap < 1 || tile_cap > rnnt_b200_max_tiles(B, T, U1)) return RNNT_B200_E_SHAPE;
+  const int max_tiles = tile_cap;
   if (tile_lo < 0 || tile_hi < tile_lo || tile_hi > max_tiles) return RNNT_B200_E_SHAPE;
   if (((uintptr_t)h_stash & 127) || ((uintptr_t)w2_bf16 & 127) || ((uintptr_t)b2_log2 & 15) ||
       ((uintptr_t)ds & 15))

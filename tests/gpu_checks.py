@@ -90,12 +90,13 @@ def _joint_inputs(B, T, U, E, D, H, V, mode, seed):
     return enc, dec, w1, b1, w2, b2, y, tl, ul
 
 
-def fused_vs_oracle(enc, dec, w1, b1, w2, b2, y, tl, ul, grads=True):
+def fused_vs_oracle(enc, dec, w1, b1, w2, b2, y, tl, ul, grads=True, host_lens=False):
     """Boundary 2 vs (i) the float64 oracle fed bf16-rounded h and W2 (kernel error only) and
     (ii) the full-precision float64 oracle (kernel + quantisation error)."""
     names = ["enc", "dec", "w1", "b1", "w2", "b2"]
     leaves = [t.to(DEV).requires_grad_(grads) for t in (enc, dec, w1, b1, w2, b2)]
-    loss = R.joint_rnnt_loss(*leaves, y.to(DEV), tl.to(DEV), ul.to(DEV), reduction="none")
+    loss = R.joint_rnnt_loss(*leaves, y.to(DEV), tl.to(DEV), ul.to(DEV), reduction="none",
+                             host_lens=(tl, ul) if host_lens else None)
     if grads:
         loss.sum().backward()
     torch.cuda.synchronize()
@@ -120,8 +121,8 @@ def fused_golden(name, grads=True):
                            t("act_lens"), t("label_lens"), grads)
 
 
-def fused_synth(B, T, U, E, D, H, V, mode="ragged", seed=2019, grads=True):
-    return fused_vs_oracle(*_joint_inputs(B, T, U, E, D, H, V, mode, seed), grads=grads)
+def fused_synth(B, T, U, E, D, H, V, mode="ragged", seed=2019, grads=True, host_lens=False):
+    return fused_vs_oracle(*_joint_inputs(B, T, U, E, D, H, V, mode, seed), grads=grads, host_lens=host_lens)
 
 
 def fused_matches_dropin(B, T, U, E, D, H, V, mode="ragged", seed=7):

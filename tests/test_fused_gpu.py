@@ -44,6 +44,12 @@ def test_synthetic(dims, mode):
     _assert_fused(G.fused_synth(*dims, mode=mode))
 
 
+def test_host_length_hint_gives_same_result():
+    # exact tile count from host lengths (no padded tiles, odd pair tails) vs the padded bound
+    _assert_fused(G.fused_synth(3, 23, 9, 64, 64, 128, 300, mode="edge", host_lens=True))
+    _assert_fused(G.fused_synth(2, 20, 8, 320, 320, 512, 4232, mode="ragged", host_lens=True))
+
+
 def test_fused_agrees_with_dropin_at_scale():
     # no CPU oracle at this size: consistency between the two CUDA boundaries
     m = G.fused_matches_dropin(4, 120, 40, 320, 320, 512, 4232)

@@ -48,7 +48,7 @@ def test_c_abi_rejects_bad_arguments_without_launching():
     assert L.rnnt_b200_logits_to_planes(one, one, one, one, 1, 1, 1, 4, 7, one, one, one, None) == -3
     assert L.rnnt_b200_lattice(one, one, one, one, 1, 4, 2000, one, one, one, one, one, None, None) == -2
     assert L.rnnt_b200_joint_fwd(one, one, one, one, one, one, one, one, one, one,
-                                 1, 4, 2, 10, 100, 0, one, one, one, one, None) == -2   # H % 64
+                                 1, 4, 2, 10, 100, 0, 1, one, one, one, one, None) == -2   # H % 64
 
 
 def test_rnntloss_is_dropin_constructible_and_validates():
