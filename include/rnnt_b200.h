@@ -114,6 +114,12 @@ int rnnt_b200_pack_vocab(const float* w2, const float* b2, int V, int H,
  * for valid cells so that dS^T . h_ext yields d b2 in its last column block. */
 int rnnt_b200_h_pitch(int H);
 
+/* Row pitch (elements) of the staged bf16 logit gradient dS: V rounded up to 64 (128-byte rows;
+ * capped at Vpad), e.g. 4288 for V=4232. The last vocabulary tile of the GEMM is issued that
+ * narrow (UMMA N = 192 instead of 256), so no tensor-core work is spent on the rest of the
+ * Vpad padding. Columns V..pitch-1 are written as zeros. */
+int rnnt_b200_ds_pitch(int V);
+
 /* Fused forward: tcgen05/TMEM GEMM  tanh(P_enc[t]+P_dec[u]) . W2^T  with an online
  * log-sum-exp epilogue; writes lse / lp_blank / lp_label planes only.
  * h_stash: bf16 workspace (max_tiles*128, H+8), 128-byte aligned: written first with
@@ -133,7 +139,7 @@ int rnnt_b200_joint_fwd(const float* p_enc, const float* p_dec,
 
 /* Fused backward, stage 1: recompute logits tiles from h_stash on the tensor cores and
  * emit dS = scale_b*(softmax*(c_blank+c_label) - onehots) as bf16 for tiles
- * [tile_lo, tile_hi) into ds (rows (tile_hi-tile_lo)*128, pitch Vpad). Rows of
+ * [tile_lo, tile_hi) into ds (rows (tile_hi-tile_lo)*128, pitch rnnt_b200_ds_pitch(V)). Rows of
  * tiles >= n_tiles[0] and rows past an utterance's last cell are written as zeros.
  * ds must be 128-byte aligned. */
 int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, const float* b2_log2,

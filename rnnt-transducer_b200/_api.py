@@ -279,14 +279,14 @@ class _JointLossFn(torch.autograd.Function):
         if need_grad:
             ctx.save_for_backward(labels, act_lens, label_lens, tile_utt, tile_cell0, n_tiles, w2q, b2l,
                                   lse, cb, cl, h_stash)
-        ctx.dims = (B, T, U1, V, H, Vpad, max_tiles, blank)
+        ctx.dims = (B, T, U1, V, H, L.rnnt_b200_ds_pitch(V), max_tiles, blank)
         return loss
 
     @staticmethod
     def backward(ctx, grad_out):
         (labels, act_lens, label_lens, tile_utt, tile_cell0, n_tiles, w2q, b2l, lse, cb, cl,
          h_stash) = ctx.saved_tensors
-        B, T, U1, V, H, Vpad, max_tiles, blank = ctx.dims
+        B, T, U1, V, H, Vds, max_tiles, blank = ctx.dims
         L = _lib.lib()
         dev = lse.device
         with torch.cuda.device(dev):
@@ -294,12 +294,13 @@ class _JointLossFn(torch.autograd.Function):
             scale = grad_out.to(torch.float32).contiguous()
             dpe = torch.zeros(B, T, H, dtype=torch.float32, device=dev)
             dpd = torch.zeros(B, U1, H, dtype=torch.float32, device=dev)
-            dw2x = torch.zeros(Vpad, H + 8, dtype=torch.float32, device=dev)  # [dW2 | db2 | 0..]
-            chunk = max(2, min(max_tiles, _DS_BUDGET_BYTES // (128 * Vpad * 2)))
+            dw2x = torch.zeros(Vds, H + 8, dtype=torch.float32, device=dev)  # [dW2 | db2 | 0..]
+            chunk = max(2, min(max_tiles, _DS_BUDGET_BYTES // (128 * Vds * 2)))
             nchunk = -(-max_tiles // chunk)
             chunk = -(-max_tiles // nchunk)          # balanced chunks,
             chunk += chunk & 1                       # whole CTA-pair tiles
-            ds = torch.empty(chunk * 128, Vpad, dtype=torch.bfloat16, device=dev)
+            ds = torch.empty(chunk * 128, Vds, dtype=torch.bfloat16, device=dev)
+            w2v = w2q[:Vds]                          # rows Vds..Vpad of the pack are padding only
             for lo in range(0, max_tiles, chunk):
                 hi = min(max_tiles, lo + chunk)
                 rows = (hi - lo) * 128
@@ -311,13 +312,13 @@ class _JointLossFn(torch.autograd.Function):
                                                     _ptr(dsc), st)
                 # two plain library GEMMs on the staged bf16 gradient tile (fp32 accumulate/out)
                 with _region("lib_gemm_dh"):
-                    dh = torch.mm(dsc, w2q)                                            # (rows, H) bf16
+                    dh = torch.mm(dsc, w2v)                                            # (rows, H) bf16
                 with _region("lib_gemm_dw2"):
                     # K = rows is huge and M x N = Vpad x (H+8) small: split K two ways (batched GEMM;
                     # measured best for N = H+8, profiles/r01_notes.md). Column H of h_ext is 1 for
                     # valid cells, so column H of the product is db2.
                     hc = h_stash[lo * 128: hi * 128]
-                    dw2x += torch.bmm(dsc.view(2, rows // 2, Vpad).transpose(1, 2),
+                    dw2x += torch.bmm(dsc.view(2, rows // 2, Vds).transpose(1, 2),
                                       hc.view(2, rows // 2, H + 8), out_dtype=torch.float32).sum(0)
                 _call("dh_reduce", L.rnnt_b200_dh_reduce, _ptr(dh), _ptr(h_stash), _ptr(act_lens), _ptr(label_lens),
                       B, T, U1, H, lo, hi, 1.0, _ptr(dpe), _ptr(dpd), st)

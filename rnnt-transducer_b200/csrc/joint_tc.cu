@@ -77,7 +77,7 @@ struct JointParams {
   const float* cl;
   const float* scale;
   __nv_bfloat16* ds;
-  int B, T, U1, V, Vpad, H, blank;
+  int B, T, U1, V, Vpad, Vds, H, blank;  // Vpad: rows of the packed W2 (NV*BN); Vds: dS pitch = V rounded up to 16
   int tile_lo, tile_hi;  // tile range of this launch
   int stages;
   long long* trace;  // RNNT_B200_TRACE: clock64 stamps of cluster 0 / rank 0 (debug only)
@@ -131,6 +131,9 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
   const int KB = p.H / kKBlock;      // A K-blocks of 64
   const int KS = p.H / kBK;          // W2 stages per vocabulary tile (K steps of 64)
   const int NV = p.Vpad / BN;        // vocabulary tiles
+  // The last vocabulary tile is issued with UMMA N = n_last (multiple of 16) instead of BN:
+  // V=4232 -> 16 tiles of 256 + one of 144 (4240 columns instead of 4352, -2.6% MMA work).
+  const int n_last = p.Vds - (NV - 1) * BN;
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + KB * kABlockBytes;
   constexpr int kStageBytes = (BN / 2) * 128;  // this CTA's half of a W2 stage: BN/2 rows x 64 k
@@ -225,10 +228,13 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         // issued before the wait on its accumulators.
         const uint32_t taddr0 = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN + half * HALF;
         float zz[2][32];
-        if (!(p.debug & 1)) tmem_ld_32x32(taddr0, zz[0]);
+        // columns of this tile that belong to this warp's half (the last tile is narrower)
+        const int ncol = min(HALF, max(0, ((vt == NV - 1) ? n_last : BN) - half * HALF));
+        const int nch = (p.debug & 1) ? 0 : (ncol + 31) >> 5;
+        if (nch > 0) tmem_ld_32x32(taddr0, zz[0]);
 #pragma unroll
         for (int c = 0; c < NCH; ++c) {
-          if (p.debug & 1) break;
+          if (c >= nch) break;
           float* z = zz[c & 1];
           const int col0 = vt * BN + half * HALF + c * 32;
           const float4* b4 = reinterpret_cast<const float4*>(p.b2l + col0);
@@ -236,13 +242,18 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
 #pragma unroll
           for (int j = 0; j < 8; ++j) bb[j] = __ldg(b4 + j);
           tmem_ld_wait();
-          if (c + 1 < NCH) tmem_ld_32x32(taddr0 + (c + 1) * 32, zz[(c + 1) & 1]);
+          if (c + 1 < nch) tmem_ld_32x32(taddr0 + (c + 1) * 32, zz[(c + 1) & 1]);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             z[4 * j + 0] = fmaf(z[4 * j + 0], RNNT_LOG2E, bb[j].x);
             z[4 * j + 1] = fmaf(z[4 * j + 1], RNNT_LOG2E, bb[j].y);
             z[4 * j + 2] = fmaf(z[4 * j + 2], RNNT_LOG2E, bb[j].z);
             z[4 * j + 3] = fmaf(z[4 * j + 3], RNNT_LOG2E, bb[j].w);
+          }
+          if (ncol - c * 32 < 32) {  // partial chunk of the narrow last tile: stale TMEM columns
+            const int nv = ncol - c * 32;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) z[j] = (j < nv) ? z[j] : RNNT_NEG_BIG;
           }
           if (MODE == 0) {
             float m0 = z[0], m1 = z[1], m2 = z[2], m3 = z[3];  // four independent max chains
@@ -334,8 +345,8 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       const int first_dead = max(n_tiles, p.tile_lo);
       const int epi_tid = threadIdx.x;  // 0..255
       for (int tile = first_dead + blockIdx.x; tile < p.tile_hi; tile += gridDim.x) {
-        uint4* dst = reinterpret_cast<uint4*>(p.ds + (size_t)(tile - p.tile_lo) * RNNT_TILE_M * p.Vpad);
-        const size_t n16 = (size_t)RNNT_TILE_M * p.Vpad / 8;
+        uint4* dst = reinterpret_cast<uint4*>(p.ds + (size_t)(tile - p.tile_lo) * RNNT_TILE_M * p.Vds);
+        const size_t n16 = (size_t)RNNT_TILE_M * p.Vds / 8;
         for (size_t i = epi_tid; i < n16; i += kEpiWarps * 32) dst[i] = make_uint4(0, 0, 0, 0);
       }
     }
@@ -358,7 +369,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
             if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[stage], 2 * kStageBytes);
             else mbar_arrive_cluster(full);
             tma_load_2d_pair(smem_b + stage * kStageBytes, &map_w2, full, ks * kBK,
-                             vt * BN + (int)rank * (BN / 2));
+                             vt * BN + (int)rank * (((vt == NV - 1) ? n_last : BN) / 2));
             if (p.trace && blockIdx.x == 0 && tr_n < 4096) {
               long long* t = p.trace + 3 * 4096;
               t[3 * tr_n + 0] = tr0; t[3 * tr_n + 1] = tr1; t[3 * tr_n + 2] = clock64();
@@ -391,19 +402,22 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
     // The whole warp walks the loop with warp-uniform control flow (cheap uniform-datapath
     // descriptor arithmetic, no single-lane waterfall code); one elected lane issues.
     if (rank == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(2 * RNNT_TILE_M, BN);
+      constexpr uint32_t idesc_full = umma_idesc_bf16(2 * RNNT_TILE_M, BN);
+      const uint32_t idesc_last = umma_idesc_bf16(2 * RNNT_TILE_M, n_last);
       uint32_t stage = 0, phase = 0, acc_it = 0;
       int it = 0, tr_n = 0;
       const uint32_t a0 = smem_u32(smem_a), b0 = smem_u32(smem_b);
       const bool tracing = p.trace != nullptr && blockIdx.x == 0;
       for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
-        for (int vt = 0; vt < NV; ++vt, ++acc_it) {
+        for (int vi = 0; vi < NV; ++vi, ++acc_it) {
+          const int vt = (vi + cid) % NV;  // same rotated order as the producer and the epilogue
+          const uint32_t idesc = (vt == NV - 1) ? idesc_last : idesc_full;
           const uint32_t buf = acc_it & 1;
           mbar_wait(&ctl->acc_empty[buf], ((acc_it >> 1) & 1) ^ 1);
           tc_fence_after();
           const uint32_t tmem_d = tmem_base + buf * BN;
           for (int ks = 0; ks < KS; ++ks) {
-            if (vt == 0) mbar_wait(&ctl->a_full[ks], it & 1);
+            if (vi == 0) mbar_wait(&ctl->a_full[ks], it & 1);
             const long long tr0 = tracing ? clock64() : 0;
             mbar_wait(&ctl->b_full[stage], phase);
             const long long tr1 = tracing ? clock64() : 0;
@@ -417,7 +431,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
                   umma_bf16_ss_pair(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | k) != 0);
               }
               umma_commit_pair_mc(&ctl->b_empty[stage], 3);
-              if (vt == NV - 1) umma_commit_pair_mc(&ctl->a_empty[ks], 3);
+              if (vi == NV - 1) umma_commit_pair_mc(&ctl->a_empty[ks], 3);
               if (ks == KS - 1) umma_commit_pair_mc(&ctl->acc_full[buf], 3);
             }
             __syncwarp();
@@ -680,7 +694,7 @@ int dispatch_joint(JointParams& p, const void* w2q, const void* h_stash, int max
   if (rc) return rc;
   CUtensorMap md = mw;
   if (MODE == 1) {  // dS chunk (rows x Vpad): 32 x 32 store boxes out of 64-byte-swizzled staging tiles
-    rc = make_map_bf16(&md, p.ds, (uint64_t)(p.tile_hi - p.tile_lo) * RNNT_TILE_M, p.Vpad, p.Vpad, 32, 32,
+    rc = make_map_bf16(&md, p.ds, (uint64_t)(p.tile_hi - p.tile_lo) * RNNT_TILE_M, p.Vds, p.Vds, 32, 32,
                        CU_TENSOR_MAP_SWIZZLE_64B);
     if (rc) return rc;
   }
@@ -721,7 +735,7 @@ extern "C" int rnnt_b200_joint_fwd(const float* p_enc, const float* p_dec, const
   p.pe = p_enc; p.pd = p_dec; p.b2l = b2_log2; p.labels = labels; p.act_lens = act_lens;
   p.label_lens = label_lens; p.tile_utt = tile_utt; p.tile_cell0 = tile_cell0; p.n_tiles = n_tiles;
   p.lse = lse; p.lpb = lp_blank; p.lpl = lp_label; p.h_stash = (__nv_bfloat16*)h_stash;
-  p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vpad = rnnt_b200_vocab_pad(V); p.H = H; p.blank = blank;
+  p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vpad = rnnt_b200_vocab_pad(V); p.Vds = rnnt_b200_ds_pitch(V); p.H = H; p.blank = blank;
   if (tile_cap < 1 || tile_cap > rnnt_b200_max_tiles(B, T, U1)) return RNNT_B200_E_SHAPE;
   p.tile_lo = 0; p.tile_hi = tile_cap;
   {
@@ -757,7 +771,7 @@ extern "C" int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, 
   p.tile_utt = tile_utt; p.tile_cell0 = tile_cell0; p.n_tiles = n_tiles;
   p.lse = const_cast<float*>(lse); p.cb = c_blank; p.cl = c_label; p.scale = scale;
   p.ds = (__nv_bfloat16*)ds;
-  p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vpad = rnnt_b200_vocab_pad(V); p.H = H; p.blank = blank;
+  p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vpad = rnnt_b200_vocab_pad(V); p.Vds = rnnt_b200_ds_pitch(V); p.H = H; p.blank = blank;
   p.tile_lo = tile_lo; p.tile_hi = tile_hi;
   return dispatch_joint<1>(p, w2_bf16, h_stash, max_tiles, (cudaStream_t)stream);
 }

@@ -6,7 +6,7 @@
 // (T_b-1,U_b), concurrently on different SMs. Thread u owns lattice column u; a
 // wavefront step d handles the cells t+u = d. The planes are stored anti-diagonal
 // major (rnnt_b200.h), so each step reads one contiguous row of lp_blank/lp_label
-// (coalesced, prefetched PF steps ahead) and writes one contiguous row of alpha/beta.
+// (coalesced, requested RING-1 steps ahead with cp.async) and writes one contiguous row of alpha/beta.
 // Neighbour exchange goes through a double-buffered shared-memory diagonal.
 // Accumulators are float64: with V=4232 the per-utterance log-likelihood is ~1e3 nats
 // and fp32 alpha/beta miss the 1e-4 gradient tolerance.
@@ -14,7 +14,22 @@
 
 namespace {
 
-constexpr int PF = 4;  // prefetch depth (wavefront steps)
+constexpr int RING = 16;  // diagonals in flight (cp.async ring in shared memory)
+
+// 4-byte asynchronous global->shared copies: the two log-prob rows of diagonal d+RING-1 are
+// requested while diagonal d is computed, so the L2/HBM latency (which bounded the PF=4
+// register-prefetch version: ~1.1 us per wavefront step, long_scoreboard) is covered by
+// RING-1 steps of work. Every thread reads back only the words it copied itself.
+__device__ __forceinline__ void cp_async4(float* dst_smem, const float* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)),
+               "l"(src)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
 
 __global__ void __launch_bounds__(1024, 1)
 lattice_kernel(const float* __restrict__ lp_blank, const float* __restrict__ lp_label,
@@ -22,8 +37,10 @@ lattice_kernel(const float* __restrict__ lp_blank, const float* __restrict__ lp_
                int T, int U1, double* __restrict__ alpha, double* __restrict__ beta,
                double* __restrict__ ll_alpha, double* __restrict__ ll_beta) {
   __shared__ double xch[2][1024 + 2];
+  extern __shared__ float ring[];  // [RING][2][blockDim.x]
   const int b = blockIdx.x;
   const int u = threadIdx.x;
+  const int nthr = blockDim.x;
   const int Tb = clamp_int(act_lens[b], 1, T);
   const int Ub = clamp_int(label_lens[b], 0, U1 - 1);
   const int nd = Tb + Ub;  // diagonals 0 .. nd-1
@@ -32,90 +49,84 @@ lattice_kernel(const float* __restrict__ lp_blank, const float* __restrict__ lp_
   const float* pl = lp_label + base;
   const bool col_ok = (u <= Ub);
   const double NEG = -INFINITY;
-  float rb[PF], rl[PF];
+  float* my_ring = ring + u;
 
   xch[0][u + 1] = NEG;
   xch[1][u + 1] = NEG;
   if (u == 0) { xch[0][0] = NEG; xch[1][0] = NEG; xch[0][blockDim.x + 1] = NEG; xch[1][blockDim.x + 1] = NEG; }
   __syncthreads();
 
-  if (blockIdx.y == 0) {
+  // request the rows of wavefront step s (alpha: diagonal s; beta: diagonal nd-1-s) into slot s%RING
+  const bool is_beta = blockIdx.y != 0;
+  auto request = [&](int s) {
+    if (s < nd && col_ok) {
+      const int d = is_beta ? nd - 1 - s : s;
+      const int t = d - u;
+      if (t >= 0 && t < Tb) {  // cells outside the valid window are never written by the producer
+        float* slot = my_ring + ((s & (RING - 1)) * 2) * nthr;
+        cp_async4(slot, pb + (size_t)d * U1 + u);
+        cp_async4(slot + nthr, pl + (size_t)d * U1 + u);
+      }
+    }
+    cp_async_commit();  // one group per step, empty or not: keeps wait_group counting uniform
+  };
+#pragma unroll 1
+  for (int s = 0; s < RING - 1; ++s) request(s);
+
+  if (!is_beta) {
     // ---------------- alpha ----------------
     double* out = alpha + base;
-#pragma unroll
-    for (int k = 0; k < PF; ++k) {
-      rb[k] = 0.f; rl[k] = 0.f;
-      if (k < nd && col_ok) { rb[k] = pb[(size_t)k * U1 + u]; rl[k] = pl[(size_t)k * U1 + u]; }
-    }
     double up = NEG;  // alpha[t-1,u] + lp_blank[t-1,u]
-    for (int d0 = 0; d0 < nd; d0 += PF) {
-#pragma unroll
-      for (int k = 0; k < PF; ++k) {
-        const int d = d0 + k;
-        if (d < nd) {  // uniform across the block
-          const int t = d - u;
-          const bool valid = col_ok && t >= 0 && t < Tb;
-          const double left = xch[d & 1][u];  // slot u holds the message of thread u-1
-          double a = (d == 0 && u == 0) ? 0.0 : log_add_exp(up, left);
-          const float lpb = rb[k], lpl = rl[k];
-          if (d + PF < nd && col_ok) {
-            rb[k] = pb[(size_t)(d + PF) * U1 + u];
-            rl[k] = pl[(size_t)(d + PF) * U1 + u];
-          }
-          double right = NEG;
-          if (valid) {
-            out[(size_t)d * U1 + u] = a;
-            up = a + (double)lpb;
-            if (u < Ub) right = a + (double)lpl;
-          } else {
-            up = NEG;
-          }
-          xch[(d + 1) & 1][u + 1] = right;
-          __syncthreads();
-        }
+#pragma unroll 1
+    for (int d = 0; d < nd; ++d) {
+      request(d + RING - 1);
+      cp_async_wait<RING - 1>();  // the group of step d has landed
+      const float* slot = my_ring + ((d & (RING - 1)) * 2) * nthr;
+      const int t = d - u;
+      const bool valid = col_ok && t >= 0 && t < Tb;
+      const double left = xch[d & 1][u];  // slot u holds the message of thread u-1
+      const double a = (d == 0 && u == 0) ? 0.0 : log_add_exp(up, left);
+      double right = NEG;
+      if (valid) {
+        const float lpb = slot[0], lpl = slot[nthr];
+        out[(size_t)d * U1 + u] = a;
+        up = a + (double)lpb;
+        if (u < Ub) right = a + (double)lpl;
+      } else {
+        up = NEG;
       }
+      xch[(d + 1) & 1][u + 1] = right;
+      __syncthreads();
     }
     if (u == Ub) ll_alpha[b] = up;  // alpha[Tb-1,Ub] + lp_blank[Tb-1,Ub]
   } else {
     // ---------------- beta ----------------
     double* out = beta + base;
-#pragma unroll
-    for (int k = 0; k < PF; ++k) {
-      const int d = nd - 1 - k;
-      rb[k] = 0.f; rl[k] = 0.f;
-      if (d >= 0 && col_ok) { rb[k] = pb[(size_t)d * U1 + u]; rl[k] = pl[(size_t)d * U1 + u]; }
-    }
     double own = NEG;  // beta[t+1,u]
-    for (int s0 = 0; s0 < nd; s0 += PF) {
-#pragma unroll
-      for (int k = 0; k < PF; ++k) {
-        const int s = s0 + k;  // step counter; diagonal d = nd-1-s
-        if (s < nd) {
-          const int d = nd - 1 - s;
-          const int t = d - u;
-          const bool valid = col_ok && t >= 0 && t < Tb;
-          const double right = xch[s & 1][u + 2];  // message of thread u+1 (beta[t,u+1])
-          const float lpb = rb[k], lpl = rl[k];
-          if (d - PF >= 0 && col_ok) {
-            rb[k] = pb[(size_t)(d - PF) * U1 + u];
-            rl[k] = pl[(size_t)(d - PF) * U1 + u];
-          }
-          double be = NEG;
-          if (valid) {
-            if (t == Tb - 1 && u == Ub) {
-              be = (double)lpb;
-            } else {
-              const double viab = own + (double)lpb;
-              const double vial = (u < Ub) ? right + (double)lpl : NEG;
-              be = log_add_exp(viab, vial);
-            }
-            out[(size_t)d * U1 + u] = be;
-          }
-          own = be;
-          xch[(s + 1) & 1][u + 1] = be;
-          __syncthreads();
+#pragma unroll 1
+    for (int s = 0; s < nd; ++s) {  // step counter; diagonal d = nd-1-s
+      request(s + RING - 1);
+      cp_async_wait<RING - 1>();
+      const float* slot = my_ring + ((s & (RING - 1)) * 2) * nthr;
+      const int d = nd - 1 - s;
+      const int t = d - u;
+      const bool valid = col_ok && t >= 0 && t < Tb;
+      const double right = xch[s & 1][u + 2];  // message of thread u+1 (beta[t,u+1])
+      double be = NEG;
+      if (valid) {
+        const float lpb = slot[0], lpl = slot[nthr];
+        if (t == Tb - 1 && u == Ub) {
+          be = (double)lpb;
+        } else {
+          const double viab = own + (double)lpb;
+          const double vial = (u < Ub) ? right + (double)lpl : NEG;
+          be = log_add_exp(viab, vial);
         }
+        out[(size_t)d * U1 + u] = be;
       }
+      own = be;
+      xch[(s + 1) & 1][u + 1] = be;
+      __syncthreads();
     }
     if (u == 0) ll_beta[b] = own;  // beta[0,0]
   }
@@ -177,8 +188,14 @@ extern "C" int rnnt_b200_lattice(const float* lp_blank, const float* lp_label,
   double* ll_a = alpha + rnnt_b200_plane_elems(B, T, U1);
   double* ll_b = beta + rnnt_b200_plane_elems(B, T, U1);
   const int threads = ((U1 + 31) / 32) * 32;
-  lattice_kernel<<<dim3(B, 2), threads, 0, st>>>(lp_blank, lp_label, act_lens, label_lens, T, U1,
-                                                 alpha, beta, ll_a, ll_b);
+  const size_t ring_bytes = (size_t)RING * 2 * threads * sizeof(float);  // <= 128 KB at 1024 threads
+  if (ring_bytes > 32 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(lattice_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)ring_bytes);
+    if (e != cudaSuccess) return (int)e;
+  }
+  lattice_kernel<<<dim3(B, 2), threads, ring_bytes, st>>>(lp_blank, lp_label, act_lens, label_lens, T, U1,
+                                                          alpha, beta, ll_a, ll_b);
   RNNT_CUDA_RETURN_IF_ERROR();
   const long long n = (long long)(T + U1 - 1) * U1;
   int gx = (int)((n + 255) / 256);

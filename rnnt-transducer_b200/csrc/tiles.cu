@@ -2,6 +2,7 @@
 // and the dh -> (dP_enc, dP_dec) reduction (the backward of the broadcast add that
 // replaces the reference's repeat+cat, /root/reference rnnt/model.py:26-31).
 #include <cuda_bf16.h>
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace {
@@ -137,6 +138,19 @@ extern "C" int rnnt_b200_vocab_pad(int V) {
   return ((V + bn - 1) / bn) * bn;
 }
 extern "C" int rnnt_b200_h_pitch(int H) { return H + 8; }
+extern "C" int rnnt_b200_ds_pitch(int V) {
+  // The UMMA N granularity is 16, but a pitch that is not a multiple of 64 elements (128 bytes)
+  // slows the library GEMMs that consume dS by more than the narrower tile saves (measured:
+  // profiles/r01_notes.md), so the last vocabulary tile is cut at the next multiple of 64.
+  int gran = 64;
+  if (const char* g = getenv("RNNT_B200_VGRAN")) {  // timing experiments only: 16, 32, 64, ...
+    const int v = atoi(g);
+    if (v >= 16 && (v & (v - 1)) == 0) gran = v;
+  }
+  const int v16 = (V + gran - 1) & ~(gran - 1);
+  const int pad = rnnt_b200_vocab_pad(V);
+  return v16 < pad ? v16 : pad;
+}
 
 extern "C" int rnnt_b200_pack_vocab(const float* w2, const float* b2, int V, int H, void* w2_bf16,
                                     float* b2_log2, void* stream) {

@@ -39,6 +39,8 @@ def test_golden(name):
     ((4, 30, 12, 128, 128, 128, 49), "edge"),       # TIMIT joint dims (config/timit.yaml:26-37)
     ((1, 1, 0, 64, 64, 64, 300), "full"),           # single cell
     ((2, 17, 130, 64, 64, 256, 1000), "ragged"),    # U+1 > 128: a tile spans < 1 lattice row
+    ((2, 9, 4, 64, 64, 64, 270), "ragged"),         # last vocabulary tile N = 64: one epilogue half idle
+    ((2, 9, 4, 64, 64, 128, 460), "full"),          # last tile N = 192: half 1 sweeps 2 of its 4 chunks
 ])
 def test_synthetic(dims, mode):
     _assert_fused(G.fused_synth(*dims, mode=mode))
