@@ -33,6 +33,7 @@
 #include <cuda_bf16.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <type_traits>
 #include "common.cuh"
 #include "sm100_ptx.cuh"
 
@@ -53,9 +54,9 @@ struct SharedCtl {
   uint64_t b_full[kMaxStages], b_empty[kMaxStages];
   uint64_t acc_full[2], acc_empty[2];
   uint32_t tmem_base;
-  uint32_t pad;
-  float4 red[RNNT_TILE_M];
+  uint32_t pad[3];
 };
+static_assert(sizeof(SharedCtl) % 16 == 0, "the regions behind ctl hold float4");
 
 struct JointParams {
   const float* pe;
@@ -77,16 +78,26 @@ struct JointParams {
   const float* cl;
   const float* scale;
   __nv_bfloat16* ds;
+  float* db2;  // (Vds) column sums of dS, accumulated with red.global.add
   int B, T, U1, V, Vpad, Vds, H, blank;  // Vpad: rows of the packed W2 (NV*BN); Vds: dS pitch = V rounded up to 16
   int tile_lo, tile_hi;  // tile range of this launch
   int stages;
   long long* trace;  // RNNT_B200_TRACE: clock64 stamps of cluster 0 / rank 0 (debug only)
+  int bias_smem;  // the b2 table fits in shared memory next to the pipeline buffers
   int debug;  // RNNT_B200_DEBUG bitmask (timing experiments only): 1 skip epilogue math, 2 skip producer math, 4 skip MMA issue
 };
 
-__host__ __device__ inline int smem_bytes_for(int H, int BN, int stages, int mode) {
-  return (H / kKBlock) * kABlockBytes + stages * (BN / 2) * 128 +
-         (mode == 1 ? kEpiWarps * 2048 : 0) + (int)sizeof(SharedCtl);
+// Shared memory of joint_kernel: [h tile | W2 ring | MODE 1: dS staging, 2 x 2 KB per epilogue warp |
+// ctl | MODE 0: red, the cross-half LSE merge | bias: the whole b2*log2(e) table (Vpad floats)].
+constexpr int kDsStageBytes = kEpiWarps * 2 * 2048;
+constexpr int kRedBytes = RNNT_TILE_M * 16;
+// A pipeline stage of the W2 ring covers ksub(H) consecutive 64-wide K blocks (two when H allows:
+// one mbarrier round trip, one commit and one issue-loop iteration per 8 MMAs instead of per 4 --
+// the single-block version spent ~620 clk per stage in the issue loop against 512 clk of MMA).
+__host__ __device__ inline int ksub_for(int H) { return (H % 128 == 0) ? 2 : 1; }
+__host__ __device__ inline int smem_bytes_for(int H, int BN, int stages, int mode, int Vpad) {
+  return (H / kKBlock) * kABlockBytes + stages * ksub_for(H) * (BN / 2) * 128 +
+         (mode == 1 ? kDsStageBytes : kRedBytes) + (int)sizeof(SharedCtl) + Vpad * 4;
 }
 
 __device__ __forceinline__ float tanh_accurate(float x) {
@@ -122,23 +133,27 @@ __device__ __forceinline__ RowCoord locate_row(const JointParams& p, int tile, i
 // ---------------------------------------------------------------------------------------
 // MODE 0 = forward (online LSE epilogue), MODE 1 = backward dS.
 // ---------------------------------------------------------------------------------------
-template <int BN, int MODE>
+template <int BN, int MODE, bool BIAS_SMEM>
 __global__ void __launch_bounds__(kThreads, 1)
 joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__ CUtensorMap map_h,
              const __grid_constant__ CUtensorMap map_ds, const JointParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];  // no static smem in this kernel: base is 1024-aligned
   if ((smem_u32(smem) & 1023u) != 0) __trap();       // the 128B-swizzle atoms need it
   const int KB = p.H / kKBlock;      // A K-blocks of 64
-  const int KS = p.H / kBK;          // W2 stages per vocabulary tile (K steps of 64)
+  const int KSUB = ksub_for(p.H);    // 64-wide K blocks per pipeline stage
+  const int KS = KB / KSUB;          // W2 stages per vocabulary tile
   const int NV = p.Vpad / BN;        // vocabulary tiles
   // The last vocabulary tile is issued with UMMA N = n_last (multiple of 16) instead of BN:
   // V=4232 -> 16 tiles of 256 + one of 144 (4240 columns instead of 4352, -2.6% MMA work).
   const int n_last = p.Vds - (NV - 1) * BN;
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + KB * kABlockBytes;
-  constexpr int kStageBytes = (BN / 2) * 128;  // this CTA's half of a W2 stage: BN/2 rows x 64 k
-  uint8_t* smem_ds = smem_b + p.stages * kStageBytes;  // MODE 1: 8 x 2 KB dS staging tiles
-  SharedCtl* ctl = reinterpret_cast<SharedCtl*>(smem_ds + (MODE == 1 ? kEpiWarps * 2048 : 0));
+  constexpr int kSlotBytes = (BN / 2) * 128;   // this CTA's half of one W2 K block: BN/2 rows x 64 k
+  const int kStageBytes = KSUB * kSlotBytes;
+  uint8_t* smem_ds = smem_b + p.stages * kStageBytes;  // MODE 1: 8 warps x 2 x 2 KB dS staging tiles
+  SharedCtl* ctl = reinterpret_cast<SharedCtl*>(smem_ds + (MODE == 1 ? kDsStageBytes : 0));
+  float4* red = reinterpret_cast<float4*>(ctl + 1);    // MODE 0 only
+  float* bias_s = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ctl + 1) + (MODE == 0 ? kRedBytes : 0));
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -168,6 +183,11 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
     }
     fence_barrier_init();
   }
+  // the bias table lives in shared memory for the whole kernel: the epilogue reads it with
+  // broadcast LDS.128 (a global/L1 load per chunk stalled the epilogue: ncu long_scoreboard 17 %)
+  if (BIAS_SMEM)
+    for (int i = threadIdx.x; i < p.Vpad / 4; i += kThreads)
+      reinterpret_cast<float4*>(bias_s)[i] = __ldg(reinterpret_cast<const float4*>(p.b2l) + i);
   __syncwarp();
   cluster_sync_all();  // barrier inits visible to the peer before any remote arrive / multicast commit
   if (warp == 9) {
@@ -182,12 +202,13 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
   if (warp < kEpiWarps) {
     // =========================== EPILOGUE ===========================
     const int q = warp & 3, half = warp >> 2;
-    uint8_t* stage_w = smem_ds + warp * 2048;  // MODE 1: per-warp dS staging tile
+    uint8_t* stage_w = smem_ds + warp * 4096;  // MODE 1: this warp's two dS staging tiles
     (void)stage_w;
     const int row = q * 32 + lane;
     constexpr int HALF = BN / 2;
-    constexpr int NCH = HALF / 32;
-    uint32_t acc_it = 0;
+    constexpr int NCH = HALF / 16;  // 16-column chunks per half tile
+    uint32_t acc_it = 0, st_it = 0;
+    (void)st_it;
     int it = 0;
     for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
       const int tile = p.tile_lo + 2 * pt + (int)rank;
@@ -203,16 +224,15 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       // forward state
       float m = -INFINITY, s = 0.f, zb = 0.f, zl = 0.f;
       // backward per-row constants
-      float nlse2 = 0.f, c0 = 0.f, cbs = 0.f, cls = 0.f;
-      if (MODE == 1) {
-        nlse2 = RNNT_NEG_BIG;  // invalid rows: exp2(z + nlse2) == 0 exactly
-        if (rc.valid) {
-          const float sc = p.scale[rc.b];
-          cbs = p.cb[pidx] * sc;
-          cls = (rc.u < rc.Ub) ? p.cl[pidx] * sc : 0.f;
-          c0 = cbs + cls;
-          nlse2 = -p.lse[pidx] * RNNT_LOG2E;
-        }
+      // dS = exp2(z + nl) - onehots with nl = log2(scale*(c_blank+c_label)) - lse*log2(e): the
+      // occupation factor rides in the exponent (one MUFU per logit, no multiply)
+      float nl = RNNT_NEG_BIG, cbs = 0.f, cls = 0.f;  // invalid rows: exp2(z + nl) == 0 exactly
+      if (MODE == 1 && rc.valid) {
+        const float sc = p.scale[rc.b];
+        cbs = p.cb[pidx] * sc;
+        cls = (rc.u < rc.Ub) ? p.cl[pidx] * sc : 0.f;
+        const float c0 = cbs + cls;
+        nl = (c0 > 0.f) ? log2f(c0) - p.lse[pidx] * RNNT_LOG2E : RNNT_NEG_BIG;
       }
       for (int vi = 0; vi < NV; ++vi, ++acc_it) {
         // pairs sweep the vocabulary in rotated order so that the 74 pairs do not all pull the
@@ -223,112 +243,178 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         mbar_wait(&ctl->acc_full[buf], (acc_it >> 1) & 1);
         const long long tr1 = p.trace ? clock64() : 0;
         tc_fence_after();
-        // Software pipeline over the NCH 32-column chunks of this warp's half tile: the TMEM load
-        // of chunk c+1 is in flight while chunk c is reduced; the bias loads of chunk c are
-        // issued before the wait on its accumulators.
+        // Software pipeline over the 16-column chunks of this warp's half tile, three register
+        // buffers deep: while chunk c goes through the MUFU-bound exponential stage, chunk c+1
+        // gets its bias FMA (+ running max) and the TMEM load of chunk c+2 is in flight, so the
+        // scheduler can fill the MUFU issue gaps with FMA-pipe work (ncu: the exponential stage
+        // and the load stalls used to run back to back, 4.5 k clk per vocabulary tile against
+        // 4.1 k clk of MMA). The accumulator buffer is handed back to the MMA warp as soon as its
+        // last TMEM load has completed, before the last two chunks are reduced.
         const uint32_t taddr0 = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN + half * HALF;
-        float zz[2][32];
-        // columns of this tile that belong to this warp's half (the last tile is narrower)
+        // columns of this tile that belong to this warp's half (the last tile is narrower; the
+        // UMMA N granularity makes every chunk a full 16 columns)
         const int ncol = min(HALF, max(0, ((vt == NV - 1) ? n_last : BN) - half * HALF));
-        const int nch = (p.debug & 1) ? 0 : (ncol + 31) >> 5;
-        if (nch > 0) tmem_ld_32x32(taddr0, zz[0]);
+        const int nch = (p.debug & 1) ? 0 : ncol >> 4;
+        const int colbase = vt * BN + half * HALF;
+        float z[3][16];
+        float cmax = -INFINITY;
+        auto release_acc = [&]() {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&ctl->acc_empty[buf]), 0));
+        };
+        // z = acc * log2(e) + b2 * log2(e)  (+ the chunk maximum in the forward pass)
+        auto bias_stage = [&](float* zc, int col) -> float {
+          const float4* b4 = reinterpret_cast<const float4*>((BIAS_SMEM ? bias_s : p.b2l) + col);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float4 bb = BIAS_SMEM ? b4[j] : __ldg(b4 + j);
+            zc[4 * j + 0] = fmaf(zc[4 * j + 0], RNNT_LOG2E, bb.x);
+            zc[4 * j + 1] = fmaf(zc[4 * j + 1], RNNT_LOG2E, bb.y);
+            zc[4 * j + 2] = fmaf(zc[4 * j + 2], RNNT_LOG2E, bb.z);
+            zc[4 * j + 3] = fmaf(zc[4 * j + 3], RNNT_LOG2E, bb.w);
+          }
+          if (MODE != 0) return 0.f;
+          float m0 = fmaxf(zc[0], zc[4]), m1 = fmaxf(zc[1], zc[5]), m2 = fmaxf(zc[2], zc[6]), m3 = fmaxf(zc[3], zc[7]);
+          m0 = fmaxf(m0, fmaxf(zc[8], zc[12])); m1 = fmaxf(m1, fmaxf(zc[9], zc[13]));
+          m2 = fmaxf(m2, fmaxf(zc[10], zc[14])); m3 = fmaxf(m3, fmaxf(zc[11], zc[15]));
+          return fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+        };
+        if (nch > 0) {
+          tmem_ld_32x16(taddr0, z[0]);
+          if (nch > 1) tmem_ld_32x16(taddr0 + 16, z[1]);
+          tmem_ld_wait();
+          if (nch <= 2) release_acc();
+          cmax = bias_stage(z[0], colbase);
+        } else {
+          release_acc();
+        }
+        // FULL: all NCH chunks present (every tile but a narrow last one) -- the pipeline
+        // conditions fold at compile time, so that the bias stage of chunk c+1 and the exponential
+        // stage of chunk c share one basic block and get interleaved by the instruction scheduler.
+        auto sweep = [&](auto full_tag) {
+        constexpr bool FULL = decltype(full_tag)::value;
+        const int nchk = FULL ? NCH : nch;
 #pragma unroll
         for (int c = 0; c < NCH; ++c) {
-          if (c >= nch) break;
-          float* z = zz[c & 1];
-          const int col0 = vt * BN + half * HALF + c * 32;
-          const float4* b4 = reinterpret_cast<const float4*>(p.b2l + col0);
-          float4 bb[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) bb[j] = __ldg(b4 + j);
-          tmem_ld_wait();
-          if (c + 1 < nch) tmem_ld_32x32(taddr0 + (c + 1) * 32, zz[(c + 1) & 1]);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            z[4 * j + 0] = fmaf(z[4 * j + 0], RNNT_LOG2E, bb[j].x);
-            z[4 * j + 1] = fmaf(z[4 * j + 1], RNNT_LOG2E, bb[j].y);
-            z[4 * j + 2] = fmaf(z[4 * j + 2], RNNT_LOG2E, bb[j].z);
-            z[4 * j + 3] = fmaf(z[4 * j + 3], RNNT_LOG2E, bb[j].w);
-          }
-          if (ncol - c * 32 < 32) {  // partial chunk of the narrow last tile: stale TMEM columns
-            const int nv = ncol - c * 32;
-#pragma unroll
-            for (int j = 0; j < 32; ++j) z[j] = (j < nv) ? z[j] : RNNT_NEG_BIG;
-          }
+          if (!FULL && c >= nchk) break;
+          const float* zc = z[c % 3];
+          const int col0 = colbase + c * 16;
+          if (c + 2 < nchk) tmem_ld_32x16(taddr0 + (c + 2) * 16, z[(c + 2) % 3]);
+          float cmax_next = -INFINITY;
+          if (c + 1 < nchk) cmax_next = bias_stage(z[(c + 1) % 3], col0 + 16);
           if (MODE == 0) {
-            float m0 = z[0], m1 = z[1], m2 = z[2], m3 = z[3];  // four independent max chains
-#pragma unroll
-            for (int j = 4; j < 32; j += 4) {
-              m0 = fmaxf(m0, z[j]); m1 = fmaxf(m1, z[j + 1]); m2 = fmaxf(m2, z[j + 2]); m3 = fmaxf(m3, z[j + 3]);
-            }
-            const float mn = fmaxf(m, fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
+            const float mn = fmaxf(m, cmax);
             float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;      // four independent sum chains
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              a0 += ex2_approx(z[j] - mn); a1 += ex2_approx(z[j + 1] - mn);
-              a2 += ex2_approx(z[j + 2] - mn); a3 += ex2_approx(z[j + 3] - mn);
+            for (int j = 0; j < 16; j += 4) {
+              a0 += ex2_approx(zc[j] - mn); a1 += ex2_approx(zc[j + 1] - mn);
+              a2 += ex2_approx(zc[j + 2] - mn); a3 += ex2_approx(zc[j + 3] - mn);
             }
             s = s * ex2_approx(m - mn) + ((a0 + a1) + (a2 + a3));
             m = mn;
-            if ((unsigned)(p.blank - col0) < 32u) {
+            if ((unsigned)(p.blank - col0) < 16u) {
               const int k = p.blank - col0;
 #pragma unroll
-              for (int j = 0; j < 32; ++j) zb = (j == k) ? z[j] : zb;
+              for (int j = 0; j < 16; ++j) zb = (j == k) ? zc[j] : zb;
             }
-            if ((unsigned)(label - col0) < 32u) {
+            if ((unsigned)(label - col0) < 16u) {
               const int k = label - col0;
 #pragma unroll
-              for (int j = 0; j < 32; ++j) zl = (j == k) ? z[j] : zl;
+              for (int j = 0; j < 16; ++j) zl = (j == k) ? zc[j] : zl;
             }
           } else {
-            float g[32];
+            float g[16];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) g[j] = ex2_approx(z[j] + nlse2) * c0;
-            if ((unsigned)(p.blank - col0) < 32u) {
+            for (int j = 0; j < 16; ++j) g[j] = ex2_approx(zc[j] + nl);  // softmax * (c_blank + c_label) * scale
+            if ((unsigned)(p.blank - col0) < 16u) {
               const int k = p.blank - col0;
 #pragma unroll
-              for (int j = 0; j < 32; ++j) g[j] -= (j == k) ? cbs : 0.f;
+              for (int j = 0; j < 16; ++j) g[j] -= (j == k) ? cbs : 0.f;
             }
-            if ((unsigned)(label - col0) < 32u) {
+            if ((unsigned)(label - col0) < 16u) {
               const int k = label - col0;
 #pragma unroll
-              for (int j = 0; j < 32; ++j) g[j] -= (j == k) ? cls : 0.f;
+              for (int j = 0; j < 16; ++j) g[j] -= (j == k) ? cls : 0.f;
             }
-            // 32 cells x 32 columns of bf16 -> this warp's 2 KB staging tile (64-byte rows,
-            // SWIZZLE_64B: conflict-free 16-byte stores) -> one TMA store (full-sector writes).
-            if (lane == 0) bulk_wait_group_read0();  // previous store has finished reading the tile
-            __syncwarp();
-            uint8_t* srow = stage_w + lane * 64;
+            // 32 cells x 32 columns of bf16 (two chunks) -> one of this warp's two 2 KB staging
+            // tiles (64-byte rows, SWIZZLE_64B: conflict-free 16-byte stores) -> one TMA store
+            // (full-sector writes). The tile written now was last read by the store before the
+            // previous one.
+            uint8_t* stile = stage_w + (st_it & 1) * 2048;
+            if ((c & 1) == 0) {
+              if (lane == 0) bulk_wait_group_read1();
+              __syncwarp();
+            }
+            uint8_t* srow = stile + lane * 64;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < 2; ++j) {
               uint4 o;
               o.x = pack_bf16x2(g[8 * j + 0], g[8 * j + 1]);
               o.y = pack_bf16x2(g[8 * j + 2], g[8 * j + 3]);
               o.z = pack_bf16x2(g[8 * j + 4], g[8 * j + 5]);
               o.w = pack_bf16x2(g[8 * j + 6], g[8 * j + 7]);
-              *reinterpret_cast<uint4*>(srow + ((j ^ ((lane >> 1) & 3)) << 4)) = o;
+              *reinterpret_cast<uint4*>(srow + (((2 * (c & 1) + j) ^ ((lane >> 1) & 3)) << 4)) = o;
             }
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0 && !dead && !(p.debug & 16)) {
-              tma_store_2d(&map_ds, stage_w, col0, (tile - p.tile_lo) * RNNT_TILE_M + q * 32);
-              bulk_commit_group();
+            if ((c & 1) == 1 || c + 1 == nchk) {
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0 && !dead && !(p.debug & 16)) {
+                tma_store_2d(&map_ds, stile, colbase + (c & ~1) * 16, (tile - p.tile_lo) * RNNT_TILE_M + q * 32);
+                bulk_commit_group();
+              }
+              ++st_it;
+              // d b2 += column sums of the staged 32 x 32 tile, on the warp-level tensor path:
+              // ones(16x32) . dS(32x32) as 2 k-steps x 4 n-blocks of m16n8k16 (every row of the
+              // product holds the sums); the staged tile is read back with ldmatrix.trans
+              // (row l of the tile = lane l's 64-byte row, 16-byte unit nb, SWIZZLE_64B).
+              // One coalesced fp32 reduction (32 columns = 128 bytes) per tile and warp.
+              if (!(p.debug & 32)) {
+                constexpr uint32_t kOnes = 0x3F803F80u;  // bf16 {1, 1}
+                const uint32_t rbase = smem_u32(stile) + lane * 64;
+                const int swz = (lane >> 1) & 3;
+                float acc[4][4];
+#pragma unroll
+                for (int nb = 0; nb < 4; ++nb) {
+                  uint32_t b0, b1, b2, b3;
+                  ldmatrix_x4_trans(rbase + ((nb ^ swz) << 4), b0, b1, b2, b3);
+                  acc[nb][0] = acc[nb][1] = acc[nb][2] = acc[nb][3] = 0.f;
+                  if (!(p.debug & 64)) {
+                  mma_m16n8k16_bf16(acc[nb], kOnes, kOnes, kOnes, kOnes, b0, b1);  // cells 0..15
+                  mma_m16n8k16_bf16(acc[nb], kOnes, kOnes, kOnes, kOnes, b2, b3);  // cells 16..31
+                  } else { acc[nb][0] = __uint_as_float(b0 ^ b2); acc[nb][1] = __uint_as_float(b1 ^ b3); }
+                }
+                // lane T holds, for every n-block, columns 8*nb + 2*(T%4) + {0,1}; lane group
+                // g = T/4 publishes n-block g/2, parity g%2 -> the 32 lanes cover the 32 columns.
+                const int g = lane >> 2;
+                const float lo = (g & 1) ? acc[0][1] : acc[0][0], l1 = (g & 1) ? acc[1][1] : acc[1][0];
+                const float l2 = (g & 1) ? acc[2][1] : acc[2][0], l3 = (g & 1) ? acc[3][1] : acc[3][0];
+                const float v = (g & 4) ? ((g & 2) ? l3 : l2) : ((g & 2) ? l1 : lo);
+                const int col = colbase + (c & ~1) * 16 + (g >> 1) * 8 + 2 * (lane & 3) + (g & 1);
+                if (!dead && col < p.Vds && !(p.debug & 128)) atomicAdd(p.db2 + col, v);
+                if ((p.debug & 128) && v == 123.456f) p.db2[0] = v;
+              }
             }
           }
+          cmax = cmax_next;
+          if (c + 2 < nchk) {
+            tmem_ld_wait();  // chunk c+2 has landed (it had this whole iteration to do so)
+            if (c + 3 == nchk) release_acc();
+          }
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&ctl->acc_empty[buf]), 0));
+        };
+        if (nch == NCH) sweep(std::true_type{});
+        else sweep(std::false_type{});
         if (p.trace && blockIdx.x == 0 && threadIdx.x == 0 && acc_it < 4096) {
           long long* t = p.trace + 6 * 4096;
           t[3 * acc_it + 0] = tr0; t[3 * acc_it + 1] = tr1; t[3 * acc_it + 2] = clock64();
         }
       }
       if (MODE == 0) {
-        if (half == 1) ctl->red[row] = make_float4(m, s, zb, zl);
+        if (half == 1) red[row] = make_float4(m, s, zb, zl);
         named_bar_sync(1, kEpiWarps * 32);
         if (half == 0 && rc.valid) {
-          const float4 o = ctl->red[row];
+          const float4 o = red[row];
           const float mn = fmaxf(m, o.x);
           const float st = s * ex2_approx(m - mn) + o.y * ex2_approx(o.x - mn);
           const float lse2 = mn + log2f(st);
@@ -368,8 +454,10 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
             const uint32_t full = mapa_u32(smem_u32(&ctl->b_full[stage]), 0);
             if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[stage], 2 * kStageBytes);
             else mbar_arrive_cluster(full);
-            tma_load_2d_pair(smem_b + stage * kStageBytes, &map_w2, full, ks * kBK,
-                             vt * BN + (int)rank * (((vt == NV - 1) ? n_last : BN) / 2));
+            const int row0 = vt * BN + (int)rank * (((vt == NV - 1) ? n_last : BN) / 2);
+            for (int sub = 0; sub < KSUB; ++sub)
+              tma_load_2d_pair(smem_b + stage * kStageBytes + sub * kSlotBytes, &map_w2, full,
+                               (ks * KSUB + sub) * kBK, row0);
             if (p.trace && blockIdx.x == 0 && tr_n < 4096) {
               long long* t = p.trace + 3 * 4096;
               t[3 * tr_n + 0] = tr0; t[3 * tr_n + 1] = tr1; t[3 * tr_n + 2] = clock64();
@@ -388,12 +476,15 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       const int tile = p.tile_lo + 2 * pt + (int)rank;
       const bool dead = tile >= n_tiles;  // odd tail: this CTA only keeps the pair's protocol going
       (void)dead;
-        for (int kb = 0; kb < KB; ++kb) {
-          mbar_wait(&ctl->a_empty[kb], (it & 1) ^ 1);
-          const uint32_t full = mapa_u32(smem_u32(&ctl->a_full[kb]), 0);
-          if (rank == 0) mbar_arrive_expect_tx(&ctl->a_full[kb], 2 * kABlockBytes);
+        for (int ks = 0; ks < KS; ++ks) {  // one barrier pair per group of KSUB K blocks
+          mbar_wait(&ctl->a_empty[ks], (it & 1) ^ 1);
+          const uint32_t full = mapa_u32(smem_u32(&ctl->a_full[ks]), 0);
+          if (rank == 0) mbar_arrive_expect_tx(&ctl->a_full[ks], 2 * KSUB * kABlockBytes);
           else mbar_arrive_cluster(full);
-          tma_load_2d_pair(smem_a + kb * kABlockBytes, &map_h, full, kb * kKBlock, tile * RNNT_TILE_M);
+          for (int sub = 0; sub < KSUB; ++sub) {
+            const int kb = ks * KSUB + sub;
+            tma_load_2d_pair(smem_a + kb * kABlockBytes, &map_h, full, kb * kKBlock, tile * RNNT_TILE_M);
+          }
         }
       }
     }
@@ -423,12 +514,14 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
             const long long tr1 = tracing ? clock64() : 0;
             tc_fence_after();
             if (elect_one_sync()) {
-              const uint64_t adesc = umma_desc_kmajor<128>(a0 + ks * kABlockBytes);
-              const uint64_t bdesc = umma_desc_kmajor<128>(b0 + stage * kStageBytes);
               if (!(p.debug & 4)) {
+                for (int sub = 0; sub < KSUB; ++sub) {
+                  const uint64_t adesc = umma_desc_kmajor<128>(a0 + (ks * KSUB + sub) * kABlockBytes);
+                  const uint64_t bdesc = umma_desc_kmajor<128>(b0 + stage * kStageBytes + sub * kSlotBytes);
 #pragma unroll
-                for (int k = 0; k < kBK / 16; ++k)
-                  umma_bf16_ss_pair(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | k) != 0);
+                  for (int k = 0; k < kBK / 16; ++k)
+                    umma_bf16_ss_pair(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | sub | k) != 0);
+                }
               }
               umma_commit_pair_mc(&ctl->b_empty[stage], 3);
               if (vi == NV - 1) umma_commit_pair_mc(&ctl->a_empty[ks], 3);
@@ -456,14 +549,12 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
 // h = bf16(tanh(P_enc[t] + P_dec[u])) for every tile row; the decomposed first joint layer
 // (model.py:26-34 without the repeat/cat). One CTA per tile, 64 threads per row (each 8
 // consecutive k: 2x16 B loads from each addend, one 16 B store), 4 rows in flight per pass.
-// Rows past an utterance's last cell and tiles past the table are written as zeros;
-// column H of the 8-wide tail is 1.0 for valid cells (the "ones" column that makes
-// dS^T.h_ext produce d b2).
+// Rows past an utterance's last cell and tiles past the table are written as zeros.
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 hidden_kernel(const JointParams p, int max_tiles) {
   const int n_tiles = min(p.n_tiles[0], max_tiles);
-  const int hp = p.H + 8;
+  const int hp = p.H;
   const int cpr = p.H / 8;            // 16-byte chunks per row
   const int rows_per_pass = 256 / cpr;  // H=512: 4 rows per pass
   const int chunk = threadIdx.x % cpr;
@@ -471,11 +562,6 @@ hidden_kernel(const JointParams p, int max_tiles) {
   for (int tile = blockIdx.x; tile < max_tiles; tile += gridDim.x) {
     const bool dead = tile >= n_tiles;
     __nv_bfloat16* dst_tile = p.h_stash + (size_t)tile * RNNT_TILE_M * hp;
-    if (threadIdx.x < RNNT_TILE_M) {
-      const RowCoord rc = locate_row(p, tile, threadIdx.x, dead);
-      *reinterpret_cast<uint4*>(dst_tile + (size_t)threadIdx.x * hp + p.H) =
-          make_uint4(rc.valid ? 0x00003F80u : 0u, 0u, 0u, 0u);
-    }
     if (rsub < rows_per_pass) {
 #pragma unroll 2
       for (int r0 = 0; r0 < RNNT_TILE_M; r0 += rows_per_pass) {
@@ -617,16 +703,20 @@ int sm_count() {
   return n;
 }
 
-int pick_stages(int H, int BN, int mode) {
-  int s = kMaxStages;
-  while (s > 2 && smem_bytes_for(H, BN, s, mode) > kSmemLimit) --s;
+int pick_stages(int H, int BN, int mode, int Vpad) {
+  // the ring depth is not critical (3, 4 and 5 stages measured equal: profiles/r01_notes.md)
+  int s = 5;
+  while (s > 2 && smem_bytes_for(H, BN, s, mode, Vpad) > kSmemLimit) --s;
   return s;
 }
 
-template <int BN, int MODE>
+template <int BN, int MODE, bool BSM>
 int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap& md, JointParams& p,
                  cudaStream_t st) {
-  p.stages = pick_stages(p.H, BN, MODE);
+  // the bias table goes to shared memory when it leaves room for >= 3 ring stages, else it is
+  // read through L1 (very large vocabularies)
+  const int bias_words = BSM ? p.Vpad : 0;
+  p.stages = pick_stages(p.H, BN, MODE, bias_words);
   {
     const char* dbg = getenv("RNNT_B200_DEBUG");
     p.debug = dbg ? atoi(dbg) : 0;
@@ -635,9 +725,9 @@ int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap
     const char* stg = getenv("RNNT_B200_STAGES");
     if (stg && atoi(stg) >= 2 && atoi(stg) < p.stages) p.stages = atoi(stg);
   }
-  const int smem = smem_bytes_for(p.H, BN, p.stages, MODE);
+  const int smem = smem_bytes_for(p.H, BN, p.stages, MODE, bias_words);
   if (smem > kSmemLimit) return RNNT_B200_E_SHAPE;
-  cudaError_t e = cudaFuncSetAttribute(joint_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  cudaError_t e = cudaFuncSetAttribute(joint_kernel<BN, MODE, BSM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return (int)e;
   int grid = sm_count() & ~1;
   const int ntile = p.tile_hi - p.tile_lo;
@@ -668,7 +758,7 @@ int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap
     if (cudaMalloc(&p.trace, trace_bytes) != cudaSuccess) p.trace = nullptr;
     else cudaMemsetAsync(p.trace, 0, trace_bytes, st);
   }
-  e = cudaLaunchKernelEx(&cfg, joint_kernel<BN, MODE>, mw, mh, md, p);
+  e = cudaLaunchKernelEx(&cfg, joint_kernel<BN, MODE, BSM>, mw, mh, md, p);
   if (e != cudaSuccess) return (int)e;
   if (p.trace) {
     long long* host = (long long*)malloc(trace_bytes);
@@ -689,7 +779,7 @@ int dispatch_joint(JointParams& p, const void* w2q, const void* h_stash, int max
   CUtensorMap mw, mh;
   int rc = make_map_bf16(&mw, w2q, p.Vpad, p.H, p.H, kBK, BN / 2, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
-  rc = make_map_bf16(&mh, h_stash, (uint64_t)max_tiles * RNNT_TILE_M, p.H, p.H + 8, kKBlock, RNNT_TILE_M,
+  rc = make_map_bf16(&mh, h_stash, (uint64_t)max_tiles * RNNT_TILE_M, p.H, p.H, kKBlock, RNNT_TILE_M,
                      CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
   CUtensorMap md = mw;
@@ -698,10 +788,19 @@ int dispatch_joint(JointParams& p, const void* w2q, const void* h_stash, int max
                        CU_TENSOR_MAP_SWIZZLE_64B);
     if (rc) return rc;
   }
+  // the bias table goes to shared memory when it leaves room for >= 3 ring stages, else it is
+  // read through L1 (very large vocabularies)
+  bool bsm = smem_bytes_for(p.H, BN, 3, MODE, p.Vpad) <= kSmemLimit;
+  if (const char* e = getenv("RNNT_B200_BSM")) {  // timing experiments only
+    if (atoi(e) == 0) bsm = false;
+    else if (smem_bytes_for(p.H, BN, 2, MODE, p.Vpad) <= kSmemLimit) bsm = true;
+  }
+  p.bias_smem = bsm ? 1 : 0;
   switch (BN) {
-    case 64: return launch_joint<64, MODE>(mw, mh, md, p, st);
-    case 128: return launch_joint<128, MODE>(mw, mh, md, p, st);
-    default: return launch_joint<256, MODE>(mw, mh, md, p, st);
+    case 64: return launch_joint<64, MODE, true>(mw, mh, md, p, st);
+    case 128: return launch_joint<128, MODE, true>(mw, mh, md, p, st);
+    default: return bsm ? launch_joint<256, MODE, true>(mw, mh, md, p, st)
+                        : launch_joint<256, MODE, false>(mw, mh, md, p, st);
   }
 }
 
@@ -752,9 +851,9 @@ extern "C" int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, 
                                       const int32_t* tile_cell0, const int32_t* n_tiles, const float* lse,
                                       const float* c_blank, const float* c_label, const float* scale, int B,
                                       int T, int U1, int V, int H, int blank, int tile_cap, int tile_lo,
-                                      int tile_hi, void* ds, void* stream) {
+                                      int tile_hi, void* ds, float* db2, void* stream) {
   if (!h_stash || !w2_bf16 || !b2_log2 || !act_lens || !label_lens || !tile_utt || !tile_cell0 || !n_tiles ||
-      !lse || !c_blank || !c_label || !scale || !ds)
+      !lse || !c_blank || !c_label || !scale || !ds || !db2)
     return RNNT_B200_E_NULL;
   if (U1 > 1 && !labels) return RNNT_B200_E_NULL;
   int rc = check_common(B, T, U1, V, H, blank);
@@ -771,6 +870,7 @@ extern "C" int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, 
   p.tile_utt = tile_utt; p.tile_cell0 = tile_cell0; p.n_tiles = n_tiles;
   p.lse = const_cast<float*>(lse); p.cb = c_blank; p.cl = c_label; p.scale = scale;
   p.ds = (__nv_bfloat16*)ds;
+  p.db2 = db2;
   p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vpad = rnnt_b200_vocab_pad(V); p.Vds = rnnt_b200_ds_pitch(V); p.H = H; p.blank = blank;
   p.tile_lo = tile_lo; p.tile_hi = tile_hi;
   return dispatch_joint<1>(p, w2_bf16, h_stash, max_tiles, (cudaStream_t)stream);
