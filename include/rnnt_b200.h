@@ -110,7 +110,10 @@ int rnnt_b200_vocab_tile(int V);
 int rnnt_b200_pack_vocab(const float* w2, const float* b2, int V, int H,
                          void* w2_bf16, float* b2_log2, void* stream);
 
-/* Row pitch (elements) of the stashed hidden activations h (currently H: rows are contiguous). */
+/* Row pitch (elements) of the stashed hidden activations h: H + 8. Column H holds 1.0 for valid
+ * cells so that the library GEMM dS^T . h_ext yields d b2 in its last column block. (Column sums
+ * inside the dS kernel were tried -- shuffles, legacy warp MMA + reductions -- and cost more than
+ * the N = H+8 GEMM shape: profiles/r01_notes.md.) */
 int rnnt_b200_h_pitch(int H);
 
 /* Row pitch (elements) of the staged bf16 logit gradient dS: V rounded up to 64 (128-byte rows;
@@ -140,17 +143,16 @@ int rnnt_b200_joint_fwd(const float* p_enc, const float* p_dec,
  * emit dS = scale_b*(softmax*(c_blank+c_label) - onehots) as bf16 for tiles
  * [tile_lo, tile_hi) into ds (rows (tile_hi-tile_lo)*128, pitch rnnt_b200_ds_pitch(V)). Rows of
  * tiles >= n_tiles[0] and rows past an utterance's last cell are written as zeros.
- * ds must be 128-byte aligned.
- * db2 (rnnt_b200_ds_pitch(V) floats, zeroed by the caller before the first chunk) accumulates
- * the column sums of dS = d loss / d b2 (warp-level tensor-core reduction of each staged tile,
- * red.global.add.f32: the summation order, hence the last bits, vary from run to run). */
+ * ds must be 128-byte aligned. lse, lp_blank, lp_label are the planes rnnt_b200_joint_fwd wrote
+ * (the two one-hot entries of each row are formed from lp_blank / lp_label).
+ */
 int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, const float* b2_log2,
                            const int32_t* labels, const int32_t* act_lens, const int32_t* label_lens,
                            const int32_t* tile_utt, const int32_t* tile_cell0, const int32_t* n_tiles,
-                           const float* lse, const float* c_blank, const float* c_label,
-                           const float* scale,
+                           const float* lse, const float* lp_blank, const float* lp_label,
+                           const float* c_blank, const float* c_label, const float* scale,
                            int B, int T, int U1, int V, int H, int blank, int tile_cap,
-                           int tile_lo, int tile_hi, void* ds, float* db2, void* stream);
+                           int tile_lo, int tile_hi, void* ds, void* stream);
 
 /* Fused backward, stage 2: dpre = dh_scale * dh * (1 - h^2) and its two reductions
  *   dP_enc[b,t,:] += sum_u dpre,   dP_dec[b,u,:] += sum_t dpre     (float32, red.global.add)

@@ -279,13 +279,13 @@ class _JointLossFn(torch.autograd.Function):
             loss, cb, cl = _lattice(lpb, lpl, act_lens, label_lens, B, T, U1)
         if need_grad:
             ctx.save_for_backward(labels, act_lens, label_lens, tile_utt, tile_cell0, n_tiles, w2q, b2l,
-                                  lse, cb, cl, h_stash)
+                                  lse, lpb, lpl, cb, cl, h_stash)
         ctx.dims = (B, T, U1, V, H, L.rnnt_b200_ds_pitch(V), max_tiles, blank)
         return loss
 
     @staticmethod
     def backward(ctx, grad_out):
-        (labels, act_lens, label_lens, tile_utt, tile_cell0, n_tiles, w2q, b2l, lse, cb, cl,
+        (labels, act_lens, label_lens, tile_utt, tile_cell0, n_tiles, w2q, b2l, lse, lpb, lpl, cb, cl,
          h_stash) = ctx.saved_tensors
         B, T, U1, V, H, Vds, max_tiles, blank = ctx.dims
         L = _lib.lib()
@@ -295,8 +295,7 @@ class _JointLossFn(torch.autograd.Function):
             scale = grad_out.to(torch.float32).contiguous()
             dpe = torch.zeros(B, T, H, dtype=torch.float32, device=dev)
             dpd = torch.zeros(B, U1, H, dtype=torch.float32, device=dev)
-            dw2p = torch.zeros(Vds, H, dtype=torch.float32, device=dev)
-            db2p = torch.zeros(Vds, dtype=torch.float32, device=dev)
+            dw2x = torch.zeros(Vds, H + 8, dtype=torch.float32, device=dev)  # [dW2 | db2 | 0..]
             chunk = max(2, min(max_tiles, _DS_BUDGET_BYTES // (128 * Vds * 2)))
             nchunk = -(-max_tiles // chunk)
             chunk = -(-max_tiles // nchunk)          # balanced chunks,
@@ -309,22 +308,23 @@ class _JointLossFn(torch.autograd.Function):
                 dsc = ds[:rows]
                 _call("joint_bwd_ds", L.rnnt_b200_joint_bwd_ds, _ptr(h_stash), _ptr(w2q), _ptr(b2l), _ptr(labels),
                                                     _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt),
-                                                    _ptr(tile_cell0), _ptr(n_tiles), _ptr(lse), _ptr(cb),
-                                                    _ptr(cl), _ptr(scale), B, T, U1, V, H, blank, max_tiles, lo, hi,
-                                                    _ptr(dsc), _ptr(db2p), st)
+                                                    _ptr(tile_cell0), _ptr(n_tiles), _ptr(lse), _ptr(lpb),
+                                                    _ptr(lpl), _ptr(cb), _ptr(cl), _ptr(scale), B, T, U1, V, H, blank, max_tiles, lo, hi,
+                                                    _ptr(dsc), st)
                 # two plain library GEMMs on the staged bf16 gradient tile (fp32 accumulate/out)
                 with _region("lib_gemm_dh"):
                     dh = torch.mm(dsc, w2v)                                            # (rows, H) bf16
                 with _region("lib_gemm_dw2"):
-                    # K = rows is huge and M x N = Vds x H small: split K (batched GEMM; measured
-                    # best, profiles/r01_notes.md). d b2 is accumulated by the dS kernel itself.
+                    # K = rows is huge and M x N = Vds x (H+8) small: split K (batched GEMM; measured
+                    # best, profiles/r01_notes.md). Column H of h_ext is 1 for valid cells, so column
+                    # H of the product is db2.
                     hc = h_stash[lo * 128: hi * 128]
-                    dw2p += torch.bmm(dsc.view(_SPLIT_K, rows // _SPLIT_K, Vds).transpose(1, 2),
-                                      hc.view(_SPLIT_K, rows // _SPLIT_K, H), out_dtype=torch.float32).sum(0)
+                    dw2x += torch.bmm(dsc.view(_SPLIT_K, rows // _SPLIT_K, Vds).transpose(1, 2),
+                                      hc.view(_SPLIT_K, rows // _SPLIT_K, H + 8), out_dtype=torch.float32).sum(0)
                 _call("dh_reduce", L.rnnt_b200_dh_reduce, _ptr(dh), _ptr(h_stash), _ptr(act_lens), _ptr(label_lens),
                       B, T, U1, H, lo, hi, 1.0, _ptr(dpe), _ptr(dpd), st)
-            dw2 = dw2p[:V]
-            db2 = db2p[:V]
+            dw2 = dw2x[:V, :H].contiguous()
+            db2 = dw2x[:V, H].contiguous()
         return dpe, dpd, dw2, db2, None, None, None, None, None
 
 

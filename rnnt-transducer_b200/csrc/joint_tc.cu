@@ -37,21 +37,21 @@
 #include "common.cuh"
 #include "sm100_ptx.cuh"
 
+
 using namespace sm100;
 
 namespace {
 
 constexpr int kThreads = 352;  // 8 epilogue warps + W2 TMA + MMA + A TMA
 constexpr int kEpiWarps = 8;
-constexpr int kKBlock = 64;              // A tile K block (128-byte swizzle span of bf16)
-constexpr int kBK = 64;                  // W2 stage K extent (128-byte swizzle span of bf16)
+constexpr int kKBlock = 64;              // K block of both operands (128-byte swizzle span of bf16)
 constexpr int kABlockBytes = RNNT_TILE_M * 128;
-constexpr int kMaxStages = 8;
+constexpr int kMaxSlots = 6;             // W2 ring slots (one K block of this CTA's half tile each)
 constexpr int kSmemLimit = 232448;       // 227 KB opt-in maximum per CTA
 
 struct SharedCtl {
-  uint64_t a_full[8], a_empty[8];
-  uint64_t b_full[kMaxStages], b_empty[kMaxStages];
+  uint64_t a_full[8], a_empty[8];        // per group of KSUB K blocks of the h tile
+  uint64_t b_full[kMaxSlots], b_empty[kMaxSlots];
   uint64_t acc_full[2], acc_empty[2];
   uint32_t tmem_base;
   uint32_t pad[3];
@@ -61,6 +61,7 @@ static_assert(sizeof(SharedCtl) % 16 == 0, "the regions behind ctl hold float4")
 struct JointParams {
   const float* pe;
   const float* pd;
+  const __nv_bfloat16* w2q;
   const float* b2l;
   const int32_t* labels;
   const int32_t* act_lens;
@@ -68,7 +69,7 @@ struct JointParams {
   const int32_t* tile_utt;
   const int32_t* tile_cell0;
   const int32_t* n_tiles;
-  // forward outputs
+  // forward outputs (the backward reads them)
   float* lse;
   float* lpb;
   float* lpl;
@@ -78,26 +79,27 @@ struct JointParams {
   const float* cl;
   const float* scale;
   __nv_bfloat16* ds;
-  float* db2;  // (Vds) column sums of dS, accumulated with red.global.add
-  int B, T, U1, V, Vpad, Vds, H, blank;  // Vpad: rows of the packed W2 (NV*BN); Vds: dS pitch = V rounded up to 16
+  int B, T, U1, V, Vpad, Vds, H, blank;  // Vpad: rows of the packed W2 (NV*BN); Vds: dS pitch
   int tile_lo, tile_hi;  // tile range of this launch
-  int stages;
+  int slots;             // W2 ring depth
   long long* trace;  // RNNT_B200_TRACE: clock64 stamps of cluster 0 / rank 0 (debug only)
-  int bias_smem;  // the b2 table fits in shared memory next to the pipeline buffers
-  int debug;  // RNNT_B200_DEBUG bitmask (timing experiments only): 1 skip epilogue math, 2 skip producer math, 4 skip MMA issue
+  int debug;  // RNNT_B200_DEBUG bitmask (timing experiments only): 1 skip epilogue math, 4 skip MMA issue,
+              // 16 skip dS stores
 };
 
-// Shared memory of joint_kernel: [h tile | W2 ring | MODE 1: dS staging, 2 x 2 KB per epilogue warp |
-// ctl | MODE 0: red, the cross-half LSE merge | bias: the whole b2*log2(e) table (Vpad floats)].
+// Shared memory of joint_kernel:
+//   [h tile: H/64 K blocks x 16 KB | W2 ring: slots x (BN/2 rows x 64 k) |
+//    MODE 1: dS staging, 2 x 2 KB per epilogue warp | ctl |
+//    MODE 0: red2, the cross-half (m, s) merge | bias ring: 2 halves x 2 buffers x BN/2 floats]
 constexpr int kDsStageBytes = kEpiWarps * 2 * 2048;
-constexpr int kRedBytes = RNNT_TILE_M * 16;
-// A pipeline stage of the W2 ring covers ksub(H) consecutive 64-wide K blocks (two when H allows:
-// one mbarrier round trip, one commit and one issue-loop iteration per 8 MMAs instead of per 4 --
-// the single-block version spent ~620 clk per stage in the issue loop against 512 clk of MMA).
+constexpr int kRedBytes = RNNT_TILE_M * 8;
+// The MMA issuer consumes ksub(H) consecutive ring slots per loop iteration (two when H allows:
+// one wait/fence/elect round per 8 MMAs -- the one-slot loop spent ~620 clk per K block against
+// 512 clk of MMA); the slots themselves are filled and released one K block at a time.
 __host__ __device__ inline int ksub_for(int H) { return (H % 128 == 0) ? 2 : 1; }
-__host__ __device__ inline int smem_bytes_for(int H, int BN, int stages, int mode, int Vpad) {
-  return (H / kKBlock) * kABlockBytes + stages * ksub_for(H) * (BN / 2) * 128 +
-         (mode == 1 ? kDsStageBytes : kRedBytes) + (int)sizeof(SharedCtl) + Vpad * 4;
+__host__ __device__ inline int smem_bytes_for(int H, int BN, int slots, int mode) {
+  return (H / kKBlock) * kABlockBytes + slots * (BN / 2) * 128 + (mode == 1 ? kDsStageBytes : kRedBytes) +
+         (int)sizeof(SharedCtl) + 2 * 2 * (BN / 2) * 4;
 }
 
 __device__ __forceinline__ float tanh_accurate(float x) {
@@ -109,6 +111,9 @@ __device__ __forceinline__ float tanh_accurate(float x) {
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float2 unpack_bf16x2(uint32_t w) {
+  return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&w));
 }
 
 // Locate row `r` of a tile: returns false when the row lies past the utterance's last cell.
@@ -133,27 +138,27 @@ __device__ __forceinline__ RowCoord locate_row(const JointParams& p, int tile, i
 // ---------------------------------------------------------------------------------------
 // MODE 0 = forward (online LSE epilogue), MODE 1 = backward dS.
 // ---------------------------------------------------------------------------------------
-template <int BN, int MODE, bool BIAS_SMEM>
+template <int BN, int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
 joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__ CUtensorMap map_h,
              const __grid_constant__ CUtensorMap map_ds, const JointParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];  // no static smem in this kernel: base is 1024-aligned
   if ((smem_u32(smem) & 1023u) != 0) __trap();       // the 128B-swizzle atoms need it
-  const int KB = p.H / kKBlock;      // A K-blocks of 64
-  const int KSUB = ksub_for(p.H);    // 64-wide K blocks per pipeline stage
-  const int KS = KB / KSUB;          // W2 stages per vocabulary tile
+  const int KB = p.H / kKBlock;      // K blocks of 64
+  const int KSUB = ksub_for(p.H);    // K blocks (ring slots) per MMA-issue iteration
+  const int KS = KB / KSUB;          // MMA-issue iterations per vocabulary tile
   const int NV = p.Vpad / BN;        // vocabulary tiles
   // The last vocabulary tile is issued with UMMA N = n_last (multiple of 16) instead of BN:
-  // V=4232 -> 16 tiles of 256 + one of 144 (4240 columns instead of 4352, -2.6% MMA work).
+  // V=4232 -> 16 tiles of 256 + one of 192 (4288 columns instead of 4352).
   const int n_last = p.Vds - (NV - 1) * BN;
+  constexpr int HALF = BN / 2;
+  constexpr int kSlotBytes = HALF * 128;  // this CTA's half of one W2 K block: BN/2 rows x 64 k
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + KB * kABlockBytes;
-  constexpr int kSlotBytes = (BN / 2) * 128;   // this CTA's half of one W2 K block: BN/2 rows x 64 k
-  const int kStageBytes = KSUB * kSlotBytes;
-  uint8_t* smem_ds = smem_b + p.stages * kStageBytes;  // MODE 1: 8 warps x 2 x 2 KB dS staging tiles
+  uint8_t* smem_ds = smem_b + p.slots * kSlotBytes;  // MODE 1: 8 warps x 2 x 2 KB dS staging tiles
   SharedCtl* ctl = reinterpret_cast<SharedCtl*>(smem_ds + (MODE == 1 ? kDsStageBytes : 0));
-  float4* red = reinterpret_cast<float4*>(ctl + 1);    // MODE 0 only
-  float* bias_s = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ctl + 1) + (MODE == 0 ? kRedBytes : 0));
+  float2* red2 = reinterpret_cast<float2*>(ctl + 1);  // MODE 0 only
+  float* bias_r = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ctl + 1) + (MODE == 0 ? kRedBytes : 0));
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -173,7 +178,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       mbar_init(&ctl->a_full[i], 2);
       mbar_init(&ctl->a_empty[i], 1);
     }
-    for (int i = 0; i < kMaxStages; ++i) {
+    for (int i = 0; i < kMaxSlots; ++i) {
       mbar_init(&ctl->b_full[i], 2);
       mbar_init(&ctl->b_empty[i], 1);
     }
@@ -183,11 +188,6 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
     }
     fence_barrier_init();
   }
-  // the bias table lives in shared memory for the whole kernel: the epilogue reads it with
-  // broadcast LDS.128 (a global/L1 load per chunk stalled the epilogue: ncu long_scoreboard 17 %)
-  if (BIAS_SMEM)
-    for (int i = threadIdx.x; i < p.Vpad / 4; i += kThreads)
-      reinterpret_cast<float4*>(bias_s)[i] = __ldg(reinterpret_cast<const float4*>(p.b2l) + i);
   __syncwarp();
   cluster_sync_all();  // barrier inits visible to the peer before any remote arrive / multicast commit
   if (warp == 9) {
@@ -201,16 +201,35 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
 
   if (warp < kEpiWarps) {
     // =========================== EPILOGUE ===========================
+    // Warp w reads TMEM lanes 32*(w&3).. (one lattice cell per thread) and the column half w>>2.
     const int q = warp & 3, half = warp >> 2;
     uint8_t* stage_w = smem_ds + warp * 4096;  // MODE 1: this warp's two dS staging tiles
     (void)stage_w;
     const int row = q * 32 + lane;
-    constexpr int HALF = BN / 2;
     constexpr int NCH = HALF / 16;  // 16-column chunks per half tile
     uint32_t acc_it = 0, st_it = 0;
     (void)st_it;
-    int it = 0;
-    for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
+    // Bias ring of this column half: buffer (acc_it & 1) holds b2*log2(e) of the current
+    // vocabulary tile's HALF columns. Warp q == 0 of the half fetches the next tile's slice into
+    // a register early in a tile, stores it into the other buffer, and one 128-thread named
+    // barrier per vocabulary tile hands it to the four warps of the half. The sweep order is
+    // vt = (cid + k) % NV for the k-th vocabulary tile this CTA processes (rotated per pair so
+    // that the 74 pairs do not pull the same W2 lines out of L2 at the same moment; the online
+    // LSE is order independent), across lattice tiles too, so the next slice is always vt+1.
+    float* bias_h = bias_r + half * 2 * HALF;
+    const bool bias_loader = (q == 0) && (lane < HALF / 4);
+    float4 bias_next = make_float4(0.f, 0.f, 0.f, 0.f);
+    int vt_fetch = cid % NV;
+    if (cid < n_pairs) {
+      if (bias_loader) {
+        reinterpret_cast<float4*>(bias_h)[lane] =
+            __ldg(reinterpret_cast<const float4*>(p.b2l + vt_fetch * BN + half * HALF) + lane);
+        vt_fetch = (vt_fetch + 1 == NV) ? 0 : vt_fetch + 1;
+        bias_next = __ldg(reinterpret_cast<const float4*>(p.b2l + vt_fetch * BN + half * HALF) + lane);
+      }
+      named_bar_sync(2 + half, 128);
+    }
+    for (int pt = cid; pt < n_pairs; pt += ncl) {
       const int tile = p.tile_lo + 2 * pt + (int)rank;
       const bool dead = tile >= n_tiles;  // odd tail: this CTA only keeps the pair's protocol going
       (void)dead;
@@ -221,54 +240,54 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         pidx = plane_index(rc.b, rc.t, rc.u, p.T, p.U1);
         if (rc.u < rc.Ub) label = clamp_int(p.labels[(size_t)rc.b * (p.U1 - 1) + rc.u], 0, p.V - 1);
       }
-      // forward state
-      float m = -INFINITY, s = 0.f, zb = 0.f, zl = 0.f;
-      // backward per-row constants
-      // dS = exp2(z + nl) - onehots with nl = log2(scale*(c_blank+c_label)) - lse*log2(e): the
-      // occupation factor rides in the exponent (one MUFU per logit, no multiply)
-      float nl = RNNT_NEG_BIG, cbs = 0.f, cls = 0.f;  // invalid rows: exp2(z + nl) == 0 exactly
+      // forward state: running maximum and sum of the online log-sum-exp (log2 domain)
+      float m = -INFINITY, s = 0.f;
+      // backward: dS = exp2(z + nl) - onehots with nl = log2(scale*(c_blank+c_label)) - lse*log2(e):
+      // the occupation factor rides in the exponent (one MUFU per logit, no multiply). The two
+      // one-hot entries of a row are not selected out of the register tile; their exact values
+      // (from the forward's lp_blank / lp_label) overwrite the staged bf16 entries instead.
+      float nl = RNNT_NEG_BIG;  // invalid rows: exp2(z + nl) == 0 exactly
+      float g_blank = 0.f, g_label = 0.f;
       if (MODE == 1 && rc.valid) {
         const float sc = p.scale[rc.b];
-        cbs = p.cb[pidx] * sc;
-        cls = (rc.u < rc.Ub) ? p.cl[pidx] * sc : 0.f;
+        const float cbs = p.cb[pidx] * sc;
+        const float cls = (rc.u < rc.Ub) ? p.cl[pidx] * sc : 0.f;
         const float c0 = cbs + cls;
         nl = (c0 > 0.f) ? log2f(c0) - p.lse[pidx] * RNNT_LOG2E : RNNT_NEG_BIG;
+        g_blank = c0 * __expf(p.lpb[pidx]) - cbs;
+        if (label >= 0) g_label = c0 * __expf(p.lpl[pidx]) - cls;
+        if (label == p.blank) { g_blank -= cls; g_label = g_blank; }
       }
       for (int vi = 0; vi < NV; ++vi, ++acc_it) {
-        // pairs sweep the vocabulary in rotated order so that the 74 pairs do not all pull the
-        // same W2 lines out of L2 at the same moment (the online LSE is order independent)
         const int vt = (vi + cid) % NV;
         const uint32_t buf = acc_it & 1;
         const long long tr0 = p.trace ? clock64() : 0;
         mbar_wait(&ctl->acc_full[buf], (acc_it >> 1) & 1);
         const long long tr1 = p.trace ? clock64() : 0;
         tc_fence_after();
-        // Software pipeline over the 16-column chunks of this warp's half tile, three register
-        // buffers deep: while chunk c goes through the MUFU-bound exponential stage, chunk c+1
-        // gets its bias FMA (+ running max) and the TMEM load of chunk c+2 is in flight, so the
-        // scheduler can fill the MUFU issue gaps with FMA-pipe work (ncu: the exponential stage
-        // and the load stalls used to run back to back, 4.5 k clk per vocabulary tile against
-        // 4.1 k clk of MMA). The accumulator buffer is handed back to the MMA warp as soon as its
-        // last TMEM load has completed, before the last two chunks are reduced.
+        if (bias_loader) {  // next tile's slice -> the buffer nobody reads during this tile
+          reinterpret_cast<float4*>(bias_h + ((acc_it + 1) & 1) * HALF)[lane] = bias_next;
+          vt_fetch = (vt_fetch + 1 == NV) ? 0 : vt_fetch + 1;
+          bias_next = __ldg(reinterpret_cast<const float4*>(p.b2l + vt_fetch * BN + half * HALF) + lane);
+        }
+        const float* bias_c = bias_h + (acc_it & 1) * HALF;
         const uint32_t taddr0 = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN + half * HALF;
         // columns of this tile that belong to this warp's half (the last tile is narrower; the
         // UMMA N granularity makes every chunk a full 16 columns)
         const int ncol = min(HALF, max(0, ((vt == NV - 1) ? n_last : BN) - half * HALF));
         const int nch = (p.debug & 1) ? 0 : ncol >> 4;
         const int colbase = vt * BN + half * HALF;
-        float z[3][16];
-        float cmax = -INFINITY;
         auto release_acc = [&]() {
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&ctl->acc_empty[buf]), 0));
         };
-        // z = acc * log2(e) + b2 * log2(e)  (+ the chunk maximum in the forward pass)
-        auto bias_stage = [&](float* zc, int col) -> float {
-          const float4* b4 = reinterpret_cast<const float4*>((BIAS_SMEM ? bias_s : p.b2l) + col);
+        // stage B: z = acc * log2(e) + b2 * log2(e)  (+ the chunk maximum in the forward pass)
+        auto bias_stage = [&](float* zc, int c) -> float {
+          const float4* b4 = reinterpret_cast<const float4*>(bias_c + c * 16);
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const float4 bb = BIAS_SMEM ? b4[j] : __ldg(b4 + j);
+            const float4 bb = b4[j];
             zc[4 * j + 0] = fmaf(zc[4 * j + 0], RNNT_LOG2E, bb.x);
             zc[4 * j + 1] = fmaf(zc[4 * j + 1], RNNT_LOG2E, bb.y);
             zc[4 * j + 2] = fmaf(zc[4 * j + 2], RNNT_LOG2E, bb.z);
@@ -280,29 +299,9 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
           m2 = fmaxf(m2, fmaxf(zc[10], zc[14])); m3 = fmaxf(m3, fmaxf(zc[11], zc[15]));
           return fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
         };
-        if (nch > 0) {
-          tmem_ld_32x16(taddr0, z[0]);
-          if (nch > 1) tmem_ld_32x16(taddr0 + 16, z[1]);
-          tmem_ld_wait();
-          if (nch <= 2) release_acc();
-          cmax = bias_stage(z[0], colbase);
-        } else {
-          release_acc();
-        }
-        // FULL: all NCH chunks present (every tile but a narrow last one) -- the pipeline
-        // conditions fold at compile time, so that the bias stage of chunk c+1 and the exponential
-        // stage of chunk c share one basic block and get interleaved by the instruction scheduler.
-        auto sweep = [&](auto full_tag) {
-        constexpr bool FULL = decltype(full_tag)::value;
-        const int nchk = FULL ? NCH : nch;
-#pragma unroll
-        for (int c = 0; c < NCH; ++c) {
-          if (!FULL && c >= nchk) break;
-          const float* zc = z[c % 3];
+        // stage C on one 16-column chunk c of this half tile
+        auto exp_stage = [&](const float* zc, int c, float cmax, int nchk) {
           const int col0 = colbase + c * 16;
-          if (c + 2 < nchk) tmem_ld_32x16(taddr0 + (c + 2) * 16, z[(c + 2) % 3]);
-          float cmax_next = -INFINITY;
-          if (c + 1 < nchk) cmax_next = bias_stage(z[(c + 1) % 3], col0 + 16);
           if (MODE == 0) {
             const float mn = fmaxf(m, cmax);
             float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;      // four independent sum chains
@@ -313,30 +312,11 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
             }
             s = s * ex2_approx(m - mn) + ((a0 + a1) + (a2 + a3));
             m = mn;
-            if ((unsigned)(p.blank - col0) < 16u) {
-              const int k = p.blank - col0;
-#pragma unroll
-              for (int j = 0; j < 16; ++j) zb = (j == k) ? zc[j] : zb;
-            }
-            if ((unsigned)(label - col0) < 16u) {
-              const int k = label - col0;
-#pragma unroll
-              for (int j = 0; j < 16; ++j) zl = (j == k) ? zc[j] : zl;
-            }
           } else {
-            float g[16];
+            uint32_t gp[8];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) g[j] = ex2_approx(zc[j] + nl);  // softmax * (c_blank + c_label) * scale
-            if ((unsigned)(p.blank - col0) < 16u) {
-              const int k = p.blank - col0;
-#pragma unroll
-              for (int j = 0; j < 16; ++j) g[j] -= (j == k) ? cbs : 0.f;
-            }
-            if ((unsigned)(label - col0) < 16u) {
-              const int k = label - col0;
-#pragma unroll
-              for (int j = 0; j < 16; ++j) g[j] -= (j == k) ? cls : 0.f;
-            }
+            for (int j = 0; j < 8; ++j)  // softmax * (c_blank + c_label) * scale, two columns per word
+              gp[j] = pack_bf16x2(ex2_approx(zc[2 * j] + nl), ex2_approx(zc[2 * j + 1] + nl));
             // 32 cells x 32 columns of bf16 (two chunks) -> one of this warp's two 2 KB staging
             // tiles (64-byte rows, SWIZZLE_64B: conflict-free 16-byte stores) -> one TMA store
             // (full-sector writes). The tile written now was last read by the store before the
@@ -347,82 +327,90 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
               __syncwarp();
             }
             uint8_t* srow = stile + lane * 64;
-#pragma unroll
-            for (int j = 0; j < 2; ++j) {
-              uint4 o;
-              o.x = pack_bf16x2(g[8 * j + 0], g[8 * j + 1]);
-              o.y = pack_bf16x2(g[8 * j + 2], g[8 * j + 3]);
-              o.z = pack_bf16x2(g[8 * j + 4], g[8 * j + 5]);
-              o.w = pack_bf16x2(g[8 * j + 6], g[8 * j + 7]);
-              *reinterpret_cast<uint4*>(srow + (((2 * (c & 1) + j) ^ ((lane >> 1) & 3)) << 4)) = o;
+            const int swz = (lane >> 1) & 3;
+            *reinterpret_cast<uint4*>(srow + (((2 * (c & 1)) ^ swz) << 4)) = make_uint4(gp[0], gp[1], gp[2], gp[3]);
+            *reinterpret_cast<uint4*>(srow + (((2 * (c & 1) + 1) ^ swz) << 4)) = make_uint4(gp[4], gp[5], gp[6], gp[7]);
+            // the row's one-hot entries: exact values over the staged ones (same thread, program order)
+            if ((unsigned)(p.blank - col0) < 16u && rc.valid) {
+              const int off = (c & 1) * 32 + (p.blank - col0) * 2;
+              *reinterpret_cast<__nv_bfloat16*>(srow + (((off >> 4) ^ swz) << 4) + (off & 15)) = __float2bfloat16_rn(g_blank);
+            }
+            if ((unsigned)(label - col0) < 16u) {
+              const int off = (c & 1) * 32 + (label - col0) * 2;
+              *reinterpret_cast<__nv_bfloat16*>(srow + (((off >> 4) ^ swz) << 4) + (off & 15)) = __float2bfloat16_rn(g_label);
             }
             if ((c & 1) == 1 || c + 1 == nchk) {
               fence_proxy_async_smem();
               __syncwarp();
+              const int colt = colbase + (c & ~1) * 16;
               if (lane == 0 && !dead && !(p.debug & 16)) {
-                tma_store_2d(&map_ds, stile, colbase + (c & ~1) * 16, (tile - p.tile_lo) * RNNT_TILE_M + q * 32);
+                tma_store_2d(&map_ds, stile, colt, (tile - p.tile_lo) * RNNT_TILE_M + q * 32);
                 bulk_commit_group();
               }
               ++st_it;
-              // d b2 += column sums of the staged 32 x 32 tile, on the warp-level tensor path:
-              // ones(16x32) . dS(32x32) as 2 k-steps x 4 n-blocks of m16n8k16 (every row of the
-              // product holds the sums); the staged tile is read back with ldmatrix.trans
-              // (row l of the tile = lane l's 64-byte row, 16-byte unit nb, SWIZZLE_64B).
-              // One coalesced fp32 reduction (32 columns = 128 bytes) per tile and warp.
-              if (!(p.debug & 32)) {
-                constexpr uint32_t kOnes = 0x3F803F80u;  // bf16 {1, 1}
-                const uint32_t rbase = smem_u32(stile) + lane * 64;
-                const int swz = (lane >> 1) & 3;
-                float acc[4][4];
-#pragma unroll
-                for (int nb = 0; nb < 4; ++nb) {
-                  uint32_t b0, b1, b2, b3;
-                  ldmatrix_x4_trans(rbase + ((nb ^ swz) << 4), b0, b1, b2, b3);
-                  acc[nb][0] = acc[nb][1] = acc[nb][2] = acc[nb][3] = 0.f;
-                  if (!(p.debug & 64)) {
-                  mma_m16n8k16_bf16(acc[nb], kOnes, kOnes, kOnes, kOnes, b0, b1);  // cells 0..15
-                  mma_m16n8k16_bf16(acc[nb], kOnes, kOnes, kOnes, kOnes, b2, b3);  // cells 16..31
-                  } else { acc[nb][0] = __uint_as_float(b0 ^ b2); acc[nb][1] = __uint_as_float(b1 ^ b3); }
-                }
-                // lane T holds, for every n-block, columns 8*nb + 2*(T%4) + {0,1}; lane group
-                // g = T/4 publishes n-block g/2, parity g%2 -> the 32 lanes cover the 32 columns.
-                const int g = lane >> 2;
-                const float lo = (g & 1) ? acc[0][1] : acc[0][0], l1 = (g & 1) ? acc[1][1] : acc[1][0];
-                const float l2 = (g & 1) ? acc[2][1] : acc[2][0], l3 = (g & 1) ? acc[3][1] : acc[3][0];
-                const float v = (g & 4) ? ((g & 2) ? l3 : l2) : ((g & 2) ? l1 : lo);
-                const int col = colbase + (c & ~1) * 16 + (g >> 1) * 8 + 2 * (lane & 3) + (g & 1);
-                if (!dead && col < p.Vds && !(p.debug & 128)) atomicAdd(p.db2 + col, v);
-                if ((p.debug & 128) && v == 123.456f) p.db2[0] = v;
-              }
             }
           }
-          cmax = cmax_next;
-          if (c + 2 < nchk) {
-            tmem_ld_wait();  // chunk c+2 has landed (it had this whole iteration to do so)
-            if (c + 3 == nchk) release_acc();
+        };
+
+        if (NCH == 8 && nch == NCH) {
+          // Software pipeline over the eight 16-column chunks, three register buffers deep:
+          // while chunk c goes through the MUFU-bound exponential stage, chunk c+1 gets its bias
+          // FMA (+ running max) in the same basic block and the TMEM load of chunk c+2 is in
+          // flight. The accumulator buffer is handed back to the MMA warp as soon as its last
+          // TMEM load has completed, before the last two chunks are reduced.
+          float z[3][16];
+          tmem_ld_32x16(taddr0, z[0]);
+          tmem_ld_32x16(taddr0 + 16, z[1]);
+          tmem_ld_wait();
+          float cmax = bias_stage(z[0], 0);
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            if (c + 2 < 8) tmem_ld_32x16(taddr0 + (c + 2) * 16, z[(c + 2) % 3]);
+            float cmax_next = -INFINITY;
+            if (c + 1 < 8) cmax_next = bias_stage(z[(c + 1) % 3], c + 1);
+            exp_stage(z[c % 3], c, cmax, 8);
+            cmax = cmax_next;
+            if (c + 2 < 8) {
+              tmem_ld_wait();  // chunk c+2 has landed (it had this whole iteration to do so)
+              if (c + 3 == 8) release_acc();
+            }
+          }
+        } else {
+          // narrow last vocabulary tile, small BN, or nothing to do: one chunk at a time
+          float z0[16];
+          if (nch == 0) release_acc();
+#pragma unroll 1
+          for (int c = 0; c < nch; ++c) {
+            tmem_ld_32x16(taddr0 + c * 16, z0);
+            tmem_ld_wait();
+            if (c + 1 == nch) release_acc();
+            const float cmax = bias_stage(z0, c);
+            exp_stage(z0, c, cmax, nch);
           }
         }
-        };
-        if (nch == NCH) sweep(std::true_type{});
-        else sweep(std::false_type{});
+        named_bar_sync(2 + half, 128);  // bias ring hand-over (see above)
         if (p.trace && blockIdx.x == 0 && threadIdx.x == 0 && acc_it < 4096) {
           long long* t = p.trace + 6 * 4096;
           t[3 * acc_it + 0] = tr0; t[3 * acc_it + 1] = tr1; t[3 * acc_it + 2] = clock64();
         }
       }
       if (MODE == 0) {
-        if (half == 1) red[row] = make_float4(m, s, zb, zl);
+        // merge the two column halves; the blank / label logits come from hidden_kernel
+        // (log2 domain, stored in the lp planes), so no register-tile selection is needed here
+        if (half == 1) red2[row] = make_float2(m, s);
         named_bar_sync(1, kEpiWarps * 32);
         if (half == 0 && rc.valid) {
-          const float4 o = red[row];
+          const float2 o = red2[row];
           const float mn = fmaxf(m, o.x);
           const float st = s * ex2_approx(m - mn) + o.y * ex2_approx(o.x - mn);
           const float lse2 = mn + log2f(st);
+          const float zb = p.lpb[pidx];
+          const float zl = p.lpl[pidx];
           p.lse[pidx] = lse2 * RNNT_LN2;
-          p.lpb[pidx] = (zb + o.z - lse2) * RNNT_LN2;
-          p.lpl[pidx] = (label >= 0) ? (zl + o.w - lse2) * RNNT_LN2 : -INFINITY;
+          p.lpb[pidx] = (zb - lse2) * RNNT_LN2;
+          p.lpl[pidx] = (label >= 0) ? (zl - lse2) * RNNT_LN2 : -INFINITY;
         }
-        named_bar_sync(1, kEpiWarps * 32);  // red[] is free again
+        named_bar_sync(1, kEpiWarps * 32);  // red2[] is free again
       }
     }
     if (MODE == 1) {
@@ -438,32 +426,29 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
     }
   } else if (warp == 8) {
     // =========================== TMA PRODUCER (W2) ===========================
+    // One ring slot = this CTA's BN/2 rows of one 64-wide K block; the leader's b_full collects
+    // both CTAs' bytes (2 arrivals + 2 x kSlotBytes).
     if (lane == 0) {
-      uint32_t stage = 0, phase = 0;
-      int it = 0, tr_n = 0;
-      for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
-      const int tile = p.tile_lo + 2 * pt + (int)rank;
-      const bool dead = tile >= n_tiles;  // odd tail: this CTA only keeps the pair's protocol going
-      (void)dead;
+      uint32_t slot = 0, phase = 0;
+      int tr_n = 0;
+      for (int pt = cid; pt < n_pairs; pt += ncl) {
         for (int vi = 0; vi < NV; ++vi) {
           const int vt = (vi + cid) % NV;
-          for (int ks = 0; ks < KS; ++ks) {
+          const int row0 = vt * BN + (int)rank * (((vt == NV - 1) ? n_last : BN) / 2);
+          for (int kb = 0; kb < KB; ++kb) {
             const long long tr0 = p.trace ? clock64() : 0;
-            mbar_wait(&ctl->b_empty[stage], phase ^ 1);
+            mbar_wait(&ctl->b_empty[slot], phase ^ 1);
             const long long tr1 = p.trace ? clock64() : 0;
-            const uint32_t full = mapa_u32(smem_u32(&ctl->b_full[stage]), 0);
-            if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[stage], 2 * kStageBytes);
+            const uint32_t full = mapa_u32(smem_u32(&ctl->b_full[slot]), 0);
+            if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[slot], 2 * kSlotBytes);
             else mbar_arrive_cluster(full);
-            const int row0 = vt * BN + (int)rank * (((vt == NV - 1) ? n_last : BN) / 2);
-            for (int sub = 0; sub < KSUB; ++sub)
-              tma_load_2d_pair(smem_b + stage * kStageBytes + sub * kSlotBytes, &map_w2, full,
-                               (ks * KSUB + sub) * kBK, row0);
+            tma_load_2d_pair(smem_b + slot * kSlotBytes, &map_w2, full, kb * kKBlock, row0);
             if (p.trace && blockIdx.x == 0 && tr_n < 4096) {
               long long* t = p.trace + 3 * 4096;
               t[3 * tr_n + 0] = tr0; t[3 * tr_n + 1] = tr1; t[3 * tr_n + 2] = clock64();
               ++tr_n;
             }
-            if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
+            if (++slot == (uint32_t)p.slots) { slot = 0; phase ^= 1; }
           }
         }
       }
@@ -473,9 +458,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
     if (lane == 0) {
       int it = 0;
       for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
-      const int tile = p.tile_lo + 2 * pt + (int)rank;
-      const bool dead = tile >= n_tiles;  // odd tail: this CTA only keeps the pair's protocol going
-      (void)dead;
+        const int tile = p.tile_lo + 2 * pt + (int)rank;  // a dead odd-tail tile loads zeros or stale rows: unused
         for (int ks = 0; ks < KS; ++ks) {  // one barrier pair per group of KSUB K blocks
           mbar_wait(&ctl->a_empty[ks], (it & 1) ^ 1);
           const uint32_t full = mapa_u32(smem_u32(&ctl->a_full[ks]), 0);
@@ -491,11 +474,13 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
   } else if (warp == 9) {
     // =========================== MMA ISSUER ===========================
     // The whole warp walks the loop with warp-uniform control flow (cheap uniform-datapath
-    // descriptor arithmetic, no single-lane waterfall code); one elected lane issues.
+    // descriptor arithmetic, no single-lane waterfall code); one elected lane issues. Each
+    // iteration takes KSUB ring slots: 4 MMAs (K = 64) per slot, the slot's b_empty commit right
+    // behind them so that the producer can refill it while the next slot is multiplied.
     if (rank == 0) {
       constexpr uint32_t idesc_full = umma_idesc_bf16(2 * RNNT_TILE_M, BN);
       const uint32_t idesc_last = umma_idesc_bf16(2 * RNNT_TILE_M, n_last);
-      uint32_t stage = 0, phase = 0, acc_it = 0;
+      uint32_t slot = 0, phase = 0, acc_it = 0;
       int it = 0, tr_n = 0;
       const uint32_t a0 = smem_u32(smem_a), b0 = smem_u32(smem_b);
       const bool tracing = p.trace != nullptr && blockIdx.x == 0;
@@ -510,20 +495,30 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
           for (int ks = 0; ks < KS; ++ks) {
             if (vi == 0) mbar_wait(&ctl->a_full[ks], it & 1);
             const long long tr0 = tracing ? clock64() : 0;
-            mbar_wait(&ctl->b_full[stage], phase);
+            const uint32_t s0 = slot, ph0 = phase;
+            if (++slot == (uint32_t)p.slots) { slot = 0; phase ^= 1; }
+            uint32_t s1 = s0;
+            mbar_wait(&ctl->b_full[s0], ph0);
+            if (KSUB == 2) {
+              s1 = slot;
+              const uint32_t ph1 = phase;
+              if (++slot == (uint32_t)p.slots) { slot = 0; phase ^= 1; }
+              mbar_wait(&ctl->b_full[s1], ph1);
+            }
             const long long tr1 = tracing ? clock64() : 0;
             tc_fence_after();
             if (elect_one_sync()) {
-              if (!(p.debug & 4)) {
-                for (int sub = 0; sub < KSUB; ++sub) {
+              for (int sub = 0; sub < KSUB; ++sub) {
+                const uint32_t sl = sub ? s1 : s0;
+                if (!(p.debug & 4)) {
                   const uint64_t adesc = umma_desc_kmajor<128>(a0 + (ks * KSUB + sub) * kABlockBytes);
-                  const uint64_t bdesc = umma_desc_kmajor<128>(b0 + stage * kStageBytes + sub * kSlotBytes);
+                  const uint64_t bdesc = umma_desc_kmajor<128>(b0 + sl * kSlotBytes);
 #pragma unroll
-                  for (int k = 0; k < kBK / 16; ++k)
+                  for (int k = 0; k < kKBlock / 16; ++k)
                     umma_bf16_ss_pair(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | sub | k) != 0);
                 }
+                umma_commit_pair_mc(&ctl->b_empty[sl], 3);
               }
-              umma_commit_pair_mc(&ctl->b_empty[stage], 3);
               if (vi == NV - 1) umma_commit_pair_mc(&ctl->a_empty[ks], 3);
               if (ks == KS - 1) umma_commit_pair_mc(&ctl->acc_full[buf], 3);
             }
@@ -532,7 +527,6 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
               p.trace[3 * tr_n + 0] = tr0; p.trace[3 * tr_n + 1] = tr1; p.trace[3 * tr_n + 2] = clock64();
               ++tr_n;
             }
-            if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
           }
         }
       }
@@ -547,37 +541,67 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
 
 // ---------------------------------------------------------------------------------------
 // h = bf16(tanh(P_enc[t] + P_dec[u])) for every tile row; the decomposed first joint layer
-// (model.py:26-34 without the repeat/cat). One CTA per tile, 64 threads per row (each 8
-// consecutive k: 2x16 B loads from each addend, one 16 B store), 4 rows in flight per pass.
-// Rows past an utterance's last cell and tiles past the table are written as zeros.
+// (model.py:26-34 without the repeat/cat). One CTA per tile, one warp per row at a time
+// (lane l owns the 16-byte chunks l, l+32, ... of the row: 2x16 B loads from each addend, one
+// 16 B store per chunk). Rows past an utterance's last cell and tiles past the table are written
+// as zeros; column H of the 8-wide row tail is 1.0 for valid cells (the "ones" column that makes
+// the library GEMM dS^T . h_ext produce d b2 next to dW2). The same pass takes the dot products of the (bf16-rounded) row with the blank and
+// the label rows of W2 -- the two logits the loss needs per cell -- and leaves them, in the log2
+// domain with the bias, in the lp_blank / lp_label planes, where the forward GEMM's epilogue turns
+// them into log-probabilities once it knows the row's log-sum-exp. (Selecting them out of the
+// GEMM's register tiles cost ~7 % of the epilogue's issue slots.)
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 hidden_kernel(const JointParams p, int max_tiles) {
   const int n_tiles = min(p.n_tiles[0], max_tiles);
-  const int hp = p.H;
-  const int cpr = p.H / 8;            // 16-byte chunks per row
-  const int rows_per_pass = 256 / cpr;  // H=512: 4 rows per pass
-  const int chunk = threadIdx.x % cpr;
-  const int rsub = threadIdx.x / cpr;
+  const int cpr = p.H / 8;  // 16-byte chunks per row
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint4* wb4 = reinterpret_cast<const uint4*>(p.w2q + (size_t)p.blank * p.H);
   for (int tile = blockIdx.x; tile < max_tiles; tile += gridDim.x) {
     const bool dead = tile >= n_tiles;
+    const int hp = p.H + 8;  // columns H..H+7 = [1, 0, ..] for valid cells: dS^T . h_ext = [dW2 | db2 | 0]
     __nv_bfloat16* dst_tile = p.h_stash + (size_t)tile * RNNT_TILE_M * hp;
-    if (rsub < rows_per_pass) {
 #pragma unroll 2
-      for (int r0 = 0; r0 < RNNT_TILE_M; r0 += rows_per_pass) {
-        const int row = r0 + rsub;
-        const RowCoord rc = locate_row(p, tile, row, dead);
+    for (int row = warp; row < RNNT_TILE_M; row += 8) {
+      const RowCoord rc = locate_row(p, tile, row, dead);
+      int label = -1;
+      if (rc.valid && rc.u < rc.Ub) label = clamp_int(p.labels[(size_t)rc.b * (p.U1 - 1) + rc.u], 0, p.V - 1);
+      const uint4* wl4 = reinterpret_cast<const uint4*>(p.w2q + (size_t)(label >= 0 ? label : p.blank) * p.H);
+      float accb = 0.f, accl = 0.f;
+      for (int ch = lane; ch < cpr; ch += 32) {
         uint4 o = make_uint4(0u, 0u, 0u, 0u);
         if (rc.valid) {
-          const float4* e4 = reinterpret_cast<const float4*>(p.pe + ((size_t)rc.b * p.T + rc.t) * p.H) + chunk * 2;
-          const float4* d4 = reinterpret_cast<const float4*>(p.pd + ((size_t)rc.b * p.U1 + rc.u) * p.H) + chunk * 2;
+          const float4* e4 = reinterpret_cast<const float4*>(p.pe + ((size_t)rc.b * p.T + rc.t) * p.H) + ch * 2;
+          const float4* d4 = reinterpret_cast<const float4*>(p.pd + ((size_t)rc.b * p.U1 + rc.u) * p.H) + ch * 2;
           const float4 e0 = __ldg(e4), e1 = __ldg(e4 + 1), d0 = __ldg(d4), d1 = __ldg(d4 + 1);
+          const uint4 wb = __ldg(wb4 + ch), wl = __ldg(wl4 + ch);
           o.x = pack_bf16x2(tanh_accurate(e0.x + d0.x), tanh_accurate(e0.y + d0.y));
           o.y = pack_bf16x2(tanh_accurate(e0.z + d0.z), tanh_accurate(e0.w + d0.w));
           o.z = pack_bf16x2(tanh_accurate(e1.x + d1.x), tanh_accurate(e1.y + d1.y));
           o.w = pack_bf16x2(tanh_accurate(e1.z + d1.z), tanh_accurate(e1.w + d1.w));
+          const uint32_t hw[4] = {o.x, o.y, o.z, o.w};
+          const uint32_t bw[4] = {wb.x, wb.y, wb.z, wb.w};
+          const uint32_t lw[4] = {wl.x, wl.y, wl.z, wl.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 hf = unpack_bf16x2(hw[j]), bf = unpack_bf16x2(bw[j]), lf = unpack_bf16x2(lw[j]);
+            accb = fmaf(hf.x, bf.x, accb); accb = fmaf(hf.y, bf.y, accb);
+            accl = fmaf(hf.x, lf.x, accl); accl = fmaf(hf.y, lf.y, accl);
+          }
         }
-        *reinterpret_cast<uint4*>(dst_tile + (size_t)row * hp + chunk * 8) = o;
+        *reinterpret_cast<uint4*>(dst_tile + (size_t)row * hp + ch * 8) = o;
+      }
+      if (lane == 0)
+        *reinterpret_cast<uint4*>(dst_tile + (size_t)row * hp + p.H) = make_uint4(rc.valid ? 0x00003F80u : 0u, 0u, 0u, 0u);
+#pragma unroll
+      for (int sh = 16; sh > 0; sh >>= 1) {
+        accb += __shfl_xor_sync(0xffffffffu, accb, sh);
+        accl += __shfl_xor_sync(0xffffffffu, accl, sh);
+      }
+      if (rc.valid && lane == 0) {
+        const size_t pidx = plane_index(rc.b, rc.t, rc.u, p.T, p.U1);
+        p.lpb[pidx] = fmaf(accb, RNNT_LOG2E, p.b2l[p.blank]);
+        p.lpl[pidx] = fmaf(accl, RNNT_LOG2E, p.b2l[label >= 0 ? label : p.blank]);
       }
     }
   }
@@ -703,31 +727,29 @@ int sm_count() {
   return n;
 }
 
-int pick_stages(int H, int BN, int mode, int Vpad) {
-  // the ring depth is not critical (3, 4 and 5 stages measured equal: profiles/r01_notes.md)
-  int s = 5;
-  while (s > 2 && smem_bytes_for(H, BN, s, mode, Vpad) > kSmemLimit) --s;
+int pick_slots(int H, int BN, int mode) {
+  int s = kMaxSlots;
+  while (s > 2 && smem_bytes_for(H, BN, s, mode) > kSmemLimit) --s;
   return s;
 }
 
-template <int BN, int MODE, bool BSM>
+template <int BN, int MODE>
 int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap& md, JointParams& p,
                  cudaStream_t st) {
   // the bias table goes to shared memory when it leaves room for >= 3 ring stages, else it is
   // read through L1 (very large vocabularies)
-  const int bias_words = BSM ? p.Vpad : 0;
-  p.stages = pick_stages(p.H, BN, MODE, bias_words);
+  p.slots = pick_slots(p.H, BN, MODE);
   {
     const char* dbg = getenv("RNNT_B200_DEBUG");
     p.debug = dbg ? atoi(dbg) : 0;
     const char* dm = getenv("RNNT_B200_DEBUG_MODE");
     if (dm && atoi(dm) != MODE) p.debug = 0;
-    const char* stg = getenv("RNNT_B200_STAGES");
-    if (stg && atoi(stg) >= 2 && atoi(stg) < p.stages) p.stages = atoi(stg);
+    const char* stg = getenv("RNNT_B200_SLOTS");
+    if (stg && atoi(stg) >= 2 && atoi(stg) < p.slots) p.slots = atoi(stg);
   }
-  const int smem = smem_bytes_for(p.H, BN, p.stages, MODE, bias_words);
+  const int smem = smem_bytes_for(p.H, BN, p.slots, MODE);
   if (smem > kSmemLimit) return RNNT_B200_E_SHAPE;
-  cudaError_t e = cudaFuncSetAttribute(joint_kernel<BN, MODE, BSM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  cudaError_t e = cudaFuncSetAttribute(joint_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return (int)e;
   int grid = sm_count() & ~1;
   const int ntile = p.tile_hi - p.tile_lo;
@@ -758,7 +780,7 @@ int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap
     if (cudaMalloc(&p.trace, trace_bytes) != cudaSuccess) p.trace = nullptr;
     else cudaMemsetAsync(p.trace, 0, trace_bytes, st);
   }
-  e = cudaLaunchKernelEx(&cfg, joint_kernel<BN, MODE, BSM>, mw, mh, md, p);
+  e = cudaLaunchKernelEx(&cfg, joint_kernel<BN, MODE>, mw, mh, md, p);
   if (e != cudaSuccess) return (int)e;
   if (p.trace) {
     long long* host = (long long*)malloc(trace_bytes);
@@ -777,9 +799,9 @@ template <int MODE>
 int dispatch_joint(JointParams& p, const void* w2q, const void* h_stash, int max_tiles, cudaStream_t st) {
   const int BN = rnnt_b200_vocab_tile(p.V);
   CUtensorMap mw, mh;
-  int rc = make_map_bf16(&mw, w2q, p.Vpad, p.H, p.H, kBK, BN / 2, CU_TENSOR_MAP_SWIZZLE_128B);
+  int rc = make_map_bf16(&mw, w2q, p.Vpad, p.H, p.H, kKBlock, BN / 2, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
-  rc = make_map_bf16(&mh, h_stash, (uint64_t)max_tiles * RNNT_TILE_M, p.H, p.H, kKBlock, RNNT_TILE_M,
+  rc = make_map_bf16(&mh, h_stash, (uint64_t)max_tiles * RNNT_TILE_M, p.H, p.H + 8, kKBlock, RNNT_TILE_M,
                      CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
   CUtensorMap md = mw;
@@ -788,19 +810,10 @@ int dispatch_joint(JointParams& p, const void* w2q, const void* h_stash, int max
                        CU_TENSOR_MAP_SWIZZLE_64B);
     if (rc) return rc;
   }
-  // the bias table goes to shared memory when it leaves room for >= 3 ring stages, else it is
-  // read through L1 (very large vocabularies)
-  bool bsm = smem_bytes_for(p.H, BN, 3, MODE, p.Vpad) <= kSmemLimit;
-  if (const char* e = getenv("RNNT_B200_BSM")) {  // timing experiments only
-    if (atoi(e) == 0) bsm = false;
-    else if (smem_bytes_for(p.H, BN, 2, MODE, p.Vpad) <= kSmemLimit) bsm = true;
-  }
-  p.bias_smem = bsm ? 1 : 0;
   switch (BN) {
-    case 64: return launch_joint<64, MODE, true>(mw, mh, md, p, st);
-    case 128: return launch_joint<128, MODE, true>(mw, mh, md, p, st);
-    default: return bsm ? launch_joint<256, MODE, true>(mw, mh, md, p, st)
-                        : launch_joint<256, MODE, false>(mw, mh, md, p, st);
+    case 64: return launch_joint<64, MODE>(mw, mh, md, p, st);
+    case 128: return launch_joint<128, MODE>(mw, mh, md, p, st);
+    default: return launch_joint<256, MODE>(mw, mh, md, p, st);
   }
 }
 
@@ -831,7 +844,7 @@ extern "C" int rnnt_b200_joint_fwd(const float* p_enc, const float* p_dec, const
       ((uintptr_t)b2_log2 & 15) || ((uintptr_t)h_stash & 127))
     return RNNT_B200_E_ALIGN;
   JointParams p = {};
-  p.pe = p_enc; p.pd = p_dec; p.b2l = b2_log2; p.labels = labels; p.act_lens = act_lens;
+  p.pe = p_enc; p.pd = p_dec; p.w2q = (const __nv_bfloat16*)w2_bf16; p.b2l = b2_log2; p.labels = labels; p.act_lens = act_lens;
   p.label_lens = label_lens; p.tile_utt = tile_utt; p.tile_cell0 = tile_cell0; p.n_tiles = n_tiles;
   p.lse = lse; p.lpb = lp_blank; p.lpl = lp_label; p.h_stash = (__nv_bfloat16*)h_stash;
   p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vpad = rnnt_b200_vocab_pad(V); p.Vds = rnnt_b200_ds_pitch(V); p.H = H; p.blank = blank;
@@ -849,11 +862,12 @@ extern "C" int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, 
                                       const int32_t* labels, const int32_t* act_lens,
                                       const int32_t* label_lens, const int32_t* tile_utt,
                                       const int32_t* tile_cell0, const int32_t* n_tiles, const float* lse,
+                                      const float* lp_blank, const float* lp_label,
                                       const float* c_blank, const float* c_label, const float* scale, int B,
                                       int T, int U1, int V, int H, int blank, int tile_cap, int tile_lo,
-                                      int tile_hi, void* ds, float* db2, void* stream) {
+                                      int tile_hi, void* ds, void* stream) {
   if (!h_stash || !w2_bf16 || !b2_log2 || !act_lens || !label_lens || !tile_utt || !tile_cell0 || !n_tiles ||
-      !lse || !c_blank || !c_label || !scale || !ds || !db2)
+      !lse || !lp_blank || !lp_label || !c_blank || !c_label || !scale || !ds)
     return RNNT_B200_E_NULL;
   if (U1 > 1 && !labels) return RNNT_B200_E_NULL;
   int rc = check_common(B, T, U1, V, H, blank);
@@ -868,9 +882,9 @@ extern "C" int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, 
   JointParams p = {};
   p.b2l = b2_log2; p.labels = labels; p.act_lens = act_lens; p.label_lens = label_lens;
   p.tile_utt = tile_utt; p.tile_cell0 = tile_cell0; p.n_tiles = n_tiles;
-  p.lse = const_cast<float*>(lse); p.cb = c_blank; p.cl = c_label; p.scale = scale;
+  p.lse = const_cast<float*>(lse); p.lpb = const_cast<float*>(lp_blank); p.lpl = const_cast<float*>(lp_label);
+  p.cb = c_blank; p.cl = c_label; p.scale = scale;
   p.ds = (__nv_bfloat16*)ds;
-  p.db2 = db2;
   p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vpad = rnnt_b200_vocab_pad(V); p.Vds = rnnt_b200_ds_pitch(V); p.H = H; p.blank = blank;
   p.tile_lo = tile_lo; p.tile_hi = tile_hi;
   return dispatch_joint<1>(p, w2_bf16, h_stash, max_tiles, (cudaStream_t)stream);

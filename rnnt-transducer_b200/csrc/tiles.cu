@@ -70,7 +70,7 @@ dh_reduce_kernel(const __nv_bfloat16* __restrict__ dh, const __nv_bfloat16* __re
   const long long c_first = (long long)t0 * w, c_last = (long long)(t0 + nt) * w;
   if (c_last <= lo || c_first >= hi) return;
   const int k2 = threadIdx.x;  // column pair
-  const int hp = H;
+  const int hp = H + 8;
   const __nv_bfloat162* dh2 = reinterpret_cast<const __nv_bfloat162*>(dh) + k2;
   const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(h) + k2;
   float2 acc_e[DH_TT];
@@ -137,7 +137,7 @@ extern "C" int rnnt_b200_vocab_pad(int V) {
   const int bn = rnnt_b200_vocab_tile(V);
   return ((V + bn - 1) / bn) * bn;
 }
-extern "C" int rnnt_b200_h_pitch(int H) { return H; }
+extern "C" int rnnt_b200_h_pitch(int H) { return H + 8; }
 extern "C" int rnnt_b200_ds_pitch(int V) {
   // The UMMA N granularity is 16, but a pitch that is not a multiple of 64 elements (128 bytes)
   // slows the library GEMMs that consume dS by more than the narrower tile saves (measured:
