@@ -17,10 +17,10 @@
 // vocabulary in lockstep in BN-column tiles with K = H; each CTA TMA-loads only its half
 // (BN/2 rows) of every W2 stage, which halves the L2->SM traffic per SM -- the measured
 // limiter of the single-CTA version (profiles/r01_notes.md). Pairs are persistent: pair c
-// walks pair-tiles c, c+gridDim/2, ...  Warp roles (352 threads per CTA):
+// walks pair-tiles c, c+gridDim/2, ...  Warp roles (384 threads per CTA):
 //   warps 0-7   epilogue: TMEM -> registers; warp w owns TMEM lanes 32*(w&3)..+31 (one
 //               lattice cell per thread) and column half (w>>2) of the BN-wide tile
-//   warp 8      TMA producer: this CTA's half of each W2 stage
+//   warps 8,11  TMA producers: this CTA's half of each W2 K block (even / odd blocks)
 //   warp 9      TMEM allocator (both CTAs) and MMA issuer (leader CTA, one elected thread)
 //   warp 10     TMA producer of the h tile (A operand, eight 64-wide K blocks, resident
 //               for the whole vocabulary sweep)
@@ -42,7 +42,7 @@ using namespace sm100;
 
 namespace {
 
-constexpr int kThreads = 352;  // 8 epilogue warps + W2 TMA + MMA + A TMA
+constexpr int kThreads = 384;  // 8 epilogue warps + W2 TMA (even K blocks) + MMA + A TMA + W2 TMA (odd K blocks)
 constexpr int kEpiWarps = 8;
 constexpr int kKBlock = 64;              // K block of both operands (128-byte swizzle span of bf16)
 constexpr int kABlockBytes = RNNT_TILE_M * 128;
@@ -90,9 +90,9 @@ struct JointParams {
 // Shared memory of joint_kernel:
 //   [h tile: H/64 K blocks x 16 KB | W2 ring: slots x (BN/2 rows x 64 k) |
 //    MODE 1: dS staging, 2 x 2 KB per epilogue warp | ctl |
-//    MODE 0: red2, the cross-half (m, s) merge | bias ring: 2 halves x 2 buffers x BN/2 floats]
+//    MODE 0: red4, the cross-half (m, s, zb, zl) merge | bias ring: 2 halves x 2 buffers x BN/2 floats]
 constexpr int kDsStageBytes = kEpiWarps * 2 * 2048;
-constexpr int kRedBytes = RNNT_TILE_M * 8;
+constexpr int kRedBytes = RNNT_TILE_M * 16;
 // The MMA issuer consumes ksub(H) consecutive ring slots per loop iteration (two when H allows:
 // one wait/fence/elect round per 8 MMAs -- the one-slot loop spent ~620 clk per K block against
 // 512 clk of MMA); the slots themselves are filled and released one K block at a time.
@@ -157,7 +157,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
   uint8_t* smem_b = smem + KB * kABlockBytes;
   uint8_t* smem_ds = smem_b + p.slots * kSlotBytes;  // MODE 1: 8 warps x 2 x 2 KB dS staging tiles
   SharedCtl* ctl = reinterpret_cast<SharedCtl*>(smem_ds + (MODE == 1 ? kDsStageBytes : 0));
-  float2* red2 = reinterpret_cast<float2*>(ctl + 1);  // MODE 0 only
+  float4* red4 = reinterpret_cast<float4*>(ctl + 1);  // MODE 0 only
   float* bias_r = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ctl + 1) + (MODE == 0 ? kRedBytes : 0));
 
   const int warp = threadIdx.x >> 5;
@@ -241,7 +241,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         if (rc.u < rc.Ub) label = clamp_int(p.labels[(size_t)rc.b * (p.U1 - 1) + rc.u], 0, p.V - 1);
       }
       // forward state: running maximum and sum of the online log-sum-exp (log2 domain)
-      float m = -INFINITY, s = 0.f;
+      float m = -INFINITY, s = 0.f, zb = 0.f, zl = 0.f;
       // backward: dS = exp2(z + nl) - onehots with nl = log2(scale*(c_blank+c_label)) - lse*log2(e):
       // the occupation factor rides in the exponent (one MUFU per logit, no multiply). The two
       // one-hot entries of a row are not selected out of the register tile; their exact values
@@ -312,6 +312,17 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
             }
             s = s * ex2_approx(m - mn) + ((a0 + a1) + (a2 + a3));
             m = mn;
+            // the blank / label logits: a dynamically indexed read of the chunk through a small
+            // local array, only in the rare chunk that holds one of them (selecting with 16
+            // compare+select pairs per chunk cost ~7 % of the epilogue's issue slots)
+            const bool hit_b = (unsigned)(p.blank - col0) < 16u, hit_l = (unsigned)(label - col0) < 16u;
+            if (hit_b || hit_l) {
+              float tmp[16];
+#pragma unroll
+              for (int j = 0; j < 16; ++j) tmp[j] = zc[j];
+              if (hit_b) zb = tmp[(p.blank - col0) & 15];
+              if (hit_l) zl = tmp[(label - col0) & 15];
+            }
           } else {
             uint32_t gp[8];
 #pragma unroll
@@ -395,22 +406,19 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         }
       }
       if (MODE == 0) {
-        // merge the two column halves; the blank / label logits come from hidden_kernel
-        // (log2 domain, stored in the lp planes), so no register-tile selection is needed here
-        if (half == 1) red2[row] = make_float2(m, s);
+        // merge the two column halves (each holds zb / zl only if it swept that column)
+        if (half == 1) red4[row] = make_float4(m, s, zb, zl);
         named_bar_sync(1, kEpiWarps * 32);
         if (half == 0 && rc.valid) {
-          const float2 o = red2[row];
+          const float4 o = red4[row];
           const float mn = fmaxf(m, o.x);
           const float st = s * ex2_approx(m - mn) + o.y * ex2_approx(o.x - mn);
           const float lse2 = mn + log2f(st);
-          const float zb = p.lpb[pidx];
-          const float zl = p.lpl[pidx];
           p.lse[pidx] = lse2 * RNNT_LN2;
-          p.lpb[pidx] = (zb - lse2) * RNNT_LN2;
-          p.lpl[pidx] = (label >= 0) ? (zl - lse2) * RNNT_LN2 : -INFINITY;
+          p.lpb[pidx] = (zb + o.z - lse2) * RNNT_LN2;
+          p.lpl[pidx] = (label >= 0) ? (zl + o.w - lse2) * RNNT_LN2 : -INFINITY;
         }
-        named_bar_sync(1, kEpiWarps * 32);  // red2[] is free again
+        named_bar_sync(1, kEpiWarps * 32);  // red4[] is free again
       }
     }
     if (MODE == 1) {
@@ -424,33 +432,37 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         for (size_t i = epi_tid; i < n16; i += kEpiWarps * 32) dst[i] = make_uint4(0, 0, 0, 0);
       }
     }
-  } else if (warp == 8) {
-    // =========================== TMA PRODUCER (W2) ===========================
+  } else if (warp == 8 || warp == 11) {
+    // =========================== TMA PRODUCERS (W2) ===========================
     // One ring slot = this CTA's BN/2 rows of one 64-wide K block; the leader's b_full collects
-    // both CTAs' bytes (2 arrivals + 2 x kSlotBytes).
+    // both CTAs' bytes (2 arrivals + 2 x kSlotBytes). Two producer warps take alternate K blocks
+    // (a single producer needed ~600 clk per slot -- wait, expect_tx, TMA issue -- against the
+    // 512 clk the MMAs of a slot take, and starved the issuer: profiles/r01_notes.md).
     if (lane == 0) {
-      uint32_t slot = 0, phase = 0;
+      const int parity = (warp == 8) ? 0 : 1;
+      const uint32_t nslot = (uint32_t)p.slots;
+      uint32_t slot = (uint32_t)parity % nslot, phase = ((uint32_t)parity / nslot) & 1;
+      int kb = parity, pt = cid, vt = cid % NV, vleft = NV;  // vleft: vocabulary tiles left in this lattice tile
+      while (kb >= KB) { kb -= KB; vt = (vt + 1 == NV) ? 0 : vt + 1; if (--vleft == 0) { vleft = NV; pt += ncl; } }
       int tr_n = 0;
-      for (int pt = cid; pt < n_pairs; pt += ncl) {
-        for (int vi = 0; vi < NV; ++vi) {
-          const int vt = (vi + cid) % NV;
-          const int row0 = vt * BN + (int)rank * (((vt == NV - 1) ? n_last : BN) / 2);
-          for (int kb = 0; kb < KB; ++kb) {
-            const long long tr0 = p.trace ? clock64() : 0;
-            mbar_wait(&ctl->b_empty[slot], phase ^ 1);
-            const long long tr1 = p.trace ? clock64() : 0;
-            const uint32_t full = mapa_u32(smem_u32(&ctl->b_full[slot]), 0);
-            if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[slot], 2 * kSlotBytes);
-            else mbar_arrive_cluster(full);
-            tma_load_2d_pair(smem_b + slot * kSlotBytes, &map_w2, full, kb * kKBlock, row0);
-            if (p.trace && blockIdx.x == 0 && tr_n < 4096) {
-              long long* t = p.trace + 3 * 4096;
-              t[3 * tr_n + 0] = tr0; t[3 * tr_n + 1] = tr1; t[3 * tr_n + 2] = clock64();
-              ++tr_n;
-            }
-            if (++slot == (uint32_t)p.slots) { slot = 0; phase ^= 1; }
-          }
+      while (pt < n_pairs) {
+        const int row0 = vt * BN + (int)rank * (((vt == NV - 1) ? n_last : BN) / 2);
+        const long long tr0 = p.trace ? clock64() : 0;
+        mbar_wait(&ctl->b_empty[slot], phase ^ 1);
+        const long long tr1 = p.trace ? clock64() : 0;
+        const uint32_t full = mapa_u32(smem_u32(&ctl->b_full[slot]), 0);
+        if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[slot], 2 * kSlotBytes);
+        else mbar_arrive_cluster(full);
+        tma_load_2d_pair(smem_b + slot * kSlotBytes, &map_w2, full, kb * kKBlock, row0);
+        if (p.trace && blockIdx.x == 0 && parity == 0 && tr_n < 4096) {
+          long long* t = p.trace + 3 * 4096;
+          t[3 * tr_n + 0] = tr0; t[3 * tr_n + 1] = tr1; t[3 * tr_n + 2] = clock64();
+          ++tr_n;
         }
+        slot += 2;
+        while (slot >= nslot) { slot -= nslot; phase ^= 1; }
+        kb += 2;
+        while (kb >= KB) { kb -= KB; vt = (vt + 1 == NV) ? 0 : vt + 1; if (--vleft == 0) { vleft = NV; pt += ncl; } }
       }
     }
   } else if (warp == 10) {
@@ -541,67 +553,46 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
 
 // ---------------------------------------------------------------------------------------
 // h = bf16(tanh(P_enc[t] + P_dec[u])) for every tile row; the decomposed first joint layer
-// (model.py:26-34 without the repeat/cat). One CTA per tile, one warp per row at a time
-// (lane l owns the 16-byte chunks l, l+32, ... of the row: 2x16 B loads from each addend, one
-// 16 B store per chunk). Rows past an utterance's last cell and tiles past the table are written
-// as zeros; column H of the 8-wide row tail is 1.0 for valid cells (the "ones" column that makes
-// the library GEMM dS^T . h_ext produce d b2 next to dW2). The same pass takes the dot products of the (bf16-rounded) row with the blank and
-// the label rows of W2 -- the two logits the loss needs per cell -- and leaves them, in the log2
-// domain with the bias, in the lp_blank / lp_label planes, where the forward GEMM's epilogue turns
-// them into log-probabilities once it knows the row's log-sum-exp. (Selecting them out of the
-// GEMM's register tiles cost ~7 % of the epilogue's issue slots.)
+// (model.py:26-34 without the repeat/cat). One CTA per tile, 64 threads per row (each 8
+// consecutive k: 2x16 B loads from each addend, one 16 B store), 4 rows in flight per pass.
+// Rows past an utterance's last cell and tiles past the table are written as zeros;
+// column H of the 8-wide tail is 1.0 for valid cells (the "ones" column that makes the library
+// GEMM dS^T.h_ext produce d b2 next to dW2). MUFU-bound: two MUFU ops per tanh.
+// (Taking the blank/label logits here as dot products with two W2 rows doubled this kernel's
+// time -- 0.45 -> 1.03 ms -- and was dropped again.)
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 hidden_kernel(const JointParams p, int max_tiles) {
   const int n_tiles = min(p.n_tiles[0], max_tiles);
-  const int cpr = p.H / 8;  // 16-byte chunks per row
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint4* wb4 = reinterpret_cast<const uint4*>(p.w2q + (size_t)p.blank * p.H);
+  const int hp = p.H + 8;
+  const int cpr = p.H / 8;            // 16-byte chunks per row
+  const int rows_per_pass = 256 / cpr;  // H=512: 4 rows per pass
+  const int chunk = threadIdx.x % cpr;
+  const int rsub = threadIdx.x / cpr;
   for (int tile = blockIdx.x; tile < max_tiles; tile += gridDim.x) {
     const bool dead = tile >= n_tiles;
-    const int hp = p.H + 8;  // columns H..H+7 = [1, 0, ..] for valid cells: dS^T . h_ext = [dW2 | db2 | 0]
     __nv_bfloat16* dst_tile = p.h_stash + (size_t)tile * RNNT_TILE_M * hp;
+    if (threadIdx.x < RNNT_TILE_M) {
+      const RowCoord rc = locate_row(p, tile, threadIdx.x, dead);
+      *reinterpret_cast<uint4*>(dst_tile + (size_t)threadIdx.x * hp + p.H) =
+          make_uint4(rc.valid ? 0x00003F80u : 0u, 0u, 0u, 0u);
+    }
+    if (rsub < rows_per_pass) {
 #pragma unroll 2
-    for (int row = warp; row < RNNT_TILE_M; row += 8) {
-      const RowCoord rc = locate_row(p, tile, row, dead);
-      int label = -1;
-      if (rc.valid && rc.u < rc.Ub) label = clamp_int(p.labels[(size_t)rc.b * (p.U1 - 1) + rc.u], 0, p.V - 1);
-      const uint4* wl4 = reinterpret_cast<const uint4*>(p.w2q + (size_t)(label >= 0 ? label : p.blank) * p.H);
-      float accb = 0.f, accl = 0.f;
-      for (int ch = lane; ch < cpr; ch += 32) {
+      for (int r0 = 0; r0 < RNNT_TILE_M; r0 += rows_per_pass) {
+        const int row = r0 + rsub;
+        const RowCoord rc = locate_row(p, tile, row, dead);
         uint4 o = make_uint4(0u, 0u, 0u, 0u);
         if (rc.valid) {
-          const float4* e4 = reinterpret_cast<const float4*>(p.pe + ((size_t)rc.b * p.T + rc.t) * p.H) + ch * 2;
-          const float4* d4 = reinterpret_cast<const float4*>(p.pd + ((size_t)rc.b * p.U1 + rc.u) * p.H) + ch * 2;
+          const float4* e4 = reinterpret_cast<const float4*>(p.pe + ((size_t)rc.b * p.T + rc.t) * p.H) + chunk * 2;
+          const float4* d4 = reinterpret_cast<const float4*>(p.pd + ((size_t)rc.b * p.U1 + rc.u) * p.H) + chunk * 2;
           const float4 e0 = __ldg(e4), e1 = __ldg(e4 + 1), d0 = __ldg(d4), d1 = __ldg(d4 + 1);
-          const uint4 wb = __ldg(wb4 + ch), wl = __ldg(wl4 + ch);
           o.x = pack_bf16x2(tanh_accurate(e0.x + d0.x), tanh_accurate(e0.y + d0.y));
           o.y = pack_bf16x2(tanh_accurate(e0.z + d0.z), tanh_accurate(e0.w + d0.w));
           o.z = pack_bf16x2(tanh_accurate(e1.x + d1.x), tanh_accurate(e1.y + d1.y));
           o.w = pack_bf16x2(tanh_accurate(e1.z + d1.z), tanh_accurate(e1.w + d1.w));
-          const uint32_t hw[4] = {o.x, o.y, o.z, o.w};
-          const uint32_t bw[4] = {wb.x, wb.y, wb.z, wb.w};
-          const uint32_t lw[4] = {wl.x, wl.y, wl.z, wl.w};
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float2 hf = unpack_bf16x2(hw[j]), bf = unpack_bf16x2(bw[j]), lf = unpack_bf16x2(lw[j]);
-            accb = fmaf(hf.x, bf.x, accb); accb = fmaf(hf.y, bf.y, accb);
-            accl = fmaf(hf.x, lf.x, accl); accl = fmaf(hf.y, lf.y, accl);
-          }
         }
-        *reinterpret_cast<uint4*>(dst_tile + (size_t)row * hp + ch * 8) = o;
-      }
-      if (lane == 0)
-        *reinterpret_cast<uint4*>(dst_tile + (size_t)row * hp + p.H) = make_uint4(rc.valid ? 0x00003F80u : 0u, 0u, 0u, 0u);
-#pragma unroll
-      for (int sh = 16; sh > 0; sh >>= 1) {
-        accb += __shfl_xor_sync(0xffffffffu, accb, sh);
-        accl += __shfl_xor_sync(0xffffffffu, accl, sh);
-      }
-      if (rc.valid && lane == 0) {
-        const size_t pidx = plane_index(rc.b, rc.t, rc.u, p.T, p.U1);
-        p.lpb[pidx] = fmaf(accb, RNNT_LOG2E, p.b2l[p.blank]);
-        p.lpl[pidx] = fmaf(accl, RNNT_LOG2E, p.b2l[label >= 0 ? label : p.blank]);
+        *reinterpret_cast<uint4*>(dst_tile + (size_t)row * hp + chunk * 8) = o;
       }
     }
   }

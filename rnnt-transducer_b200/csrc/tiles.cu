@@ -38,17 +38,30 @@ pack_vocab_kernel(const float* __restrict__ w2, const float* __restrict__ b2, in
   }
 }
 
-// dpre = dh * (1 - h^2) and its two reductions. One CTA per (utterance b, block of TT lattice
-// rows t); thread k owns hidden columns 2k, 2k+1 (bf16x2 loads, 128 B per warp and row). The u
-// loop is outermost so that the sum over the block's t rows for dP_dec[b,u,:] lives in a
-// register and costs ONE float2 red per (CTA,u); the TT partial sums for dP_enc[b,t,:] stay in
-// registers for the whole sweep (the u range is additionally split DH_US ways over gridDim.z). Cells of an utterance are contiguous in the tile-packed row
-// order, so row(t,u) = first_tile_b*128 + t*(U_b+1) + u; a launch covers the packed rows of
-// tiles [tile_lo, tile_hi) only (the caller stages dS/dh in chunks), hence the atomics on dP_enc.
+// dpre = dh * (1 - h^2) and its two reductions. One CTA per (utterance b, block of DH_TT lattice
+// rows t). A thread owns 8 consecutive hidden columns (16-byte bf16 loads), H/8 threads span a
+// packed row and the 256/(H/8) row lanes of the CTA take u = lane, lane + lanes, ...  The u loop
+// is outermost so that the sum over the block's t rows for dP_dec[b,u,:] lives in registers and
+// costs two float4 reductions per (row lane, u); the DH_TT partial sums for dP_enc[b,t,:] stay in
+// registers for the whole sweep and are reduced into memory at the end. All 2*DH_TT loads of an
+// iteration are unconditional (masked cells are redirected to a row that is always inside the
+// window) and issue back to back. Cells of an utterance are
+// contiguous in the tile-packed row order, so row(t,u) = first_tile_b*128 + t*(U_b+1) + u; a launch
+// covers the packed rows of tiles [tile_lo, tile_hi) only (the caller stages dS/dh in chunks),
+// hence the atomics on dP_enc.
 constexpr int DH_TT = 8;
-constexpr int DH_US = 4;  // u range split over gridDim.z: the u loop is a serial latency chain
 
-__global__ void __launch_bounds__(256, 4)
+__device__ __forceinline__ void unpack8(const uint4& w, float (&f)[8]) {
+  const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&ww[j]));
+    f[2 * j] = v.x;
+    f[2 * j + 1] = v.y;
+  }
+}
+
+__global__ void __launch_bounds__(256, 2)
 dh_reduce_kernel(const __nv_bfloat16* __restrict__ dh, const __nv_bfloat16* __restrict__ h,
                  const int32_t* __restrict__ act_lens, const int32_t* __restrict__ label_lens,
                  int T, int U1, int H, int tile_lo, int tile_hi, float dh_scale,
@@ -69,46 +82,60 @@ dh_reduce_kernel(const __nv_bfloat16* __restrict__ dh, const __nv_bfloat16* __re
   const int nt = min(DH_TT, Tb - t0);
   const long long c_first = (long long)t0 * w, c_last = (long long)(t0 + nt) * w;
   if (c_last <= lo || c_first >= hi) return;
-  const int k2 = threadIdx.x;  // column pair
+  const int cpr = H / 8;              // 16-byte chunks per row
+  const int lanes = 256 / cpr;        // row lanes of the CTA
+  const int chunk = threadIdx.x % cpr;
+  const int rl = threadIdx.x / cpr;
+  if (rl >= lanes) return;
   const int hp = H + 8;
-  const __nv_bfloat162* dh2 = reinterpret_cast<const __nv_bfloat162*>(dh) + k2;
-  const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(h) + k2;
-  float2 acc_e[DH_TT];
+  const uint4* dh4 = reinterpret_cast<const uint4*>(dh) + chunk;                // row pitch H/8 uint4
+  const uint4* h4 = reinterpret_cast<const uint4*>(h + (size_t)first_tile * RNNT_TILE_M * hp) + chunk;  // pitch hp/8
+  float acc_e[DH_TT][8];
 #pragma unroll
-  for (int i = 0; i < DH_TT; ++i) acc_e[i] = make_float2(0.f, 0.f);
-  const int u_per = (w + DH_US - 1) / DH_US;
-  const int u_lo = blockIdx.z * u_per, u_hi = min(w, u_lo + u_per);
-  // a row that is always inside the window (loads of masked-out cells are redirected to it so
-  // that all 2*DH_TT loads of an iteration are unconditional and issue back to back)
+  for (int i = 0; i < DH_TT; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc_e[i][j] = 0.f;
+  // a row that is always inside the window
   const long long c_safe = max(c_first, lo);
-  for (int u = u_lo; u < u_hi; ++u) {
-    __nv_bfloat162 g[DH_TT], hv[DH_TT];
-    bool ok[DH_TT];
+  for (int u = rl; u < w; u += lanes) {
+    float acc_d[8];
 #pragma unroll
-    for (int i = 0; i < DH_TT; ++i) {
-      const long long c = (long long)(t0 + i) * w + u;
-      ok[i] = (i < nt) && c >= lo && c < hi;
-      const long long cc = ok[i] ? c : c_safe;
-      g[i] = dh2[(size_t)(cc - lo) * (H / 2)];
-      hv[i] = h2[((size_t)first_tile * RNNT_TILE_M + cc) * (hp / 2)];
-    }
-    float2 acc_d = make_float2(0.f, 0.f);
+    for (int j = 0; j < 8; ++j) acc_d[j] = 0.f;
 #pragma unroll
-    for (int i = 0; i < DH_TT; ++i) {
-      const float2 gf = __bfloat1622float2(g[i]), hf = __bfloat1622float2(hv[i]);
-      const float vx = ok[i] ? gf.x * (1.f - hf.x * hf.x) : 0.f;
-      const float vy = ok[i] ? gf.y * (1.f - hf.y * hf.y) : 0.f;
-      acc_d.x += vx; acc_d.y += vy;
-      acc_e[i].x += vx; acc_e[i].y += vy;
+    for (int i0 = 0; i0 < DH_TT; i0 += 4) {  // two batches of 4 rows: 8 x 16 bytes in flight per thread
+      uint4 g[4], hv[4];
+      bool ok[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const long long c = (long long)(t0 + i0 + i) * w + u;
+        ok[i] = (i0 + i < nt) && c >= lo && c < hi;
+        const long long cc = ok[i] ? c : c_safe;
+        g[i] = __ldg(dh4 + (size_t)(cc - lo) * (H / 8));
+        hv[i] = __ldg(h4 + (size_t)cc * (hp / 8));
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float gf[8], hf[8];
+        unpack8(g[i], gf);
+        unpack8(hv[i], hf);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float v = ok[i] ? gf[j] * (1.f - hf[j] * hf[j]) : 0.f;
+          acc_d[j] += v;
+          acc_e[i0 + i][j] += v;
+        }
+      }
     }
-    acc_d.x *= dh_scale; acc_d.y *= dh_scale;
-    atomicAdd(reinterpret_cast<float2*>(dpd + ((size_t)b * U1 + u) * H) + k2, acc_d);
+    float4* dst = reinterpret_cast<float4*>(dpd + ((size_t)b * U1 + u) * H + chunk * 8);
+    atomicAdd(dst, make_float4(acc_d[0] * dh_scale, acc_d[1] * dh_scale, acc_d[2] * dh_scale, acc_d[3] * dh_scale));
+    atomicAdd(dst + 1, make_float4(acc_d[4] * dh_scale, acc_d[5] * dh_scale, acc_d[6] * dh_scale, acc_d[7] * dh_scale));
   }
 #pragma unroll
   for (int i = 0; i < DH_TT; ++i)
     if (i < nt) {
-      acc_e[i].x *= dh_scale; acc_e[i].y *= dh_scale;
-      atomicAdd(reinterpret_cast<float2*>(dpe + ((size_t)b * T + t0 + i) * H) + k2, acc_e[i]);
+      float4* dst = reinterpret_cast<float4*>(dpe + ((size_t)b * T + t0 + i) * H + chunk * 8);
+      atomicAdd(dst, make_float4(acc_e[i][0] * dh_scale, acc_e[i][1] * dh_scale, acc_e[i][2] * dh_scale, acc_e[i][3] * dh_scale));
+      atomicAdd(dst + 1, make_float4(acc_e[i][4] * dh_scale, acc_e[i][5] * dh_scale, acc_e[i][6] * dh_scale, acc_e[i][7] * dh_scale));
     }
 }
 
@@ -175,7 +202,7 @@ extern "C" int rnnt_b200_dh_reduce(const void* dh_bf16, const void* h_stash, con
       tile_hi < tile_lo)
     return RNNT_B200_E_SHAPE;
   if (tile_hi == tile_lo) return RNNT_B200_OK;
-  dh_reduce_kernel<<<dim3((T + DH_TT - 1) / DH_TT, B, DH_US), H / 2, 0, (cudaStream_t)stream>>>(
+  dh_reduce_kernel<<<dim3((T + DH_TT - 1) / DH_TT, B), 256, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)dh_bf16, (const __nv_bfloat16*)h_stash, act_lens, label_lens, T, U1, H, tile_lo,
       tile_hi, dh_scale, dp_enc, dp_dec);
   RNNT_CUDA_RETURN_IF_ERROR();
