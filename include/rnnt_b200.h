@@ -122,22 +122,29 @@ int rnnt_b200_h_pitch(int H);
  * Vpad padding. Columns V..pitch-1 are written as zeros. */
 int rnnt_b200_ds_pitch(int V);
 
-/* Fused forward: tcgen05/TMEM GEMM  tanh(P_enc[t]+P_dec[u]) . W2^T  with an online
- * log-sum-exp epilogue; writes lse / lp_blank / lp_label planes only.
- * h_stash: bf16 workspace (max_tiles*128, rnnt_b200_h_pitch(H)), 128-byte aligned: written first with
- * h = tanh(P_enc[t]+P_dec[u]) by a streaming kernel, then read as the GEMM's A operand by TMA;
- * the backward reads it again.
+/* Hidden activations of the joint: h = bf16(tanh(P_enc[b,t,:] + P_dec[b,u,:])) for every valid
+ * lattice cell, tile-packed (model.py:26-34 without the repeat/cat): row tile*128 + r of h_stash is
+ * cell tile_cell0[tile] + r of utterance tile_utt[tile]; rows past an utterance's last cell and
+ * tiles past the table are zeros; column H is 1.0 for valid cells.
+ * h_stash: bf16 workspace (tile_cap*128, rnnt_b200_h_pitch(H)), 128-byte aligned. It is the A
+ * operand of rnnt_b200_joint_fwd / _bwd_ds (TMA) and an operand of the backward library GEMMs. */
+int rnnt_b200_joint_hidden(const float* p_enc, const float* p_dec,
+                           const int32_t* act_lens, const int32_t* label_lens,
+                           const int32_t* tile_utt, const int32_t* tile_cell0, const int32_t* n_tiles,
+                           int B, int T, int U1, int H, int tile_cap, void* h_stash, void* stream);
+
+/* Fused forward: tcgen05/TMEM GEMM  h . W2^T  with an online log-sum-exp epilogue; writes
+ * lse / lp_blank / lp_label planes only. h_stash as written by rnnt_b200_joint_hidden.
  * tile_cap: number of tiles the tile-indexed workspaces (h_stash, tile table) are sized for;
  * rnnt_b200_max_tiles(B,T,U1) when the lengths are only known on the device, or the exact
  * sum_b ceil(T_b*(U_b+1)/128) when the caller also has them on the host (skips all padded work).
  * It must not be smaller than the number of tiles actually present. */
-int rnnt_b200_joint_fwd(const float* p_enc, const float* p_dec,
+int rnnt_b200_joint_fwd(const void* h_stash,
                         const void* w2_bf16, const float* b2_log2,
                         const int32_t* labels, const int32_t* act_lens, const int32_t* label_lens,
                         const int32_t* tile_utt, const int32_t* tile_cell0, const int32_t* n_tiles,
                         int B, int T, int U1, int V, int H, int blank, int tile_cap,
-                        float* lse, float* lp_blank, float* lp_label,
-                        void* h_stash, void* stream);
+                        float* lse, float* lp_blank, float* lp_label, void* stream);
 
 /* Fused backward, stage 1: recompute logits tiles from h_stash on the tensor cores and
  * emit dS = scale_b*(softmax*(c_blank+c_label) - onehots) as bf16 for tiles

@@ -47,7 +47,7 @@ class KernelTimer:
     active = None
     # kernels launched per C-ABI call
     KERNELS = {"logits_to_planes": 1, "lattice": 2, "planes_to_dlogits": 1, "build_tiles": 1,
-               "pack_vocab": 1, "joint_fwd": 1, "joint_bwd_ds": 1, "dh_reduce": 1}
+               "pack_vocab": 1, "joint_hidden": 1, "joint_fwd": 1, "joint_bwd_ds": 1, "dh_reduce": 1}
 
     def __init__(self, events: bool = True):
         self.events = events
@@ -272,10 +272,12 @@ class _JointLossFn(torch.autograd.Function):
             lpl = torch.empty(n, dtype=torch.float32, device=dev)
             # bf16 hidden activations, tile-packed (M x (H+8), never M x V): the GEMM's A operand
             h_stash = torch.empty(max_tiles * 128, L.rnnt_b200_h_pitch(H), dtype=torch.bfloat16, device=dev)
-            _call("joint_fwd", L.rnnt_b200_joint_fwd, _ptr(pe), _ptr(pd), _ptr(w2q), _ptr(b2l), _ptr(labels),
+            _call("joint_hidden", L.rnnt_b200_joint_hidden, _ptr(pe), _ptr(pd), _ptr(act_lens), _ptr(label_lens),
+                  _ptr(tile_utt), _ptr(tile_cell0), _ptr(n_tiles), B, T, U1, H, max_tiles, _ptr(h_stash), st)
+            _call("joint_fwd", L.rnnt_b200_joint_fwd, _ptr(h_stash), _ptr(w2q), _ptr(b2l), _ptr(labels),
                                              _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt),
                                              _ptr(tile_cell0), _ptr(n_tiles), B, T, U1, V, H, blank, max_tiles,
-                                             _ptr(lse), _ptr(lpb), _ptr(lpl), _ptr(h_stash), st)
+                                             _ptr(lse), _ptr(lpb), _ptr(lpl), st)
             loss, cb, cl = _lattice(lpb, lpl, act_lens, label_lens, B, T, U1)
         if need_grad:
             ctx.save_for_backward(labels, act_lens, label_lens, tile_utt, tile_cell0, n_tiles, w2q, b2l,

@@ -31,7 +31,8 @@ SIGNATURES = {
     "rnnt_b200_pack_vocab": (_i, [_p, _p, _i, _i, _p, _p, _p]),
     "rnnt_b200_h_pitch": (_i, [_i]),
     "rnnt_b200_ds_pitch": (_i, [_i]),
-    "rnnt_b200_joint_fwd": (_i, [_p] * 10 + [_i] * 7 + [_p] * 5),
+    "rnnt_b200_joint_hidden": (_i, [_p] * 7 + [_i] * 5 + [_p, _p]),
+    "rnnt_b200_joint_fwd": (_i, [_p] * 9 + [_i] * 7 + [_p] * 4),
     "rnnt_b200_joint_bwd_ds": (_i, [_p] * 15 + [_i] * 9 + [_p, _p]),
     "rnnt_b200_dh_reduce": (_i, [_p] * 4 + [_i] * 6 + [ctypes.c_float] + [_p, _p, _p]),
     "rnnt_b200_selftest_gemm": (_i, [_p, _p, _p, _i, _i, _i, _p]),

@@ -831,33 +831,49 @@ int check_common(int B, int T, int U1, int V, int H, int blank) {
 
 }  // namespace
 
-extern "C" int rnnt_b200_joint_fwd(const float* p_enc, const float* p_dec, const void* w2_bf16,
+extern "C" int rnnt_b200_joint_hidden(const float* p_enc, const float* p_dec, const int32_t* act_lens,
+                                      const int32_t* label_lens, const int32_t* tile_utt,
+                                      const int32_t* tile_cell0, const int32_t* n_tiles, int B, int T, int U1,
+                                      int H, int tile_cap, void* h_stash, void* stream) {
+  if (!p_enc || !p_dec || !act_lens || !label_lens || !tile_utt || !tile_cell0 || !n_tiles || !h_stash)
+    return RNNT_B200_E_NULL;
+  int rc = check_common(B, T, U1, 1, H, 0);
+  if (rc) return rc;
+  if (((uintptr_t)p_enc & 15) || ((uintptr_t)p_dec & 15) || ((uintptr_t)h_stash & 127)) return RNNT_B200_E_ALIGN;
+  if (tile_cap < 1 || tile_cap > rnnt_b200_max_tiles(B, T, U1)) return RNNT_B200_E_SHAPE;
+  JointParams p = {};
+  p.pe = p_enc; p.pd = p_dec; p.act_lens = act_lens; p.label_lens = label_lens;
+  p.tile_utt = tile_utt; p.tile_cell0 = tile_cell0; p.n_tiles = n_tiles; p.h_stash = (__nv_bfloat16*)h_stash;
+  p.B = B; p.T = T; p.U1 = U1; p.H = H;
+  const int sms = sm_count();
+  const int grid = tile_cap < sms * 8 ? tile_cap : sms * 8;
+  hidden_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p, tile_cap);
+  RNNT_CUDA_RETURN_IF_ERROR();
+  return RNNT_B200_OK;
+}
+
+extern "C" int rnnt_b200_joint_fwd(const void* h_stash, const void* w2_bf16,
                                    const float* b2_log2, const int32_t* labels, const int32_t* act_lens,
                                    const int32_t* label_lens, const int32_t* tile_utt,
                                    const int32_t* tile_cell0, const int32_t* n_tiles, int B, int T, int U1,
                                    int V, int H, int blank, int tile_cap, float* lse, float* lp_blank,
-                                   float* lp_label, void* h_stash, void* stream) {
-  if (!p_enc || !p_dec || !w2_bf16 || !b2_log2 || !act_lens || !label_lens || !tile_utt || !tile_cell0 ||
-      !n_tiles || !lse || !lp_blank || !lp_label || !h_stash)
+                                   float* lp_label, void* stream) {
+  if (!h_stash || !w2_bf16 || !b2_log2 || !act_lens || !label_lens || !tile_utt || !tile_cell0 ||
+      !n_tiles || !lse || !lp_blank || !lp_label)
     return RNNT_B200_E_NULL;
   if (U1 > 1 && !labels) return RNNT_B200_E_NULL;
   int rc = check_common(B, T, U1, V, H, blank);
   if (rc) return rc;
-  if (((uintptr_t)p_enc & 15) || ((uintptr_t)p_dec & 15) || ((uintptr_t)w2_bf16 & 127) ||
-      ((uintptr_t)b2_log2 & 15) || ((uintptr_t)h_stash & 127))
+  if (((uintptr_t)w2_bf16 & 127) || ((uintptr_t)b2_log2 & 15) || ((uintptr_t)h_stash & 127))
     return RNNT_B200_E_ALIGN;
   JointParams p = {};
-  p.pe = p_enc; p.pd = p_dec; p.w2q = (const __nv_bfloat16*)w2_bf16; p.b2l = b2_log2; p.labels = labels; p.act_lens = act_lens;
+  p.w2q = (const __nv_bfloat16*)w2_bf16; p.b2l = b2_log2; p.labels = labels; p.act_lens = act_lens;
   p.label_lens = label_lens; p.tile_utt = tile_utt; p.tile_cell0 = tile_cell0; p.n_tiles = n_tiles;
-  p.lse = lse; p.lpb = lp_blank; p.lpl = lp_label; p.h_stash = (__nv_bfloat16*)h_stash;
+  p.lse = lse; p.lpb = lp_blank; p.lpl = lp_label;
+  p.h_stash = (__nv_bfloat16*)const_cast<void*>(h_stash);
   p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vpad = rnnt_b200_vocab_pad(V); p.Vds = rnnt_b200_ds_pitch(V); p.H = H; p.blank = blank;
   if (tile_cap < 1 || tile_cap > rnnt_b200_max_tiles(B, T, U1)) return RNNT_B200_E_SHAPE;
   p.tile_lo = 0; p.tile_hi = tile_cap;
-  {
-    int grid = p.tile_hi < 148 * 8 ? p.tile_hi : 148 * 8;
-    hidden_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p, p.tile_hi);
-    RNNT_CUDA_RETURN_IF_ERROR();
-  }
   return dispatch_joint<0>(p, w2_bf16, h_stash, p.tile_hi, (cudaStream_t)stream);
 }
 

@@ -50,8 +50,12 @@ def test_c_abi_rejects_bad_arguments_without_launching():
     one = ctypes.c_void_p(16)
     assert L.rnnt_b200_logits_to_planes(one, one, one, one, 1, 1, 1, 4, 7, one, one, one, None) == -3
     assert L.rnnt_b200_lattice(one, one, one, one, 1, 4, 2000, one, one, one, one, one, None, None) == -2
-    assert L.rnnt_b200_joint_fwd(one, one, one, one, one, one, one, one, one, one,
-                                 1, 4, 2, 10, 100, 0, 1, one, one, one, one, None) == -2   # H % 64
+    assert L.rnnt_b200_joint_fwd(one, one, one, one, one, one, one, one, one,
+                                 1, 4, 2, 10, 100, 0, 1, one, one, one, None) == -2   # H % 64
+    assert L.rnnt_b200_joint_hidden(one, one, one, one, one, one, one, 1, 4, 2, 100, 1, one, None) == -2
+    al = ctypes.c_void_p(256)
+    assert L.rnnt_b200_joint_hidden(al, al, one, one, one, one, one, 1, 4, 2, 64, 99, al, None) == -2  # tile_cap
+    assert L.rnnt_b200_joint_hidden(al, al, one, one, one, one, one, 1, 4, 2, 64, 1, one, None) == -4  # h_stash alignment
 
 
 def test_rnntloss_is_dropin_constructible_and_validates():
