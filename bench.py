@@ -249,17 +249,35 @@ def main():
     # ---------------- end to end through the public API with HOST buffers (e2e) ----------------
     loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
 
+    # Host inputs are staged the way a training loop's loader does it: the pinned batch of step
+    # i+1 is copied on a side stream while step i computes (every step still copies its own inputs
+    # host->device inside the timed region and reads its loss back).
+    copy_stream = torch.cuda.Stream()
+    main_stream = torch.cuda.current_stream()
+    pending = []
+
+    def stage_inputs():
+        with torch.cuda.stream(copy_stream):
+            ts = [t.to(dev, non_blocking=True) for t in (h_enc, h_dec, h_y, h_tl, h_ul)]
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+        pending.append((ts, ev))
+
     def step_e2e():
-        enc = h_enc.to(dev, non_blocking=True)
-        dec = h_dec.to(dev, non_blocking=True)
-        yy = h_y.to(dev, non_blocking=True)
-        tll = h_tl.to(dev, non_blocking=True)
-        ull = h_ul.to(dev, non_blocking=True)
-        l = step(enc, dec, yy, tll, ull)
+        if not pending:
+            stage_inputs()
+        ts, ev = pending.pop(0)
+        main_stream.wait_event(ev)
+        for t in ts:
+            t.record_stream(main_stream)
+        stage_inputs()                       # next step's batch, overlapped with this step
+        l = step(*ts)
         loss_host.copy_(l.reshape(1), non_blocking=True)
         return l
 
     step_e2e()
+    torch.cuda.synchronize()
+    pending.clear()                          # the timed region starts with no copy in flight
     ms_e2e, _ = timed(step_e2e, args.steps)
     h2d = sum(t.numel() * t.element_size() for t in (h_enc, h_dec, h_y, h_tl, h_ul))
 
