@@ -110,10 +110,12 @@ int rnnt_b200_vocab_tile(int V);
 int rnnt_b200_pack_vocab(const float* w2, const float* b2, int V, int H,
                          void* w2_bf16, float* b2_log2, void* stream);
 
-/* Row pitch (elements) of the stashed hidden activations h: H + 8. Column H holds 1.0 for valid
- * cells so that the library GEMM dS^T . h_ext yields d b2 in its last column block. (Column sums
- * inside the dS kernel were tried -- shuffles, legacy warp MMA + reductions -- and cost more than
- * the N = H+8 GEMM shape: profiles/r01_notes.md.) */
+/* Row pitch (elements) of the stashed hidden activations h: H + 32. Column H holds 1.0 for valid
+ * cells (columns H+1..H+7 zero, H+8.. unwritten) so that the library GEMM h_ext^T . dS yields d b2
+ * in row H of its output. (Column sums inside the dS kernel -- shuffles, legacy warp MMA +
+ * reductions -- and a separate column-sum pass over dS were tried and cost more than the wider
+ * GEMM shape; pitch H+32 is the fastest of the widths the library was tried with:
+ * profiles/r01_notes.md.) */
 int rnnt_b200_h_pitch(int H);
 
 /* Row pitch (elements) of the staged bf16 logit gradient dS: V rounded up to 64 (128-byte rows;

@@ -270,7 +270,7 @@ class _JointLossFn(torch.autograd.Function):
             lse = torch.empty(n, dtype=torch.float32, device=dev)
             lpb = torch.empty(n, dtype=torch.float32, device=dev)
             lpl = torch.empty(n, dtype=torch.float32, device=dev)
-            # bf16 hidden activations, tile-packed (M x (H+8), never M x V): the GEMM's A operand
+            # bf16 hidden activations, tile-packed (M x h_pitch, never M x V): the GEMM's A operand
             h_stash = torch.empty(max_tiles * 128, L.rnnt_b200_h_pitch(H), dtype=torch.bfloat16, device=dev)
             _call("joint_hidden", L.rnnt_b200_joint_hidden, _ptr(pe), _ptr(pd), _ptr(act_lens), _ptr(label_lens),
                   _ptr(tile_utt), _ptr(tile_cell0), _ptr(n_tiles), B, T, U1, H, max_tiles, _ptr(h_stash), st)
@@ -297,7 +297,8 @@ class _JointLossFn(torch.autograd.Function):
             scale = grad_out.to(torch.float32).contiguous()
             dpe = torch.zeros(B, T, H, dtype=torch.float32, device=dev)
             dpd = torch.zeros(B, U1, H, dtype=torch.float32, device=dev)
-            dw2x = torch.zeros(Vds, H + 8, dtype=torch.float32, device=dev)  # [dW2 | db2 | 0..]
+            hp = h_stash.shape[1]
+            dw2x = torch.zeros(hp, Vds, dtype=torch.float32, device=dev)  # [dW2 | db2 | unused rows]^T
             chunk = max(2, min(max_tiles, _DS_BUDGET_BYTES // (128 * Vds * 2)))
             nchunk = -(-max_tiles // chunk)
             chunk = -(-max_tiles // nchunk)          # balanced chunks,
@@ -317,16 +318,19 @@ class _JointLossFn(torch.autograd.Function):
                 with _region("lib_gemm_dh"):
                     dh = torch.mm(dsc, w2v)                                            # (rows, H) bf16
                 with _region("lib_gemm_dw2"):
-                    # K = rows is huge and M x N = Vds x (H+8) small: split K (batched GEMM; measured
-                    # best, profiles/r01_notes.md). Column H of h_ext is 1 for valid cells, so column
-                    # H of the product is db2.
+                    # K = rows is huge and the output (pitch x Vds) small: split K (batched GEMM;
+                    # measured best, profiles/r01_notes.md). Column H of the stash is 1 for valid
+                    # cells, so row H of the product is db2; the stash pitch (H+32) and this
+                    # orientation (h^T . dS) are the fastest of the shapes the library was tried
+                    # with (tools/dw2_gemm_bench.py). Rows H+8.. of the product are never read.
                     hc = h_stash[lo * 128: hi * 128]
-                    dw2x += torch.bmm(dsc.view(_SPLIT_K, rows // _SPLIT_K, Vds).transpose(1, 2),
-                                      hc.view(_SPLIT_K, rows // _SPLIT_K, H + 8), out_dtype=torch.float32).sum(0)
+                    dw2x += torch.bmm(hc.view(_SPLIT_K, rows // _SPLIT_K, hp).transpose(1, 2),
+                                      dsc.view(_SPLIT_K, rows // _SPLIT_K, Vds),
+                                      out_dtype=torch.float32).sum(0)
                 _call("dh_reduce", L.rnnt_b200_dh_reduce, _ptr(dh), _ptr(h_stash), _ptr(act_lens), _ptr(label_lens),
                       B, T, U1, H, lo, hi, 1.0, _ptr(dpe), _ptr(dpd), st)
-            dw2 = dw2x[:V, :H].contiguous()
-            db2 = dw2x[:V, H].contiguous()
+            dw2 = dw2x[:H, :V].t().contiguous()
+            db2 = dw2x[H, :V].contiguous()
         return dpe, dpd, dw2, db2, None, None, None, None, None
 
 

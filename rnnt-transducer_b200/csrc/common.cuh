@@ -15,9 +15,25 @@
     if (e__ != cudaSuccess) return (int)e__;               \
   } while (0)
 
+// Row pitch (elements) of the tile-packed bf16 hidden-activation stash: H columns, the ones column
+// at column H (its GEMM against dS gives d b2), padding up to the pitch.
+#ifndef RNNT_H_PAD
+#define RNNT_H_PAD 32
+#endif
+__host__ __device__ constexpr int rnnt_hp(int H) { return H + RNNT_H_PAD; }
+
 // Anti-diagonal-major plane index of cell (t,u) of utterance b (see rnnt_b200.h).
 __host__ __device__ __forceinline__ size_t plane_index(int b, int t, int u, int T, int U1) {
   return ((size_t)b * (size_t)(T + U1 - 1) + (size_t)(t + u)) * (size_t)U1 + (size_t)u;
+}
+
+// 16-byte read of data that is touched once: read-only path, no L1 allocation.
+__device__ __forceinline__ uint4 ld_stream_u4(const uint4* p) {
+  uint4 v;
+  asm("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p));
+  return v;
 }
 
 __device__ __forceinline__ int clamp_int(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }

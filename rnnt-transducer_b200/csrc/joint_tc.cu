@@ -83,15 +83,16 @@ struct JointParams {
   int tile_lo, tile_hi;  // tile range of this launch
   int slots;             // W2 ring depth
   long long* trace;  // RNNT_B200_TRACE: clock64 stamps of cluster 0 / rank 0 (debug only)
+  int trace_cta;  // RNNT_B200_TRACE_CTA: the CTA whose stamps are recorded (default 0)
   int debug;  // RNNT_B200_DEBUG bitmask (timing experiments only): 1 skip epilogue math, 4 skip MMA issue,
               // 16 skip dS stores
 };
 
 // Shared memory of joint_kernel:
 //   [h tile: H/64 K blocks x 16 KB | W2 ring: slots x (BN/2 rows x 64 k) |
-//    MODE 1: dS staging, 2 x 2 KB per epilogue warp | ctl |
+//    MODE 1: dS staging, 2 KB per epilogue warp | ctl |
 //    MODE 0: red4, the cross-half (m, s, zb, zl) merge | bias ring: 2 halves x 2 buffers x BN/2 floats]
-constexpr int kDsStageBytes = kEpiWarps * 2 * 2048;
+constexpr int kDsStageBytes = kEpiWarps * 2048;  // one 2 KB (32 cells x 32 columns) tile per epilogue warp  // one 2 KB (32 cells x 32 columns) tile per epilogue warp
 constexpr int kRedBytes = RNNT_TILE_M * 16;
 // The MMA issuer consumes ksub(H) consecutive ring slots per loop iteration (two when H allows:
 // one wait/fence/elect round per 8 MMAs -- the one-slot loop spent ~620 clk per K block against
@@ -215,12 +216,13 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
     // =========================== EPILOGUE ===========================
     // Warp w reads TMEM lanes 32*(w&3).. (one lattice cell per thread) and the column half w>>2.
     const int q = warp & 3, half = warp >> 2;
-    uint8_t* stage_w = smem_ds + warp * 4096;  // MODE 1: this warp's two dS staging tiles
+    uint8_t* stage_w = smem_ds + warp * 2048;  // MODE 1: this warp's dS staging tile
     (void)stage_w;
     const int row = q * 32 + lane;
     constexpr int NCH = HALF / 16;  // 16-column chunks per half tile
-    uint32_t acc_it = 0, st_it = 0;
-    (void)st_it;
+    uint32_t acc_it = 0;
+    uint32_t gp_hold[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};  // MODE 1: packed even chunk waiting for its odd partner
+    (void)gp_hold;
     // Bias ring of this column half: buffer (acc_it & 1) holds b2*log2(e) of the current
     // vocabulary tile's HALF columns. Warp q == 0 of the half fetches the next tile's slice into
     // a register early in a tile, stores it into the other buffer, and one 128-thread named
@@ -258,6 +260,9 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       // the occupation factor rides in the exponent (one MUFU per logit, no multiply). The two
       // one-hot entries of a row are not selected out of the register tile; their exact values
       // (from the forward's lp_blank / lp_label) overwrite the staged bf16 entries instead.
+      // (Walking this load chain for the next lattice tile during the current one's last
+      // vocabulary tiles was tried: the tile switch is not where the time goes, and the extra
+      // live registers slowed the steady state.)
       float nl = RNNT_NEG_BIG;  // invalid rows: exp2(z + nl) == 0 exactly
       float g_blank = 0.f, g_label = 0.f;
       if (MODE == 1 && rc.valid) {
@@ -300,10 +305,8 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const float4 bb = b4[j];
-            zc[4 * j + 0] = fmaf(zc[4 * j + 0], RNNT_LOG2E, bb.x);
-            zc[4 * j + 1] = fmaf(zc[4 * j + 1], RNNT_LOG2E, bb.y);
-            zc[4 * j + 2] = fmaf(zc[4 * j + 2], RNNT_LOG2E, bb.z);
-            zc[4 * j + 3] = fmaf(zc[4 * j + 3], RNNT_LOG2E, bb.w);
+            ffma2(zc[4 * j + 0], zc[4 * j + 1], RNNT_LOG2E, bb.x, bb.y);
+            ffma2(zc[4 * j + 2], zc[4 * j + 3], RNNT_LOG2E, bb.z, bb.w);
           }
           if (MODE != 0) return 0.f;
           float m0 = fmaxf(zc[0], zc[4]), m1 = fmaxf(zc[1], zc[5]), m2 = fmaxf(zc[2], zc[6]), m3 = fmaxf(zc[3], zc[7]);
@@ -316,11 +319,15 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
           const int col0 = colbase + c * 16;
           if (MODE == 0) {
             const float mn = fmaxf(m, cmax);
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;      // four independent sum chains
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;      // four independent sum chains (two packed pairs)
+            const float nmn = -mn;
 #pragma unroll
             for (int j = 0; j < 16; j += 4) {
-              a0 += ex2_approx(zc[j] - mn); a1 += ex2_approx(zc[j + 1] - mn);
-              a2 += ex2_approx(zc[j + 2] - mn); a3 += ex2_approx(zc[j + 3] - mn);
+              float d0, d1, d2, d3;
+              fadd2(d0, d1, zc[j], zc[j + 1], nmn, nmn);
+              fadd2(d2, d3, zc[j + 2], zc[j + 3], nmn, nmn);
+              fadd2(a0, a1, a0, a1, ex2_approx(d0), ex2_approx(d1));
+              fadd2(a2, a3, a2, a3, ex2_approx(d2), ex2_approx(d3));
             }
             s = s * ex2_approx(m - mn) + ((a0 + a1) + (a2 + a3));
             m = mn;
@@ -338,39 +345,51 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
           } else {
             uint32_t gp[8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j)  // softmax * (c_blank + c_label) * scale, two columns per word
-              gp[j] = pack_bf16x2(ex2_approx(zc[2 * j] + nl), ex2_approx(zc[2 * j + 1] + nl));
-            // 32 cells x 32 columns of bf16 (two chunks) -> one of this warp's two 2 KB staging
-            // tiles (64-byte rows, SWIZZLE_64B: conflict-free 16-byte stores) -> one TMA store
-            // (full-sector writes). The tile written now was last read by the store before the
-            // previous one.
-            uint8_t* stile = stage_w + (st_it & 1) * 2048;
-            if ((c & 1) == 0) {
-              if (lane == 0) bulk_wait_group_read1();
+            for (int j = 0; j < 8; ++j) {  // softmax * (c_blank + c_label) * scale, two columns per word
+              float d0, d1;
+              fadd2(d0, d1, zc[2 * j], zc[2 * j + 1], nl, nl);
+              gp[j] = pack_bf16x2(ex2_approx(d0), ex2_approx(d1));
+            }
+            // 32 cells x 32 columns of bf16 (two chunks) -> this warp's 2 KB staging tile (64-byte
+            // rows, SWIZZLE_64B: conflict-free 16-byte stores) -> one TMA store (full-sector
+            // writes). The tile is single buffered (the 16 KB a second one would take hold the
+            // fifth W2 ring slot), so an even chunk is only packed and HELD in registers; both
+            // chunks are written behind the wait on the previous store's smem read, which by then
+            // is two exponential stages old. (Tried instead of the TMA store: transposed 16-byte
+            // st.global from the staged tile, 6.6 ms, and one 32-byte st.global per lane and chunk
+            // straight from registers, 8.7 ms, against 5.65 ms.)
+            const bool last = c + 1 == nchk;
+            if ((c & 1) == 0 && !last) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) gp_hold[j] = gp[j];
+            } else {
+              if (lane == 0) bulk_wait_group_read0();
               __syncwarp();
-            }
-            uint8_t* srow = stile + lane * 64;
-            const int swz = (lane >> 1) & 3;
-            *reinterpret_cast<uint4*>(srow + (((2 * (c & 1)) ^ swz) << 4)) = make_uint4(gp[0], gp[1], gp[2], gp[3]);
-            *reinterpret_cast<uint4*>(srow + (((2 * (c & 1) + 1) ^ swz) << 4)) = make_uint4(gp[4], gp[5], gp[6], gp[7]);
-            // the row's one-hot entries: exact values over the staged ones (same thread, program order)
-            if ((unsigned)(p.blank - col0) < 16u && rc.valid) {
-              const int off = (c & 1) * 32 + (p.blank - col0) * 2;
-              *reinterpret_cast<__nv_bfloat16*>(srow + (((off >> 4) ^ swz) << 4) + (off & 15)) = __float2bfloat16_rn(g_blank);
-            }
-            if ((unsigned)(label - col0) < 16u) {
-              const int off = (c & 1) * 32 + (label - col0) * 2;
-              *reinterpret_cast<__nv_bfloat16*>(srow + (((off >> 4) ^ swz) << 4) + (off & 15)) = __float2bfloat16_rn(g_label);
-            }
-            if ((c & 1) == 1 || c + 1 == nchk) {
+              uint8_t* srow = stage_w + lane * 64;
+              const int swz = (lane >> 1) & 3;
+              const int cbase = col0 - (c & 1) * 16;  // first column of the staged tile
+              if (c & 1) {
+                *reinterpret_cast<uint4*>(srow + ((0 ^ swz) << 4)) = make_uint4(gp_hold[0], gp_hold[1], gp_hold[2], gp_hold[3]);
+                *reinterpret_cast<uint4*>(srow + ((1 ^ swz) << 4)) = make_uint4(gp_hold[4], gp_hold[5], gp_hold[6], gp_hold[7]);
+              }
+              *reinterpret_cast<uint4*>(srow + (((2 * (c & 1)) ^ swz) << 4)) = make_uint4(gp[0], gp[1], gp[2], gp[3]);
+              *reinterpret_cast<uint4*>(srow + (((2 * (c & 1) + 1) ^ swz) << 4)) = make_uint4(gp[4], gp[5], gp[6], gp[7]);
+              // the row's one-hot entries: exact values over the staged ones (same thread, program order)
+              const int ncols = 16 + (c & 1) * 16;
+              if ((unsigned)(p.blank - cbase) < (unsigned)ncols && rc.valid) {
+                const int off = (p.blank - cbase) * 2;
+                *reinterpret_cast<__nv_bfloat16*>(srow + (((off >> 4) ^ swz) << 4) + (off & 15)) = __float2bfloat16_rn(g_blank);
+              }
+              if ((unsigned)(label - cbase) < (unsigned)ncols) {
+                const int off = (label - cbase) * 2;
+                *reinterpret_cast<__nv_bfloat16*>(srow + (((off >> 4) ^ swz) << 4) + (off & 15)) = __float2bfloat16_rn(g_label);
+              }
               fence_proxy_async_smem();
               __syncwarp();
-              const int colt = colbase + (c & ~1) * 16;
               if (lane == 0 && !dead && !(p.debug & 16)) {
-                tma_store_2d(&map_ds, stile, colt, (tile - p.tile_lo) * RNNT_TILE_M + q * 32);
+                tma_store_2d(&map_ds, stage_w, cbase, (tile - p.tile_lo) * RNNT_TILE_M + q * 32);
                 bulk_commit_group();
               }
-              ++st_it;
             }
           }
         };
@@ -412,7 +431,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
           }
         }
         named_bar_sync(2 + half, 128);  // bias ring hand-over (see above)
-        if (p.trace && blockIdx.x == 0 && threadIdx.x == 0 && acc_it < 4096) {
+        if (p.trace && blockIdx.x == p.trace_cta && threadIdx.x == 0 && acc_it < 4096) {
           long long* t = p.trace + 6 * 4096;
           t[3 * acc_it + 0] = tr0; t[3 * acc_it + 1] = tr1; t[3 * acc_it + 2] = clock64();
         }
@@ -466,7 +485,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[slot], 2 * kSlotBytes);
         else mbar_arrive_cluster(full);
         tma_load_2d_pair(smem_b + slot * kSlotBytes, &map_w2, full, kb * kKBlock, row0);
-        if (p.trace && blockIdx.x == 0 && parity == 0 && tr_n < 4096) {
+        if (p.trace && blockIdx.x == p.trace_cta && parity == 0 && tr_n < 4096) {
           long long* t = p.trace + 3 * 4096;
           t[3 * tr_n + 0] = tr0; t[3 * tr_n + 1] = tr1; t[3 * tr_n + 2] = clock64();
           ++tr_n;
@@ -507,7 +526,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       uint32_t slot = 0, phase = 0, acc_it = 0;
       int it = 0, tr_n = 0;
       const uint32_t a0 = smem_u32(smem_a), b0 = smem_u32(smem_b);
-      const bool tracing = p.trace != nullptr && blockIdx.x == 0;
+      const bool tracing = p.trace != nullptr && blockIdx.x == p.trace_cta;
       for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
         for (int vi = 0; vi < NV; ++vi, ++acc_it) {
           const int vt = (vi + cid) % NV;  // same rotated order as the producer and the epilogue
@@ -576,7 +595,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
 __global__ void __launch_bounds__(256)
 hidden_kernel(const JointParams p, int max_tiles) {
   const int n_tiles = min(p.n_tiles[0], max_tiles);
-  const int hp = p.H + 8;
+  const int hp = rnnt_hp(p.H);
   const int cpr = p.H / 8;            // 16-byte chunks per row
   const int rows_per_pass = 256 / cpr;  // H=512: 4 rows per pass
   const int chunk = threadIdx.x % cpr;
@@ -778,6 +797,10 @@ int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap
   const char* trace_mode = getenv("RNNT_B200_DEBUG_MODE");
   if (trace_path && trace_mode && atoi(trace_mode) != MODE) trace_path = nullptr;
   p.trace = nullptr;
+  {
+    const char* tc = getenv("RNNT_B200_TRACE_CTA");
+    p.trace_cta = tc ? atoi(tc) : 0;
+  }
   const size_t trace_bytes = 9 * 4096 * sizeof(long long);
   if (trace_path) {
     if (cudaMalloc(&p.trace, trace_bytes) != cudaSuccess) p.trace = nullptr;
@@ -804,7 +827,7 @@ int dispatch_joint(JointParams& p, const void* w2q, const void* h_stash, int max
   CUtensorMap mw, mh;
   int rc = make_map_bf16(&mw, w2q, p.Vpad, p.H, p.H, kKBlock, BN / 2, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
-  rc = make_map_bf16(&mh, h_stash, (uint64_t)max_tiles * RNNT_TILE_M, p.H, p.H + 8, kKBlock, RNNT_TILE_M,
+  rc = make_map_bf16(&mh, h_stash, (uint64_t)max_tiles * RNNT_TILE_M, p.H, rnnt_hp(p.H), kKBlock, RNNT_TILE_M,
                      CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
   CUtensorMap md = mw;

@@ -87,7 +87,7 @@ dh_reduce_kernel(const __nv_bfloat16* __restrict__ dh, const __nv_bfloat16* __re
   const int chunk = threadIdx.x % cpr;
   const int rl = threadIdx.x / cpr;
   if (rl >= lanes) return;
-  const int hp = H + 8;
+  const int hp = rnnt_hp(H);
   const uint4* dh4 = reinterpret_cast<const uint4*>(dh) + chunk;                // row pitch H/8 uint4
   const uint4* h4 = reinterpret_cast<const uint4*>(h + (size_t)first_tile * RNNT_TILE_M * hp) + chunk;  // pitch hp/8
   float acc_e[DH_TT][8];
@@ -164,7 +164,7 @@ extern "C" int rnnt_b200_vocab_pad(int V) {
   const int bn = rnnt_b200_vocab_tile(V);
   return ((V + bn - 1) / bn) * bn;
 }
-extern "C" int rnnt_b200_h_pitch(int H) { return H + 8; }
+extern "C" int rnnt_b200_h_pitch(int H) { return rnnt_hp(H); }
 extern "C" int rnnt_b200_ds_pitch(int V) {
   // The UMMA N granularity is 16, but a pitch that is not a multiple of 64 elements (128 bytes)
   // slows the library GEMMs that consume dS by more than the narrower tile saves (measured:
