@@ -103,22 +103,25 @@ __host__ __device__ inline int smem_bytes_for(int H, int BN, int slots, int mode
          (int)sizeof(SharedCtl) + 2 * 2 * (BN / 2) * 4;
 }
 
-// hidden_kernel is MUFU-bound (ncu: XU pipe 63 %, 0.71 ms at the AISHELL shape with the two-MUFU
-// form 1 - 2/(exp(2x)+1), |err| ~1e-7 absolute). tanh.approx.f32 is ONE MUFU op, but its 2^-11
-// relative error pushed the per-utterance loss of one-cell utterances to 4e-5 relative (stated
-// tolerance 2e-5) for no measurable step-time gain, so it stays off (-DRNNT_TANH_EXACT=0).
-#ifndef RNNT_TANH_EXACT
-#define RNNT_TANH_EXACT 1
-#endif
-__device__ __forceinline__ float tanh_accurate(float x) {
-#if RNNT_TANH_EXACT
-  const float e = ex2_approx(x * (2.f * RNNT_LOG2E));
-  return 1.f - __fdividef(2.f, e + 1.f);
-#else
-  float y;
-  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-#endif
+// tanh for hidden_kernel. (tanh.approx.f32 is one MUFU op, but its 2^-11 relative error pushed the
+// per-utterance loss of one-cell utterances to 4e-5 relative -- stated tolerance 2e-5 -- for no
+// measurable step-time gain.)
+// Four tanh at once, tanh(x) = 1 - 2/(exp(2x)+1), with ONE reciprocal for the four denominators
+// (1/d0 = d1 * (d2 d3) / (d0 d1 d2 d3), ...): 5 MUFU operations per 4 values instead of 8 for 9
+// extra multiplies on the FMA pipe. x is clamped at 10 (tanh(10)
+// rounds to 1.0f) so that the product of four denominators stays below 2^116.
+__device__ __forceinline__ void tanh4(const float (&x)[4], float (&y)[4]) {
+  float d[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) d[i] = ex2_approx(fminf(x[i], 10.f) * (2.f * RNNT_LOG2E)) + 1.f;
+  const float p01 = d[0] * d[1], p23 = d[2] * d[3];
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(p01 * p23));
+  const float r01 = r * p23, r23 = r * p01;  // 1/(d0 d1), 1/(d2 d3)
+  y[0] = fmaf(-2.f, r01 * d[1], 1.f);
+  y[1] = fmaf(-2.f, r01 * d[0], 1.f);
+  y[2] = fmaf(-2.f, r23 * d[3], 1.f);
+  y[3] = fmaf(-2.f, r23 * d[2], 1.f);
 }
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
@@ -584,11 +587,14 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
 
 // ---------------------------------------------------------------------------------------
 // h = bf16(tanh(P_enc[t] + P_dec[u])) for every tile row; the decomposed first joint layer
-// (model.py:26-34 without the repeat/cat). One CTA per tile, 64 threads per row (each 8
-// consecutive k: 2x16 B loads from each addend, one 16 B store), 4 rows in flight per pass.
+// (model.py:26-34 without the repeat/cat). One CTA per tile, H/8 threads per row (each 8
+// consecutive k: 2x16 B loads from each addend, one 16 B store), 256/(H/8) rows per pass.
+// A tile's rows are consecutive cells (t, u) of ONE utterance, u fastest: the tile table and the
+// lengths are read once per tile, (t, u) advance incrementally (no division per row) and the
+// P_enc slice stays in registers while t does not change (every ~(U+1)/4 passes).
 // Rows past an utterance's last cell and tiles past the table are written as zeros;
 // column H of the 8-wide tail is 1.0 for valid cells (the "ones" column that makes the library
-// GEMM dS^T.h_ext produce d b2 next to dW2). MUFU-bound: two MUFU ops per tanh.
+// GEMM h_ext^T.dS produce d b2 next to dW2).
 // (Taking the blank/label logits here as dot products with two W2 rows doubled this kernel's
 // time -- 0.45 -> 1.03 ms -- and was dropped again.)
 // ---------------------------------------------------------------------------------------
@@ -603,27 +609,48 @@ hidden_kernel(const JointParams p, int max_tiles) {
   for (int tile = blockIdx.x; tile < max_tiles; tile += gridDim.x) {
     const bool dead = tile >= n_tiles;
     __nv_bfloat16* dst_tile = p.h_stash + (size_t)tile * RNNT_TILE_M * hp;
-    if (threadIdx.x < RNNT_TILE_M) {
-      const RowCoord rc = locate_row(p, tile, threadIdx.x, dead);
-      *reinterpret_cast<uint4*>(dst_tile + (size_t)threadIdx.x * hp + p.H) =
-          make_uint4(rc.valid ? 0x00003F80u : 0u, 0u, 0u, 0u);
+    int b = 0, cell0 = 0, w = 1, ncell = 0;  // dead tile: no valid cell
+    if (!dead) {
+      b = __ldg(p.tile_utt + tile);
+      cell0 = __ldg(p.tile_cell0 + tile);
+      w = clamp_int(__ldg(p.label_lens + b), 0, p.U1 - 1) + 1;
+      ncell = clamp_int(__ldg(p.act_lens + b), 1, p.T) * w;
     }
+    if (threadIdx.x < RNNT_TILE_M)
+      *reinterpret_cast<uint4*>(dst_tile + (size_t)threadIdx.x * hp + p.H) =
+          make_uint4(cell0 + (int)threadIdx.x < ncell ? 0x00003F80u : 0u, 0u, 0u, 0u);
     if (rsub < rows_per_pass) {
+      int cell = cell0 + rsub;
+      int t = cell / w, u = cell - t * w;
+      int t_have = -1;
+      float4 e0 = make_float4(0.f, 0.f, 0.f, 0.f), e1 = e0;
+      const float4* pe4 = reinterpret_cast<const float4*>(p.pe + (size_t)b * p.T * p.H) + chunk * 2;
+      const float4* pd4 = reinterpret_cast<const float4*>(p.pd + (size_t)b * p.U1 * p.H) + chunk * 2;
+      const int h4 = p.H / 4;  // float4 per row of P_enc / P_dec
 #pragma unroll 2
-      for (int r0 = 0; r0 < RNNT_TILE_M; r0 += rows_per_pass) {
-        const int row = r0 + rsub;
-        const RowCoord rc = locate_row(p, tile, row, dead);
+      for (int row = rsub; row < RNNT_TILE_M; row += rows_per_pass) {
         uint4 o = make_uint4(0u, 0u, 0u, 0u);
-        if (rc.valid) {
-          const float4* e4 = reinterpret_cast<const float4*>(p.pe + ((size_t)rc.b * p.T + rc.t) * p.H) + chunk * 2;
-          const float4* d4 = reinterpret_cast<const float4*>(p.pd + ((size_t)rc.b * p.U1 + rc.u) * p.H) + chunk * 2;
-          const float4 e0 = __ldg(e4), e1 = __ldg(e4 + 1), d0 = __ldg(d4), d1 = __ldg(d4 + 1);
-          o.x = pack_bf16x2(tanh_accurate(e0.x + d0.x), tanh_accurate(e0.y + d0.y));
-          o.y = pack_bf16x2(tanh_accurate(e0.z + d0.z), tanh_accurate(e0.w + d0.w));
-          o.z = pack_bf16x2(tanh_accurate(e1.x + d1.x), tanh_accurate(e1.y + d1.y));
-          o.w = pack_bf16x2(tanh_accurate(e1.z + d1.z), tanh_accurate(e1.w + d1.w));
+        if (cell < ncell) {
+          const float4 d0 = __ldg(pd4 + (size_t)u * h4), d1 = __ldg(pd4 + (size_t)u * h4 + 1);
+          if (t != t_have) {
+            e0 = __ldg(pe4 + (size_t)t * h4);
+            e1 = __ldg(pe4 + (size_t)t * h4 + 1);
+            t_have = t;
+          }
+          const float xa[4] = {e0.x + d0.x, e0.y + d0.y, e0.z + d0.z, e0.w + d0.w};
+          const float xb[4] = {e1.x + d1.x, e1.y + d1.y, e1.z + d1.z, e1.w + d1.w};
+          float ya[4], yb[4];
+          tanh4(xa, ya);
+          tanh4(xb, yb);
+          o.x = pack_bf16x2(ya[0], ya[1]);
+          o.y = pack_bf16x2(ya[2], ya[3]);
+          o.z = pack_bf16x2(yb[0], yb[1]);
+          o.w = pack_bf16x2(yb[2], yb[3]);
         }
         *reinterpret_cast<uint4*>(dst_tile + (size_t)row * hp + chunk * 8) = o;
+        cell += rows_per_pass;
+        u += rows_per_pass;
+        while (u >= w) { u -= w; ++t; }
       }
     }
   }
