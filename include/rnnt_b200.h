@@ -173,6 +173,17 @@ int rnnt_b200_dh_reduce(const void* dh_bf16, const void* h_stash,
                         int B, int T, int U1, int H, int tile_lo, int tile_hi, float dh_scale,
                         float* dp_enc, float* dp_dec, void* stream);
 
+/* Greedy decoding, one frame for B <= 64 utterances at once (replaces the per-utterance, per-frame
+ * joint + softmax + argmax + .item() of rnnt/model.py:90-93 / rnnt/search.py):
+ *   pred[b] = argmax_v ( W2 . tanh(pe_t[b,:] + pd[b,:]) + b2 )[v]       (lowest index on ties)
+ * pe_t: row b at pe_t + b*pe_stride (float32, e.g. the slice [:,t,:] of the (B,T,H) first-layer
+ * product: pe_stride = T*H); pd (B,H), w2 (V,H), b2 (V) float32 contiguous; H a multiple of 64 in
+ * [64,512]. work: B+1 64-bit words, zeroed once by the caller before the first step (every call
+ * leaves them zeroed again). pred: (B) int64. fp32 arithmetic; no logits are written. */
+int rnnt_b200_joint_step_argmax(const float* pe_t, long long pe_stride, const float* pd,
+                                const float* w2, const float* b2, int B, int H, int V,
+                                unsigned long long* work, long long* pred, void* stream);
+
 /* Plain bf16 tensor-core GEMM used to validate the tcgen05/TMA plumbing on its own:
  * C (M,N) float32 = A (M,K) bf16 . B (N,K)^T bf16; M%128==0, N%64==0, K%64==0. */
 int rnnt_b200_selftest_gemm(const void* a_bf16, const void* b_bf16, float* c,

@@ -23,6 +23,7 @@ from . import _lib
 from ._shard import allreduce_grads_and_loss, global_mean_loss, shard_batch
 
 __all__ = ["RNNTLoss", "rnnt_loss", "JointNet", "JointRNNTLoss", "joint_rnnt_loss",
+           "fold_output_projections", "ProjectedJointRNNTLoss", "greedy_decode",
            "build_extension", "extension_path", "selftest_gemm", "KernelTimer",
            "shard_batch", "global_mean_loss", "allreduce_grads_and_loss"]
 
@@ -47,7 +48,8 @@ class KernelTimer:
     active = None
     # kernels launched per C-ABI call
     KERNELS = {"logits_to_planes": 1, "lattice": 2, "planes_to_dlogits": 1, "build_tiles": 1,
-               "pack_vocab": 1, "joint_hidden": 1, "joint_fwd": 1, "joint_bwd_ds": 1, "dh_reduce": 1}
+               "pack_vocab": 1, "joint_hidden": 1, "joint_fwd": 1, "joint_bwd_ds": 1, "dh_reduce": 1,
+               "joint_step_argmax": 1}
 
     def __init__(self, events: bool = True):
         self.events = events
@@ -379,6 +381,49 @@ def joint_rnnt_loss(enc_state, dec_state, w1, b1, w2, b2, labels, act_lens, labe
     return _reduce(loss_b, reduction)
 
 
+def fold_output_projections(enc_proj_w, enc_proj_b, dec_proj_w, dec_proj_b, w1, b1):
+    """SURVEY.md section 8(f) rank 1. The encoder's and the decoder's ``output_proj``
+    (rnnt/encoder.py:18-20,38; rnnt/decoder.py:19,42) feed the joint's ``forward_layer``
+    (rnnt/model.py:13,32) with no nonlinearity in between, so
+
+        forward_layer([enc_proj(x_t); dec_proj(y_u)]) = (W1e Weo) x_t + (W1d Wdo) y_u
+                                                        + (b1 + W1e beo + W1d bdo)
+
+    Returns ``(w_enc (H,He), w_dec (H,Hd), bias (H))``: one GEMM per side straight from the LSTM
+    outputs instead of two, and no (B,T,E) / (B,U+1,D) round trip through HBM. Plain torch ops:
+    autograd carries the gradients back to all six parameter tensors."""
+    E = enc_proj_w.shape[0]
+    if w1.shape[1] != E + dec_proj_w.shape[0]:
+        raise ValueError("forward_layer.weight does not match the two output projections")
+    w1e, w1d = w1[:, :E], w1[:, E:]
+    return w1e @ enc_proj_w, w1d @ dec_proj_w, b1 + w1e @ enc_proj_b + w1d @ dec_proj_b
+
+
+class ProjectedJointRNNTLoss(nn.Module):
+    """``ProjectedJointRNNTLoss(joint, enc_proj, dec_proj)(enc_rnn_out, dec_rnn_out, labels,
+    act_lens, label_lens) -> loss`` where ``enc_rnn_out`` (B,T,He) / ``dec_rnn_out`` (B,U+1,Hd)
+    are the LSTM outputs BEFORE ``output_proj`` and ``enc_proj`` / ``dec_proj`` are those
+    ``nn.Linear`` modules (``model.encoder.output_proj``, ``model.decoder.output_proj`` of the
+    reference). Same value as ``JointRNNTLoss(joint)(enc_proj(enc_rnn_out),
+    dec_proj(dec_rnn_out), ...)`` up to fp32 reassociation of the first layer."""
+
+    def __init__(self, joint: nn.Module, enc_proj: nn.Linear, dec_proj: nn.Linear, blank: int = 0,
+                 reduction: str = "mean"):
+        super().__init__()
+        self.joint, self.enc_proj, self.dec_proj = joint, enc_proj, dec_proj
+        self.blank, self.reduction = blank, reduction
+
+    def forward(self, enc_rnn_out, dec_rnn_out, labels, act_lens, label_lens, host_lens=None):
+        j = self.joint
+        w_enc, w_dec, bias = fold_output_projections(
+            self.enc_proj.weight, self.enc_proj.bias, self.dec_proj.weight, self.dec_proj.bias,
+            j.forward_layer.weight, j.forward_layer.bias)
+        # [w_enc | w_dec] plays forward_layer.weight for inputs of widths He and Hd
+        return joint_rnnt_loss(enc_rnn_out, dec_rnn_out, torch.cat((w_enc, w_dec), dim=1), bias,
+                               j.project_layer.weight, j.project_layer.bias, labels, act_lens,
+                               label_lens, self.blank, self.reduction, host_lens)
+
+
 class JointNet(nn.Module):
     """Same parameters, names and forward semantics as rnnt/model.py:9-37, so reference
     checkpoints (utils.py:74-85, key 'joint') load unchanged. ``forward`` materialises logits
@@ -422,6 +467,62 @@ class JointRNNTLoss(nn.Module):
         return joint_rnnt_loss(enc_state, dec_state, j.forward_layer.weight, j.forward_layer.bias,
                                j.project_layer.weight, j.project_layer.bias, labels, act_lens,
                                label_lens, self.blank, self.reduction, host_lens)
+
+
+@torch.no_grad()
+def greedy_decode(enc_state, inputs_length, decoder: nn.Module, joint: nn.Module, blank: int = 0):
+    """Batched, on-device greedy search with the semantics of ``Transducer.recognize``
+    (rnnt/model.py:74-111; the same loop is duplicated in rnnt/search.py:5-40): per utterance, walk
+    the frames t = 0..len-1; at each frame take argmax of the joint on (enc_state[t], dec_state);
+    a non-blank prediction is emitted and fed to the decoder (at most ONE symbol per frame).
+
+    The reference runs this per utterance with a ``.item()`` sync per frame. Here all B utterances
+    advance together: the first joint layer's encoder half is one GEMM for the whole batch, each
+    frame is one ``rnnt_b200_joint_step_argmax`` launch (fp32, no logits written) plus one batched
+    decoder step whose result is kept only where a symbol was emitted; nothing is read back until
+    the end. ``decoder(tokens (B,1), hidden=hidden) -> (out (B,1,D), hidden)`` is the reference's
+    ``BaseDecoder`` interface (rnnt/decoder.py:24-44).
+
+    Returns ``(tokens (B,T) int64, zero padded; counts (B) int64)`` on ``enc_state.device``;
+    ``[tokens[i, :counts[i]].tolist() for i in range(B)]`` is ``recognize``'s return value."""
+    if enc_state.dim() != 3 or not enc_state.is_cuda or enc_state.dtype != torch.float32:
+        raise ValueError("enc_state must be a float32 CUDA tensor (B,T,E)")
+    B, T, E = enc_state.shape
+    w1, b1 = joint.forward_layer.weight, joint.forward_layer.bias
+    w2 = joint.project_layer.weight.detach().float().contiguous()
+    b2 = joint.project_layer.bias.detach().float().contiguous()
+    H, V = w1.shape[0], w2.shape[0]
+    if H % 64 or not 64 <= H <= 512:
+        raise ValueError(f"joint inner size {H} unsupported: need a multiple of 64 in [64,512]")
+    if not 0 <= blank < V:
+        raise ValueError(f"blank {blank} not in [0,{V})")
+    dev = enc_state.device
+    L = _lib.lib()
+    lengths = inputs_length.to(dev).long()
+    pe = F.linear(enc_state, w1[:, :E], b1).contiguous()          # (B,T,H), once
+    w1d = w1[:, E:]
+    tokens = torch.zeros(B, max(T, 1), dtype=torch.long, device=dev)
+    counts = torch.zeros(B, dtype=torch.long, device=dev)
+    pred = torch.empty(B, dtype=torch.long, device=dev)
+    work = torch.zeros(B + (B + 63) // 64, dtype=torch.long, device=dev)  # one B+1 area per 64-row launch
+    dec_out, hidden = decoder(torch.full((B, 1), blank, dtype=torch.long, device=dev))
+    with torch.cuda.device(dev):
+        st = _stream()
+        for t in range(T):
+            pd = F.linear(dec_out[:, 0], w1d).contiguous()          # (B,H)
+            for c, lo in enumerate(range(0, B, 64)):
+                n = min(64, B - lo)
+                _call("joint_step_argmax", L.rnnt_b200_joint_step_argmax,
+                      pe.data_ptr() + (lo * T + t) * H * 4, T * H, _ptr(pd[lo:]), _ptr(w2), _ptr(b2),
+                      n, H, V, work.data_ptr() + (lo + c) * 8, pred.data_ptr() + lo * 8, st)
+            emit = (pred != blank) & (lengths > t)
+            new_out, new_hidden = decoder(pred.unsqueeze(1), hidden=hidden)
+            dec_out = torch.where(emit[:, None, None], new_out, dec_out)
+            hidden = tuple(torch.where(emit[None, :, None], n_, o_) for n_, o_ in zip(new_hidden, hidden))
+            # a row that emits nothing rewrites a zero at its next free slot
+            tokens.scatter_(1, counts.unsqueeze(1), torch.where(emit, pred, torch.zeros_like(pred)).unsqueeze(1))
+            counts += emit
+    return tokens, counts
 
 
 def selftest_gemm(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:

@@ -110,7 +110,7 @@ def fused_vs_oracle(enc, dec, w1, b1, w2, b2, y, tl, ul, grads=True, host_lens=F
             for n, a, b in zip(names, leaves, ol):
                 out[f"d{n}_rel_l2_{tag}"] = rel_l2(a.grad, b.grad)
                 out[f"d{n}_max_abs_{tag}"] = max_abs(a.grad, b.grad)
-    out["loss_mean"] = float(loss.mean())
+    out["loss_mean"] = float(loss.detach().mean())
     return out
 
 
@@ -137,3 +137,64 @@ def fused_matches_dropin(B, T, U, E, D, H, V, mode="ragged", seed=7):
     loss_d = R.rnnt_loss(logits, y, tl, ul, reduction="none")
     torch.cuda.synchronize()
     return {"loss_rel": float(((loss_f - loss_d).abs() / loss_d.abs()).max()), "loss_mean": float(loss_d.mean())}
+
+
+def projected_matches_two_step(B, T, U, He, Hd, E, D, H, V, mode="ragged", seed=11):
+    """ProjectedJointRNNTLoss on the LSTM outputs against output_proj followed by
+    JointRNNTLoss -- loss and the gradients of every tensor both paths share."""
+    g = torch.Generator().manual_seed(seed)
+    joint = R.JointNet(E + D, H, V).to(DEV)
+    enc_proj = torch.nn.Linear(He, E).to(DEV)
+    dec_proj = torch.nn.Linear(Hd, D).to(DEV)
+    xe = torch.randn(B, T, He, generator=g).to(DEV).requires_grad_(True)
+    xd = torch.randn(B, U + 1, Hd, generator=g).to(DEV).requires_grad_(True)
+    from tests.helpers import synth_labels, synth_lengths
+    tl, ul = synth_lengths(B, T, U, mode, g)
+    y = synth_labels(B, U, V, ul, g).to(DEV)
+    tl, ul = tl.to(DEV), ul.to(DEV)
+    params = [xe, xd] + list(enc_proj.parameters()) + list(dec_proj.parameters()) + list(joint.parameters())
+
+    def run(fn):
+        for q in params:
+            q.grad = None
+        loss = fn()
+        loss.sum().backward()
+        return loss.detach().clone(), [q.grad.detach().clone() for q in params]
+
+    two = R.JointRNNTLoss(joint, reduction="none")
+    one = R.ProjectedJointRNNTLoss(joint, enc_proj, dec_proj, reduction="none")
+    l2, g2 = run(lambda: two(enc_proj(xe), dec_proj(xd), y, tl, ul))
+    l1, g1 = run(lambda: one(xe, xd, y, tl, ul))
+    torch.cuda.synchronize()
+    names = ["enc_rnn", "dec_rnn", "enc_proj.w", "enc_proj.b", "dec_proj.w", "dec_proj.b", "w1", "b1", "w2", "b2"]
+    out = {"loss_rel": float(((l1 - l2).abs() / l2.abs()).max())}
+    for n, a, b in zip(names, g1, g2):
+        out["d" + n] = float((a - b).norm() / b.norm().clamp_min(1e-30))
+    return out
+
+
+def greedy_matches_oracle(B, T, E, D, H, V, hidden=48, layers=1, seed=5, scale=3.0):
+    """batched on-device greedy search against the per-utterance restatement of
+    Transducer.recognize (oracle/greedy_oracle.py), same modules, same device."""
+    from oracle.greedy_oracle import greedy_search
+    from tests.helpers import make_decoder
+    g = torch.Generator().manual_seed(seed)
+    torch.manual_seed(seed)
+    joint = R.JointNet(E + D, H, V).to(DEV)
+    with torch.no_grad():  # spread the logits so that blanks and symbols both occur
+        joint.project_layer.weight.mul_(scale * 4)
+        joint.project_layer.bias.mul_(scale)
+    dec = make_decoder(hidden, V, D, layers, seed).to(DEV).eval()
+    enc = (torch.randn(B, T, E, generator=g) * scale).to(DEV)
+    with torch.no_grad():  # calibrate the blank bias so that about half of the frames emit nothing
+        d0, _ = dec(torch.zeros(1, 1, dtype=torch.long, device=DEV))
+        lg = joint.project_layer(torch.tanh(joint.forward_layer(
+            torch.cat((enc.reshape(-1, E), d0.view(1, -1).expand(B * T, -1)), dim=-1))))
+        joint.project_layer.bias[0] += (lg[:, 1:].max(dim=1).values - lg[:, 0]).median()
+    lens = torch.randint(max(1, T // 2), T + 1, (B,), generator=g)
+    lens[0] = T
+    tokens, counts = R.greedy_decode(enc, lens, dec, joint)
+    got = [tokens[i, :int(counts[i])].tolist() for i in range(B)]
+    want = greedy_search(enc, lens, dec, joint)
+    return {"equal": got == want, "n_symbols": sum(len(w) for w in want),
+            "n_frames": int(lens.sum()), "got": got[:2], "want": want[:2]}

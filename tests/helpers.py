@@ -41,3 +41,27 @@ def rel_l2(a, b):
 def max_abs(a, b):
     a, b = torch.as_tensor(a).detach().double().cpu(), torch.as_tensor(b).detach().double().cpu()
     return float((a - b).abs().max())
+
+
+def make_decoder(hidden_size, vocab_size, output_size, n_layers=1, seed=0):
+    """A prediction network with the interface of the reference's BaseDecoder
+    (rnnt/decoder.py:5-44): embedding -> LSTM -> output_proj; forward(inputs, length=None,
+    hidden=None) -> (outputs, hidden). Only the length=None path (decoding) is needed here."""
+    import torch
+    import torch.nn as nn
+
+    class Decoder(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.embedding = nn.Embedding(vocab_size, hidden_size, padding_idx=0)
+            self.lstm = nn.LSTM(input_size=hidden_size, hidden_size=hidden_size, num_layers=n_layers,
+                                batch_first=True)
+            self.output_proj = nn.Linear(hidden_size, output_size)
+
+        def forward(self, inputs, length=None, hidden=None):
+            assert length is None
+            outputs, hidden = self.lstm(self.embedding(inputs), hidden)
+            return self.output_proj(outputs), hidden
+
+    torch.manual_seed(seed)
+    return Decoder()

@@ -56,3 +56,25 @@ def test_fused_agrees_with_dropin_at_scale():
     # no CPU oracle at this size: consistency between the two CUDA boundaries
     m = G.fused_matches_dropin(4, 120, 40, 320, 320, 512, 4232)
     assert m["loss_rel"] < 2e-5, m
+
+
+def test_projected_loss_matches_output_proj_then_joint():
+    # folding encoder/decoder output_proj into the joint's first layer only
+    # reassociates fp32 sums ahead of the bf16 rounding of h
+    m = G.projected_matches_two_step(3, 21, 7, 96, 80, 64, 64, 128, 300)
+    assert m["loss_rel"] < 5e-5, m
+    for k, v in m.items():
+        if k != "loss_rel":
+            assert v < 2e-2, (k, m)
+
+
+@pytest.mark.parametrize("dims", [
+    (5, 30, 32, 32, 64, 50),       # small everything, ragged lengths
+    (3, 12, 320, 320, 512, 4232),  # AISHELL joint dims
+    (70, 6, 16, 16, 128, 40),      # B > 64: two launches per frame
+])
+def test_greedy_decode_matches_reference_loop(dims):
+    # SURVEY 8(f)-3 (rnnt/model.py:74-111): same token sequences as the per-utterance loop
+    m = G.greedy_matches_oracle(*dims)
+    assert m["equal"], m
+    assert 0 < m["n_symbols"] < m["n_frames"], m   # the case exercises both blanks and symbols

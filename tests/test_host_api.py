@@ -105,3 +105,20 @@ def test_fused_entry_validates_shapes_on_cpu():
     ul = torch.tensor([1], dtype=torch.int32)
     with pytest.raises(RuntimeError, match="no CPU path"):
         f(torch.zeros(1, 2, 8), torch.zeros(1, 2, 8), y, tl, ul)
+
+
+def test_fold_output_projections_algebra():
+    # SURVEY 8(f)-1, float64 on CPU: forward_layer([enc_proj(x); dec_proj(y)]) == folded form
+    import torch
+    from rnnt_transducer_b200 import fold_output_projections
+    g = torch.Generator().manual_seed(3)
+    He, Hd, E, D, H = 12, 10, 6, 5, 7
+    r = lambda *s: torch.randn(*s, generator=g, dtype=torch.float64)
+    Weo, beo, Wdo, bdo, W1, b1 = r(E, He), r(E), r(D, Hd), r(D), r(H, E + D), r(H)
+    x, y = r(4, He), r(4, Hd)
+    ref = torch.cat((x @ Weo.t() + beo, y @ Wdo.t() + bdo), dim=1) @ W1.t() + b1
+    we, wd, b = fold_output_projections(Weo, beo, Wdo, bdo, W1, b1)
+    assert torch.allclose(x @ we.t() + y @ wd.t() + b, ref, atol=1e-12)
+    import pytest
+    with pytest.raises(ValueError):
+        fold_output_projections(Weo, beo, Wdo, bdo, W1[:, :-1], b1)
