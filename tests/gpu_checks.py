@@ -198,3 +198,42 @@ def greedy_matches_oracle(B, T, E, D, H, V, hidden=48, layers=1, seed=5, scale=3
     want = greedy_search(enc, lens, dec, joint)
     return {"equal": got == want, "n_symbols": sum(len(w) for w in want),
             "n_frames": int(lens.sum()), "got": got[:2], "want": want[:2]}
+
+
+def full_size_properties(B=32, T=500, U=100, E=320, D=320, H=512, V=4232, seed=2019):
+    """BASELINE.json's headline shape, where no CPU oracle finishes: size-independent properties.
+    (1) every row of dS sums to zero (softmax*c0 minus the two occupation terms), hence sum(db2) = 0;
+    (2) an utterance's loss does not depend on what else is in the batch;
+    (3) the backward pass is linear in grad_output (a power-of-two factor is exact in bf16/fp32
+        up to the order of the fp32 reductions);
+    (4) full T and U against the drop-in boundary (materialised logits) on a 2-utterance slice."""
+    names = ["enc", "dec", "w1", "b1", "w2", "b2"]
+    ins = _joint_inputs(B, T, U, E, D, H, V, "ragged", seed)
+    y, tl, ul = (t.to(DEV) for t in ins[6:])
+
+    def run(scale, sl=slice(None)):
+        leaves = [t.to(DEV).clone().requires_grad_(True) for t in ins[:6]]
+        enc, dec = leaves[0][sl], leaves[1][sl]
+        loss = R.joint_rnnt_loss(enc, dec, *leaves[2:], y[sl], tl[sl], ul[sl], reduction="none")
+        (loss.sum() * scale).backward()
+        return loss.detach(), [t.grad for t in leaves]
+
+    l1, g1 = run(1.0)
+    l2, g2 = run(2.0)
+    ls, _ = run(1.0, slice(0, 3))
+    out = {"loss_mean": float(l1.mean()), "finite": bool(all(torch.isfinite(g).all() for g in g1)),
+           "db2_sum_over_abs": float(g1[5].sum().abs() / g1[5].abs().sum()),
+           "loss_subbatch_rel": float(((ls - l1[:3]).abs() / l1[:3].abs()).max())}
+    for n, a, b in zip(names, g1, g2):
+        out[f"lin_{n}"] = float((b - 2 * a).norm() / (2 * a).norm())
+    # (4) drop-in boundary on two utterances at full T, U, fed the bf16-consistent logits
+    enc, dec, w1, b1, w2, b2 = (t.to(DEV) for t in ins[:6])
+    sl = slice(0, 2)
+    pe = torch.nn.functional.linear(enc[sl], w1[:, :E], b1)
+    pd = torch.nn.functional.linear(dec[sl], w1[:, E:])
+    h = torch.tanh(pe.unsqueeze(2) + pd.unsqueeze(1)).to(torch.bfloat16).float()
+    logits = (h @ w2.to(torch.bfloat16).float().t() + b2).contiguous()
+    ld = R.rnnt_loss(logits, y[sl], tl[sl], ul[sl], reduction="none")
+    torch.cuda.synchronize()
+    out["loss_vs_dropin_rel"] = float(((l1[sl] - ld).abs() / ld.abs()).max())
+    return out

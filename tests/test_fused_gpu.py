@@ -78,3 +78,14 @@ def test_greedy_decode_matches_reference_loop(dims):
     m = G.greedy_matches_oracle(*dims)
     assert m["equal"], m
     assert 0 < m["n_symbols"] < m["n_frames"], m   # the case exercises both blanks and symbols
+
+
+def test_full_size_properties_at_the_headline_shape():
+    # B=32, T=500, U=100, V=4232, H=512 (BASELINE.json configs[2]); see the check's docstring
+    m = G.full_size_properties()
+    assert m["finite"], m
+    assert m["db2_sum_over_abs"] < 2e-3, m          # bf16 rounding of dS leaves ~1e-4
+    assert m["loss_subbatch_rel"] < 1e-6, m
+    assert m["loss_vs_dropin_rel"] < 2e-5, m
+    for n in GRADS:
+        assert m[f"lin_{n}"] < 1e-5, (n, m)
