@@ -23,7 +23,7 @@ from . import _lib
 from ._shard import allreduce_grads_and_loss, global_mean_loss, shard_batch
 
 __all__ = ["RNNTLoss", "rnnt_loss", "JointNet", "JointRNNTLoss", "joint_rnnt_loss",
-           "fold_output_projections", "ProjectedJointRNNTLoss", "greedy_decode",
+           "fold_output_projections", "ProjectedJointRNNTLoss", "greedy_decode", "GreedyDecoder",
            "build_extension", "extension_path", "selftest_gemm", "KernelTimer",
            "shard_batch", "global_mean_loss", "allreduce_grads_and_loss"]
 
@@ -523,6 +523,41 @@ def greedy_decode(enc_state, inputs_length, decoder: nn.Module, joint: nn.Module
             tokens.scatter_(1, counts.unsqueeze(1), torch.where(emit, pred, torch.zeros_like(pred)).unsqueeze(1))
             counts += emit
     return tokens, counts
+
+
+class GreedyDecoder:
+    """``GreedyDecoder(decoder, joint)(enc_state, inputs_length) -> (tokens, counts)``:
+    ``greedy_decode`` with the whole frame loop captured once per input shape in a CUDA graph
+    (the loop is launch bound: ~15 small launches per frame) and
+    replayed on static buffers. Weights are read at replay time, so parameter updates between
+    calls are seen; a change of shape captures a new graph. ``tokens``/``counts`` are views of
+    static buffers: clone them if they must survive the next call."""
+
+    def __init__(self, decoder: nn.Module, joint: nn.Module, blank: int = 0):
+        self.decoder, self.joint, self.blank = decoder, joint, blank
+        self._graphs = {}
+
+    @torch.no_grad()
+    def __call__(self, enc_state, inputs_length):
+        key = (tuple(enc_state.shape), enc_state.device)
+        ent = self._graphs.get(key)
+        if ent is None:
+            enc_s = enc_state.detach().clone()
+            len_s = inputs_length.to(enc_state.device).long().clone()
+            side = torch.cuda.Stream(device=enc_state.device)
+            side.wait_stream(torch.cuda.current_stream(enc_state.device))
+            with torch.cuda.stream(side):  # warm-up off the capture: lazy init of cuDNN / cuBLAS
+                greedy_decode(enc_s, len_s, self.decoder, self.joint, self.blank)
+            torch.cuda.current_stream(enc_state.device).wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                out = greedy_decode(enc_s, len_s, self.decoder, self.joint, self.blank)
+            ent = self._graphs[key] = (graph, enc_s, len_s, out)
+        graph, enc_s, len_s, out = ent
+        enc_s.copy_(enc_state)
+        len_s.copy_(inputs_length.to(enc_s.device))
+        graph.replay()
+        return out
 
 
 def selftest_gemm(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:

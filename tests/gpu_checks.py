@@ -196,7 +196,11 @@ def greedy_matches_oracle(B, T, E, D, H, V, hidden=48, layers=1, seed=5, scale=3
     tokens, counts = R.greedy_decode(enc, lens, dec, joint)
     got = [tokens[i, :int(counts[i])].tolist() for i in range(B)]
     want = greedy_search(enc, lens, dec, joint)
-    return {"equal": got == want, "n_symbols": sum(len(w) for w in want),
+    gd = R.GreedyDecoder(dec, joint)
+    for _ in range(2):  # capture, then a pure replay
+        tg, cg = gd(enc, lens)
+    graph_equal = [tg[i, :int(cg[i])].tolist() for i in range(B)] == want
+    return {"equal": got == want, "graph_equal": graph_equal, "n_symbols": sum(len(w) for w in want),
             "n_frames": int(lens.sum()), "got": got[:2], "want": want[:2]}
 
 

@@ -77,6 +77,7 @@ def test_greedy_decode_matches_reference_loop(dims):
     # SURVEY 8(f)-3 (rnnt/model.py:74-111): same token sequences as the per-utterance loop
     m = G.greedy_matches_oracle(*dims)
     assert m["equal"], m
+    assert m["graph_equal"], m                      # GreedyDecoder: CUDA-graph capture + replay
     assert 0 < m["n_symbols"] < m["n_frames"], m   # the case exercises both blanks and symbols
 
 
