@@ -173,6 +173,17 @@ int rnnt_b200_dh_reduce(const void* dh_bf16, const void* h_stash,
                         int B, int T, int U1, int H, int tile_lo, int tile_hi, float dh_scale,
                         float* dp_enc, float* dp_dec, void* stream);
 
+/* Fused backward, weight/bias gradient of project_layer for one staged dS chunk:
+ *   dw2[v, j] += sum_r dS[r, v] * h[r, j]      (v < ds_pitch(V), j < H)      (rnnt/model.py:16,35)
+ *   db2[v]    += sum_r dS[r, v]
+ * ds: bf16, rows x rnnt_b200_ds_pitch(V), 128-byte aligned; h_rows: the chunk's first row of the h
+ * stash (bf16, pitch rnnt_b200_h_pitch(H)); rows a multiple of 64; H in {256, 512}.
+ * dw2 (ds_pitch(V), H) and db2 (ds_pitch(V)) float32, zeroed by the caller before the first chunk
+ * (split-K partial sums are added with red.global.add). tcgen05 GEMM with both operands MN-major;
+ * other H use the library GEMM against the ones column of the stash. */
+int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long long rows, int V, int H,
+                       float* dw2, float* db2, void* stream);
+
 /* Greedy decoding, one frame for B <= 64 utterances at once (replaces the per-utterance, per-frame
  * joint + softmax + argmax + .item() of rnnt/model.py:90-93 / rnnt/search.py):
  *   pred[b] = argmax_v ( W2 . tanh(pe_t[b,:] + pd[b,:]) + b2 )[v]       (lowest index on ties)

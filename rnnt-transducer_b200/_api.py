@@ -49,7 +49,7 @@ class KernelTimer:
     # kernels launched per C-ABI call
     KERNELS = {"logits_to_planes": 1, "lattice": 2, "planes_to_dlogits": 1, "build_tiles": 1,
                "pack_vocab": 1, "joint_hidden": 1, "joint_fwd": 1, "joint_bwd_ds": 1, "dh_reduce": 1,
-               "joint_step_argmax": 1}
+               "joint_step_argmax": 1, "dw2_gemm": 1}
 
     def __init__(self, events: bool = True):
         self.events = events
@@ -300,7 +300,14 @@ class _JointLossFn(torch.autograd.Function):
             dpe = torch.zeros(B, T, H, dtype=torch.float32, device=dev)
             dpd = torch.zeros(B, U1, H, dtype=torch.float32, device=dev)
             hp = h_stash.shape[1]
-            dw2x = torch.zeros(hp, Vds, dtype=torch.float32, device=dev)  # [dW2 | db2 | unused rows]^T
+            # dW2/db2: own tcgen05 GEMM (csrc/dw2_gemm.cu) where it covers the shape, else the
+            # library GEMM against the ones column of the stash (RNNT_B200_DW2=lib: A/B timing)
+            own_gemm = H % 256 == 0 and os.environ.get("RNNT_B200_DW2", "own") == "own"
+            if own_gemm:
+                dw2x = torch.zeros(Vds, H, dtype=torch.float32, device=dev)
+                db2x = torch.zeros(Vds, dtype=torch.float32, device=dev)
+            else:
+                dw2x = torch.zeros(hp, Vds, dtype=torch.float32, device=dev)  # [dW2 | db2 | unused rows]^T
             chunk = max(2, min(max_tiles, _DS_BUDGET_BYTES // (128 * Vds * 2)))
             nchunk = -(-max_tiles // chunk)
             chunk = -(-max_tiles // nchunk)          # balanced chunks,
@@ -319,7 +326,11 @@ class _JointLossFn(torch.autograd.Function):
                 # two plain library GEMMs on the staged bf16 gradient tile (fp32 accumulate/out)
                 with _region("lib_gemm_dh"):
                     dh = torch.mm(dsc, w2v)                                            # (rows, H) bf16
-                with _region("lib_gemm_dw2"):
+                if own_gemm:
+                    _call("dw2_gemm", L.rnnt_b200_dw2_gemm, _ptr(dsc), h_stash.data_ptr() + lo * 128 * hp * 2,
+                          rows, V, H, _ptr(dw2x), _ptr(db2x), st)
+                else:
+                  with _region("lib_gemm_dw2"):
                     # K = rows is huge and the output (pitch x Vds) small: split K (batched GEMM;
                     # measured best, profiles/r01_notes.md). Column H of the stash is 1 for valid
                     # cells, so row H of the product is db2; the stash pitch (H+32) and this
@@ -331,8 +342,11 @@ class _JointLossFn(torch.autograd.Function):
                                       out_dtype=torch.float32).sum(0)
                 _call("dh_reduce", L.rnnt_b200_dh_reduce, _ptr(dh), _ptr(h_stash), _ptr(act_lens), _ptr(label_lens),
                       B, T, U1, H, lo, hi, 1.0, _ptr(dpe), _ptr(dpd), st)
-            dw2 = dw2x[:H, :V].t().contiguous()
-            db2 = dw2x[H, :V].contiguous()
+            if own_gemm:
+                dw2, db2 = dw2x[:V].contiguous(), db2x[:V].contiguous()
+            else:
+                dw2 = dw2x[:H, :V].t().contiguous()
+                db2 = dw2x[H, :V].contiguous()
         return dpe, dpd, dw2, db2, None, None, None, None, None
 
 

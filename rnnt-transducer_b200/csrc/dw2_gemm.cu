@@ -1,0 +1,261 @@
+// [dW2 | db2] += dS^T . [h | 1] for one staged dS chunk -- the weight/bias gradient of
+// project_layer (rnnt/model.py:16,35; the reference gets it from autograd through the
+// materialised logits). The contraction runs over the chunk's ROWS (cells), so both operands are
+// "MN-major" for the tensor core: dS (rows x Vds) supplies A[m = v][k = row], the h stash
+// (rows x pitch) supplies B[n = j][k = row]. The library does this GEMM at N = H + 32 (the ones
+// column that yields db2 rides in the h stash) and loses ~25 % to that shape; here db2 is one extra
+// UMMA of N = 16 against a constant tile of ones, accumulated in 16 spare TMEM columns.
+//
+// Work unit = (K split s, vocabulary tile of 256 rows of dW2, half j of the H = 512 columns): one
+// CTA pair (cta_group::2, UMMA 256 x 256 x 16), fp32 accumulator in 256 TMEM columns per CTA.
+// Per 64-row K block and CTA: two 64(v) x 64(row) and two 64(j) x 64(row) TMA boxes (SWIZZLE_128B:
+// a box lands as 64 rows of 128 bytes = eight 8-row swizzle atoms, exactly the canonical MN-major
+// layout ((8,n),(8,k)) : ((1,LBO),(8,SBO)) in 16-byte units with SBO = 1024 B between 8-row groups
+// and LBO = 8192 B between the two 64-wide blocks). The two units (j halves) of a (split, tile)
+// run on neighbouring pairs at the same time, so the second read of dS hits L2.
+// Warps: 0 dS TMA producer, 6 h TMA producer, 1 MMA issuer (+ TMEM), 2-5 epilogue (TMEM ->
+// red.global.add.v4.f32).
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <stdlib.h>
+#include "common.cuh"
+#include "sm100_ptx.cuh"
+#include "tma_host.cuh"
+
+using namespace sm100;
+
+namespace {
+
+constexpr int GW_THREADS = 224;  // warps: 0 dS TMA, 1 MMA, 2-5 epilogue, 6 h TMA
+constexpr int GW_STAGES = 7;
+constexpr int GW_BLOCK = 64 * 128;           // one 64 x 64 bf16 box
+constexpr int GW_STAGE = 4 * GW_BLOCK;       // A: 2 boxes (128 v), B: 2 boxes (128 j)
+constexpr int GW_ONES = 16 * 128;            // 16 k-rows x 128 B of bf16 1.0
+constexpr int GW_SMEM = GW_STAGES * GW_STAGE + GW_ONES + 256;
+
+struct GwCtl {
+  uint64_t full[GW_STAGES], empty[GW_STAGES], acc_full, acc_empty;
+  uint32_t tmem_base;
+};
+
+struct GwParams {
+  float* dw2;      // (Vds, H) fp32, accumulated
+  float* db2;      // (Vds) fp32, accumulated
+  int Vds, H;
+  int nvt, nj;     // vocabulary tiles of 256, column halves of 256
+  int ksteps;      // 64-row K blocks in the chunk
+  int splits, ks_per_split;
+  int debug;  // RNNT_B200_DW2_DEBUG (timing experiments): 1 no ones-MMA, 2 no main MMA, 4 no epilogue adds, 8 no TMA loads
+};
+
+// MN-major operand, SWIZZLE_128B (see the header comment); version 1 = sm_100.
+__device__ __forceinline__ uint64_t umma_desc_mn128(uint32_t saddr, uint32_t lbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)(lbo_bytes >> 4) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+__host__ __device__ constexpr uint32_t umma_idesc_bf16_mn(int M, int N) {
+  return umma_idesc_bf16(M, N) | (1u << 15) | (1u << 16);  // a_major = b_major = MN
+}
+
+__global__ void __launch_bounds__(GW_THREADS, 1)
+dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constant__ CUtensorMap map_h,
+                const GwParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  uint8_t* ones = smem + GW_STAGES * GW_STAGE;
+  GwCtl* ctl = reinterpret_cast<GwCtl*>(ones + GW_ONES);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  // All units of a K split walk the chunk's rows in step: the nj column halves of a vocabulary
+  // tile share their dS boxes and all vocabulary tiles share the h boxes through L2. (A stream-K
+  // split that gave every pair an equal share of the (tile, K) space but different K offsets ran
+  // 25 % slower: h was re-read from HBM once per vocabulary tile.)
+  const int cid = blockIdx.x >> 1, ncl = gridDim.x >> 1;
+  const int n_units = p.splits * p.nvt * p.nj;
+
+  for (int i = threadIdx.x; i < GW_ONES / 4; i += GW_THREADS) reinterpret_cast<uint32_t*>(ones)[i] = 0x3F803F80u;
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_ds);
+    tma_prefetch_desc(&map_h);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < GW_STAGES; ++i) {
+      mbar_init(&ctl->full[i], 4);  // {dS, h} producer x {leader, peer}
+      mbar_init(&ctl->empty[i], 1);
+    }
+    mbar_init(&ctl->acc_full, 1);
+    mbar_init(&ctl->acc_empty, 2 * 4);
+    fence_barrier_init();
+  }
+  fence_proxy_async_smem();  // the ones tile is read by the tensor core (async proxy)
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) {
+    tmem_alloc_pair(&ctl->tmem_base, 512);
+    tmem_relinquish_pair();
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = ctl->tmem_base;
+
+  if (warp == 0 || warp == 6) {
+    // =========================== TMA PRODUCERS ===========================
+    // One thread per operand (a single producer needed longer for its wait + expect_tx + four
+    // TMA issues than the 512 clk the four MMAs of a stage take).
+    const bool is_a = warp == 0;
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int u = cid; u < n_units; u += ncl) {
+        const int jh = u % p.nj, vt = (u / p.nj) % p.nvt, s = u / (p.nj * p.nvt);
+        const int k0 = s * p.ks_per_split, k1 = min(p.ksteps, k0 + p.ks_per_split);
+        const int v0 = vt * 256 + (int)rank * 128, j0 = jh * 256 + (int)rank * 128;
+        for (int k = k0; k < k1; ++k) {
+          mbar_wait(&ctl->empty[stage], phase ^ 1);
+          const uint32_t full = mapa_u32(smem_u32(&ctl->full[stage]), 0);
+          if (p.debug & 8) {  // no loads: the MMAs run on whatever the buffers hold
+            mbar_arrive_cluster(full);
+            if (++stage == GW_STAGES) { stage = 0; phase ^= 1; }
+            continue;
+          }
+          if (rank == 0) mbar_arrive_expect_tx(&ctl->full[stage], GW_STAGE);  // this operand, both CTAs
+          else mbar_arrive_cluster(full);
+          uint8_t* st = smem + stage * GW_STAGE + (is_a ? 0 : 2 * GW_BLOCK);
+          const CUtensorMap* map = is_a ? &map_ds : &map_h;
+          const int c0 = is_a ? v0 : j0;
+          tma_load_2d_pair(st, map, full, c0, k * 64);
+          tma_load_2d_pair(st + GW_BLOCK, map, full, c0 + 64, k * 64);
+          if (++stage == GW_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // =========================== MMA ISSUER (leader CTA) ===========================
+    if (rank == 0) {
+      constexpr uint32_t idesc_main = umma_idesc_bf16_mn(256, 256);
+      constexpr uint32_t idesc_ones = umma_idesc_bf16_mn(256, 16);
+      const uint32_t s0 = smem_u32(smem);
+      const uint64_t ones_desc = umma_desc_mn128(smem_u32(ones), GW_BLOCK);
+      uint32_t stage = 0, phase = 0;
+      int it = 0;
+      for (int u = cid; u < n_units; u += ncl, ++it) {
+        const int jh = u % p.nj, s = u / (p.nj * p.nvt);
+        const int k0 = s * p.ks_per_split, k1 = min(p.ksteps, k0 + p.ks_per_split);
+        mbar_wait(&ctl->acc_empty, (it & 1) ^ 1);
+        tc_fence_after();
+        for (int k = k0; k < k1; ++k) {
+          mbar_wait(&ctl->full[stage], phase);
+          tc_fence_after();
+          if (elect_one_sync()) {
+            const uint32_t a0 = s0 + stage * GW_STAGE, b0 = a0 + 2 * GW_BLOCK;
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {  // 16 rows = two 8-row swizzle atoms = 2048 bytes
+              const uint64_t adesc = umma_desc_mn128(a0 + kk * 2048, GW_BLOCK);
+              const uint64_t bdesc = umma_desc_mn128(b0 + kk * 2048, GW_BLOCK);
+              const uint32_t acc = (k > k0 || kk > 0) ? 1u : 0u;
+              if (!(p.debug & 2)) umma_bf16_ss_pair(tmem_base, adesc, bdesc, idesc_main, acc);
+              if (jh == 0 && !(p.debug & 1)) umma_bf16_ss_pair(tmem_base + 256, adesc, ones_desc, idesc_ones, acc);
+            }
+            umma_commit_pair_mc(&ctl->empty[stage], 3);
+            if (k == k1 - 1) umma_commit_pair_mc(&ctl->acc_full, 3);
+          }
+          __syncwarp();
+          if (++stage == GW_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp < 6) {
+    // =========================== EPILOGUE ===========================
+    const int q = warp & 3;  // TMEM lane quadrant this warp may read
+    int it = 0;
+    for (int u = cid; u < n_units; u += ncl, ++it) {
+      const int jh = u % p.nj, vt = (u / p.nj) % p.nvt;
+      const int v = vt * 256 + (int)rank * 128 + q * 32 + lane;
+      {
+        mbar_wait(&ctl->acc_full, it & 1);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+        float* dst = p.dw2 + (size_t)v * p.H + jh * 256;
+#pragma unroll 1
+        for (int c = 0; c < 16; ++c) {
+          float z[16];
+          tmem_ld_32x16(taddr + c * 16, z);
+          tmem_ld_wait();
+          if (v < p.Vds && !(p.debug & 4)) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              atomicAdd(reinterpret_cast<float4*>(dst + c * 16) + i,
+                        make_float4(z[4 * i], z[4 * i + 1], z[4 * i + 2], z[4 * i + 3]));
+          }
+        }
+        if (jh == 0) {
+          float z[16];
+          tmem_ld_32x16(taddr + 256, z);
+          tmem_ld_wait();
+          if (v < p.Vds) atomicAdd(p.db2 + v, z[0]);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&ctl->acc_empty), 0));
+    }
+  }
+  __syncwarp();
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) tmem_dealloc_pair(tmem_base, 512);
+}
+
+}  // namespace
+
+extern "C" int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long long rows, int V, int H,
+                                  float* dw2, float* db2, void* stream) {
+  if (!ds_bf16 || !h_rows || !dw2 || !db2) return RNNT_B200_E_NULL;
+  if (rows < 0 || (rows & 63) || V <= 0 || H < 256 || H > 512 || (H & 255)) return RNNT_B200_E_SHAPE;
+  if ((reinterpret_cast<uintptr_t>(ds_bf16) & 127u) || (reinterpret_cast<uintptr_t>(h_rows) & 15u) ||
+      (reinterpret_cast<uintptr_t>(dw2) & 15u))
+    return RNNT_B200_E_ALIGN;
+  if (rows == 0) return RNNT_B200_OK;
+  const int Vds = rnnt_b200_ds_pitch(V);
+  CUtensorMap mds, mh;
+  int rc = make_map_bf16(&mds, ds_bf16, (uint64_t)rows, (uint64_t)Vds, (uint64_t)Vds, 64, 64,
+                         CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc != RNNT_B200_OK) return rc;
+  rc = make_map_bf16(&mh, h_rows, (uint64_t)rows, (uint64_t)H, (uint64_t)rnnt_hp(H), 64, 64,
+                     CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc != RNNT_B200_OK) return rc;
+  GwParams p;
+  p.dw2 = dw2; p.db2 = db2; p.Vds = Vds; p.H = H;
+  p.nvt = (Vds + 255) / 256;
+  p.nj = H / 256;
+  p.ksteps = (int)(rows / 64);
+  const int pairs = sm_count() / 2;
+  int splits = pairs / (p.nvt * p.nj);
+  if (splits < 1) splits = 1;
+  if (splits > p.ksteps) splits = p.ksteps;
+  p.ks_per_split = (p.ksteps + splits - 1) / splits;
+  p.splits = (p.ksteps + p.ks_per_split - 1) / p.ks_per_split;  // every unit has K blocks
+  { const char* d = getenv("RNNT_B200_DW2_DEBUG"); p.debug = d ? atoi(d) : 0; }
+  const int units = p.splits * p.nvt * p.nj;
+  const int grid = 2 * (units < pairs ? units : pairs);
+  cudaError_t e = cudaFuncSetAttribute(dw2_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GW_SMEM);
+  if (e != cudaSuccess) return (int)e;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(GW_THREADS);
+  cfg.dynamicSmemBytes = GW_SMEM;
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  e = cudaLaunchKernelEx(&cfg, dw2_gemm_kernel, mds, mh, p);
+  if (e != cudaSuccess) return (int)e;
+  return RNNT_B200_OK;
+}

@@ -36,6 +36,7 @@
 #include <type_traits>
 #include "common.cuh"
 #include "sm100_ptx.cuh"
+#include "tma_host.cuh"
 
 
 using namespace sm100;
@@ -737,45 +738,6 @@ selftest_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
 }
 
 // ------------------------------------------------------------------ host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
-                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
-                                  CUtensorMapFloatOOBfill);
-
-EncodeTiledFn get_encode_fn() {
-  static EncodeTiledFn fn = nullptr;  // idempotent, benign race: same value written
-  if (!fn) {
-    void* ptr = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = (EncodeTiledFn)ptr;
-  }
-  return fn;
-}
-
-// bf16 row-major matrix (rows x cols, row pitch in elements) -> 2-D tiled map with box
-// (box_cols x box_rows) and the given swizzle.
-int make_map_bf16(CUtensorMap* m, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_elems,
-                  uint32_t box_cols, uint32_t box_rows, CUtensorMapSwizzle sw) {
-  EncodeTiledFn fn = get_encode_fn();
-  if (!fn) return RNNT_B200_E_DRIVER;
-  cuuint64_t dims[2] = {cols, rows};
-  cuuint64_t strides[1] = {pitch_elems * 2};
-  cuuint32_t box[2] = {box_cols, box_rows};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS ? RNNT_B200_OK : RNNT_B200_E_DRIVER;
-}
-
-int sm_count() {
-  int dev = 0, n = 148;
-  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-  return n;
-}
-
 int pick_slots(int H, int BN, int mode) {
   int s = kMaxSlots;
   while (s > 2 && smem_bytes_for(H, BN, s, mode) > kSmemLimit) --s;

@@ -241,3 +241,24 @@ def full_size_properties(B=32, T=500, U=100, E=320, D=320, H=512, V=4232, seed=2
     torch.cuda.synchronize()
     out["loss_vs_dropin_rel"] = float(((l1[sl] - ld).abs() / ld.abs()).max())
     return out
+
+
+def dw2_gemm_vs_torch(rows, V, H, seed=0):
+    """rnnt_b200_dw2_gemm (tcgen05, MN-major operands, split-K red.global.add) against fp32 torch
+    products of the same bf16 operands; called twice to check that it ACCUMULATES."""
+    from rnnt_transducer_b200 import _lib
+    L = _lib.lib()
+    Vds, hp = L.rnnt_b200_ds_pitch(V), L.rnnt_b200_h_pitch(H)
+    g = torch.Generator().manual_seed(seed)
+    ds = (torch.randn(rows, Vds, generator=g) * 0.05).to(torch.bfloat16).to(DEV)
+    h = torch.tanh(torch.randn(rows, hp, generator=g)).to(torch.bfloat16).to(DEV)
+    dw2 = torch.zeros(Vds, H, device=DEV)
+    db2 = torch.zeros(Vds, device=DEV)
+    st = torch.cuda.current_stream().cuda_stream
+    for _ in range(2):
+        rc = L.rnnt_b200_dw2_gemm(ds.data_ptr(), h.data_ptr(), rows, V, H, dw2.data_ptr(), db2.data_ptr(), st)
+        assert rc == 0, rc
+    torch.cuda.synchronize()
+    ref = 2 * (ds.double().t() @ h[:, :H].double())
+    refb = 2 * ds.double().sum(0)
+    return {"dw2_rel_l2": rel_l2(dw2.cpu(), ref.cpu()), "db2_rel_l2": rel_l2(db2.cpu(), refb.cpu())}

@@ -90,3 +90,10 @@ def test_full_size_properties_at_the_headline_shape():
     assert m["loss_vs_dropin_rel"] < 2e-5, m
     for n in GRADS:
         assert m[f"lin_{n}"] < 1e-5, (n, m)
+
+
+@pytest.mark.parametrize("rows,V,H", [(64, 200, 256), (128, 256, 512), (1024, 500, 512), (8192, 4232, 512)])
+def test_dw2_gemm_matches_torch(rows, V, H):
+    # the MN-major tcgen05 GEMM behind dW2/db2 on its own (fp32 accumulation of bf16 products)
+    m = G.dw2_gemm_vs_torch(rows, V, H)
+    assert m["dw2_rel_l2"] < 1e-5 and m["db2_rel_l2"] < 1e-5, m

@@ -122,3 +122,13 @@ def test_fold_output_projections_algebra():
     import pytest
     with pytest.raises(ValueError):
         fold_output_projections(Weo, beo, Wdo, bdo, W1[:, :-1], b1)
+
+
+def test_dw2_gemm_rejects_bad_arguments():
+    L = _lib.lib()
+    a = 256  # aligned fake pointer: argument checks run before anything is dereferenced
+    assert L.rnnt_b200_dw2_gemm(None, a, 128, 100, 512, a, a, None) == -1
+    assert L.rnnt_b200_dw2_gemm(a, a, 100, 100, 512, a, a, None) == -2      # rows % 64
+    assert L.rnnt_b200_dw2_gemm(a, a, 128, 100, 128, a, a, None) == -2      # H not a multiple of 256
+    assert L.rnnt_b200_dw2_gemm(a + 2, a, 128, 100, 512, a, a, None) == -4  # alignment
+    assert L.rnnt_b200_dw2_gemm(a, a, 0, 100, 512, a, a, None) == 0         # nothing to do
