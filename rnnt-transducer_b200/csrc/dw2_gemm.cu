@@ -148,6 +148,10 @@ dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
         const int k0 = s * p.ks_per_split, k1 = min(p.ksteps, k0 + p.ks_per_split);
         mbar_wait(&ctl->acc_empty, (it & 1) ^ 1);
         tc_fence_after();
+        // The db2 UMMAs are dealt to the nj column halves by K-block parity: the partner units
+        // stay in step (the one that did all of them fell ~6 % behind, ~100 MB of dS by the end
+        // of a chunk -- more than L2 holds -- and re-read its dS boxes from HBM).
+        const int k_ones0 = k0 + ((p.nj == 2 && ((k0 + jh) & 1)) ? 1 : 0);
         for (int k = k0; k < k1; ++k) {
           mbar_wait(&ctl->full[stage], phase);
           tc_fence_after();
@@ -159,7 +163,8 @@ dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
               const uint64_t bdesc = umma_desc_mn128(b0 + kk * 2048, GW_BLOCK);
               const uint32_t acc = (k > k0 || kk > 0) ? 1u : 0u;
               if (!(p.debug & 2)) umma_bf16_ss_pair(tmem_base, adesc, bdesc, idesc_main, acc);
-              if (jh == 0 && !(p.debug & 1)) umma_bf16_ss_pair(tmem_base + 256, adesc, ones_desc, idesc_ones, acc);
+              if ((p.nj == 1 || ((k + jh) & 1) == 0) && !(p.debug & 1))
+                umma_bf16_ss_pair(tmem_base + 256, adesc, ones_desc, idesc_ones, (k > k_ones0 || kk > 0) ? 1u : 0u);
             }
             umma_commit_pair_mc(&ctl->empty[stage], 3);
             if (k == k1 - 1) umma_commit_pair_mc(&ctl->acc_full, 3);
@@ -174,7 +179,9 @@ dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
     const int q = warp & 3;  // TMEM lane quadrant this warp may read
     int it = 0;
     for (int u = cid; u < n_units; u += ncl, ++it) {
-      const int jh = u % p.nj, vt = (u / p.nj) % p.nvt;
+      const int jh = u % p.nj, vt = (u / p.nj) % p.nvt, s = u / (p.nj * p.nvt);
+      const int k0 = s * p.ks_per_split, k1 = min(p.ksteps, k0 + p.ks_per_split);
+      const bool has_ones = k0 + ((p.nj == 2 && ((k0 + jh) & 1)) ? 1 : 0) < k1;
       const int v = vt * 256 + (int)rank * 128 + q * 32 + lane;
       {
         mbar_wait(&ctl->acc_full, it & 1);
@@ -193,7 +200,7 @@ dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
                         make_float4(z[4 * i], z[4 * i + 1], z[4 * i + 2], z[4 * i + 3]));
           }
         }
-        if (jh == 0) {
+        if (has_ones) {
           float z[16];
           tmem_ld_32x16(taddr + 256, z);
           tmem_ld_wait();
