@@ -74,3 +74,18 @@ def test_uniform_logits_closed_form():
                                          torch.tensor([U], dtype=torch.int32, device="cuda"))
         ref = uniform_closed_form(T, U, V)
         assert abs(float(l) - ref) / ref < 1e-6
+
+
+def test_hypothesis_ragged_shapes_against_the_oracle():
+    # randomly drawn (B,T,U,V) and ragged lengths through the C ABI
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=20, deadline=None, derandomize=True)
+    @given(st.integers(1, 4), st.integers(1, 40), st.integers(0, 45), st.sampled_from([3, 8, 49, 130, 515]),
+           st.sampled_from(["ragged", "edge", "full"]), st.integers(0, 2 ** 16))
+    def check(B, T, U, V, mode, seed):
+        m = G.dropin_synth(B, T, U, V, mode=mode, seed=seed)
+        assert m["loss_rel"] < LOSS_RTOL, m
+        assert m["grad_max_abs"] < GRAD_ATOL, m
+        assert m["grad_outside_window_max"] == 0.0, m
+    check()

@@ -103,3 +103,30 @@ def test_c_oracle_rejects_bad_arguments():
         C.rnnt_loss(x, np.array([[1]]), np.array([3]), np.array([1]))   # act_len > T
     with pytest.raises(ValueError):
         C.rnnt_loss(x, np.array([[1]]), np.array([2]), np.array([2]))   # label_len > U
+
+
+def test_hypothesis_ragged_shapes_c_oracle_vs_torch_oracle():
+    # randomly drawn ragged shapes; the two independent restatements
+    # (C, OpenMP float64 / torch autograd float64) must agree and keep the structural properties
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=25, deadline=None, derandomize=True)
+    @given(st.integers(1, 3), st.integers(1, 7), st.integers(0, 5), st.integers(2, 11), st.integers(0, 2 ** 16))
+    def check(B, T, U, V, seed):
+        g = torch.Generator().manual_seed(seed)
+        x = torch.randn(B, T, U + 1, V, generator=g)
+        y = torch.randint(1, V, (B, max(U, 1)), generator=g, dtype=torch.int32)[:, :U]
+        tl = torch.randint(1, T + 1, (B,), generator=g, dtype=torch.int32)
+        ul = torch.randint(0, U + 1, (B,), generator=g, dtype=torch.int32)
+        xd = x.double().requires_grad_(True)
+        lo = O.rnnt_loss(xd, y, tl, ul)
+        lo.sum().backward()
+        lc, gc = C.rnnt_loss(x.numpy(), y.numpy().reshape(B, U), tl.numpy(), ul.numpy())
+        assert np.allclose(lc, lo.detach().numpy(), rtol=1e-10)
+        assert max_abs(gc, xd.grad) < 1e-6
+        for b in range(B):
+            tb, ub = int(tl[b]), int(ul[b])
+            assert float(np.abs(gc[b, tb:]).max(initial=0.0)) == 0.0
+            assert float(np.abs(gc[b, :, ub + 1:]).max(initial=0.0)) == 0.0
+            assert float(np.abs(gc[b, :tb, :ub + 1].sum(-1)).max()) < 1e-5   # softmax-Jacobian rows sum to 0
+    check()
