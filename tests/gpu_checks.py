@@ -262,3 +262,4 @@ def dw2_gemm_vs_torch(rows, V, H, seed=0):
     ref = 2 * (ds.double().t() @ h[:, :H].double())
     refb = 2 * ds.double().sum(0)
     return {"dw2_rel_l2": rel_l2(dw2.cpu(), ref.cpu()), "db2_rel_l2": rel_l2(db2.cpu(), refb.cpu())}
+

@@ -97,3 +97,4 @@ def test_dw2_gemm_matches_torch(rows, V, H):
     # the MN-major tcgen05 GEMM behind dW2/db2 on its own (fp32 accumulation of bf16 products)
     m = G.dw2_gemm_vs_torch(rows, V, H)
     assert m["dw2_rel_l2"] < 1e-5 and m["db2_rel_l2"] < 1e-5, m
+
