@@ -114,7 +114,7 @@ __host__ __device__ inline int smem_bytes_for(int H, int BN, int slots, int mode
 __device__ __forceinline__ void tanh4(const float (&x)[4], float (&y)[4]) {
   float d[4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) d[i] = ex2_approx(fminf(x[i], 10.f) * (2.f * RNNT_LOG2E)) + 1.f;
+  for (int i = 0; i < 4; ++i) d[i] = ex2_approx((x[i] > 10.f ? 10.f : x[i]) * (2.f * RNNT_LOG2E)) + 1.f;  // NaN stays NaN
   const float p01 = d[0] * d[1], p23 = d[2] * d[3];
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(p01 * p23));
