@@ -7,4 +7,8 @@ __path__.insert(0, _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.absp
                                  "rnnt-transducer_b200"))
 
 from ._api import *  # noqa: F401,F403,E402
-from ._api import __all__  # noqa: E402
+from ._model import *  # noqa: F401,F403,E402
+from ._api import __all__ as _api_all  # noqa: E402
+from ._model import __all__ as _model_all  # noqa: E402
+
+__all__ = list(_api_all) + list(_model_all)

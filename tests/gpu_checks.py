@@ -263,3 +263,35 @@ def dw2_gemm_vs_torch(rows, V, H, seed=0):
     refb = 2 * ds.double().sum(0)
     return {"dw2_rel_l2": rel_l2(dw2.cpu(), ref.cpu()), "db2_rel_l2": rel_l2(db2.cpu(), refb.cpu())}
 
+
+
+def transducer_vs_reference_fixture():
+    """the assembled Transducer with the reference's weights (fixture from the unmodified
+    reference): recognize() must return the reference's greedy tokens; the training forward (fused loss,
+    folded projections) is checked against the float64 oracle fed the reference's encoder/decoder
+    outputs, and against the unfolded variant."""
+    from tests.helpers import load_ref_model_tiny
+    model, g = load_ref_model_tiny()
+    model = model.to(DEV)
+    t = lambda k: torch.from_numpy(g[k])
+    tokens = model.recognize(t("inputs").to(DEV), t("inputs_length"))
+    want = [g["tokens"][i, :int(g["token_counts"][i])].tolist() for i in range(len(tokens))]
+    args = (t("inputs").to(DEV), t("inputs_length").to(DEV), t("targets").to(DEV), t("targets_length").to(DEV))
+    model.train()
+    loss = model(*args)
+    loss.backward()
+    grads_finite = all(p.grad is not None and bool(torch.isfinite(p.grad).all()) for p in model.parameters())
+    import copy
+    m2 = copy.deepcopy(model)
+    m2.fold_projections = False
+    loss2 = m2(*args)
+    sd = {k: v.detach().cpu().double() for k, v in model.joint.state_dict().items()}
+    Umax = int(g["targets_length"].max())
+    lo = O.joint_rnnt_loss(t("enc_state").double(), t("dec_state").double(), sd["forward_layer.weight"],
+                           sd["forward_layer.bias"], sd["project_layer.weight"], sd["project_layer.bias"],
+                           t("targets")[:, :Umax].int(), t("inputs_length").int(), t("targets_length").int(),
+                           reduction="mean")
+    torch.cuda.synchronize()
+    return {"tokens_equal": tokens == want, "tokens": tokens, "want": want, "grads_finite": grads_finite,
+            "loss_rel_oracle": float(abs(float(loss) - float(lo)) / abs(float(lo))),
+            "loss_rel_unfolded": float(abs(float(loss) - float(loss2)) / abs(float(loss2)))}

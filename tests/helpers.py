@@ -65,3 +65,20 @@ def make_decoder(hidden_size, vocab_size, output_size, n_layers=1, seed=0):
 
     torch.manual_seed(seed)
     return Decoder()
+
+
+REF_MODEL_TINY_CFG = dict(enc=dict(type="lstm", hidden_size=16, output_size=12, n_layers=2, bidirectional=True),
+                          dec=dict(type="lstm", hidden_size=16, output_size=12, n_layers=1),
+                          joint=dict(input_size=24, inner_size=64), vocab_size=30, share_weight=False,
+                          share_embedding=False, feature_dim=20, dropout=0.0)  # = tests/golden/make_model_golden.py
+
+
+def load_ref_model_tiny():
+    """(Transducer with the reference's weights, fixture dict) from tests/golden/ref_model_tiny.npz."""
+    import torch
+    import rnnt_transducer_b200 as R
+    g = load_golden("ref_model_tiny")
+    model = R.Transducer(REF_MODEL_TINY_CFG).eval()
+    sd = {k[4:]: torch.from_numpy(g[k]) for k in g if k.startswith("sd__")}
+    model.load_state_dict(sd, strict=True)   # same key names and shapes as the reference's Transducer
+    return model, g

@@ -98,3 +98,11 @@ def test_dw2_gemm_matches_torch(rows, V, H):
     m = G.dw2_gemm_vs_torch(rows, V, H)
     assert m["dw2_rel_l2"] < 1e-5 and m["db2_rel_l2"] < 1e-5, m
 
+
+
+def test_transducer_with_reference_weights():
+    # greedy tokens pinned on the reference's own recognize(); loss within the bf16-path tolerance
+    m = G.transducer_vs_reference_fixture()
+    assert m["tokens_equal"], m
+    assert m["grads_finite"], m
+    assert m["loss_rel_oracle"] < 2e-3 and m["loss_rel_unfolded"] < 2e-3, m

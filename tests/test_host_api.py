@@ -132,3 +132,20 @@ def test_dw2_gemm_rejects_bad_arguments():
     assert L.rnnt_b200_dw2_gemm(a, a, 128, 100, 128, a, a, None) == -2      # H not a multiple of 256
     assert L.rnnt_b200_dw2_gemm(a + 2, a, 128, 100, 512, a, a, None) == -4  # alignment
     assert L.rnnt_b200_dw2_gemm(a, a, 0, 100, 512, a, a, None) == 0         # nothing to do
+
+
+def test_transducer_loads_reference_checkpoint_and_matches_its_encoder_decoder_joint():
+    # the module tree mirrors rnnt/model.py:40-59, so the reference's own state_dict
+    # (fixture made by tests/golden/make_model_golden.py from the unmodified reference) loads strictly
+    # and the stock-PyTorch parts reproduce the reference's outputs on CPU
+    import torch
+    from tests.helpers import load_ref_model_tiny, max_abs
+    model, g = load_ref_model_tiny()
+    t = lambda k: torch.from_numpy(g[k])
+    with torch.no_grad():
+        enc, _ = model.encoder(t("inputs"), t("inputs_length"))
+        concat = torch.nn.functional.pad(t("targets"), pad=(1, 0, 0, 0), value=0)
+        dec, _ = model.decoder(concat, t("targets_length").add(1))
+        logits = model.joint(enc, dec)
+    assert max_abs(enc, g["enc_state"]) < 1e-5 and max_abs(dec, g["dec_state"]) < 1e-5
+    assert max_abs(logits, g["logits"]) < 1e-3 * float(abs(g["logits"]).max())
