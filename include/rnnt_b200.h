@@ -177,7 +177,7 @@ int rnnt_b200_dh_reduce(const void* dh_bf16, const void* h_stash,
  *   dw2[v, j] += sum_r dS[r, v] * h[r, j]      (v < ds_pitch(V), j < H)      (rnnt/model.py:16,35)
  *   db2[v]    += sum_r dS[r, v]
  * ds: bf16, rows x rnnt_b200_ds_pitch(V), 128-byte aligned; h_rows: the chunk's first row of the h
- * stash (bf16, pitch rnnt_b200_h_pitch(H)); rows a multiple of 64; H in {256, 512}.
+ * stash (bf16, pitch rnnt_b200_h_pitch(H)); rows a multiple of 64; H in {128, 256, 512}.
  * dw2 (ds_pitch(V), H) and db2 (ds_pitch(V)) float32, zeroed by the caller before the first chunk
  * (split-K partial sums are added with red.global.add). tcgen05 GEMM with both operands MN-major;
  * other H use the library GEMM against the ones column of the stash. */

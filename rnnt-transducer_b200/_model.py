@@ -113,8 +113,12 @@ class Transducer(nn.Module):
             enc, _ = self.encoder(inputs, inputs_length)
             dec, _ = self.decoder(concat_targets, targets_length.add(1))
         labels = targets[:, :dec.shape[1] - 1].int().contiguous()  # outputs are trimmed to the longest sequence
+        # Lengths that arrive on the host (as a DataLoader yields them, train.py:24-31) size the
+        # tile loops exactly and cost no device read-back anywhere in the step (the reference
+        # syncs twice per step on .max().item(), train.py:30-33).
+        host_lens = (inputs_length, targets_length) if not (inputs_length.is_cuda or targets_length.is_cuda) else None
         return self.crit(enc.contiguous(), dec.contiguous(), labels, inputs_length.int().to(enc.device),
-                         targets_length.int().to(enc.device))
+                         targets_length.int().to(enc.device), host_lens=host_lens)
 
     @torch.no_grad()
     def recognize(self, inputs, inputs_length):

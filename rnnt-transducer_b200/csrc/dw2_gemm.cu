@@ -42,7 +42,8 @@ struct GwParams {
   float* dw2;      // (Vds, H) fp32, accumulated
   float* db2;      // (Vds) fp32, accumulated
   int Vds, H;
-  int nvt, nj;     // vocabulary tiles of 256, column halves of 256
+  int nvt, nj;     // vocabulary tiles of 256, column units of N
+  int N;           // UMMA N of a unit: 256 (H a multiple of 256) or 128 (H = 128)
   int ksteps;      // 64-row K blocks in the chunk
   int splits, ks_per_split;
   int debug;  // RNNT_B200_DW2_DEBUG (timing experiments): 1 no ones-MMA, 2 no main MMA, 4 no epilogue adds, 8 no TMA loads
@@ -114,7 +115,7 @@ dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
       for (int u = cid; u < n_units; u += ncl) {
         const int jh = u % p.nj, vt = (u / p.nj) % p.nvt, s = u / (p.nj * p.nvt);
         const int k0 = s * p.ks_per_split, k1 = min(p.ksteps, k0 + p.ks_per_split);
-        const int v0 = vt * 256 + (int)rank * 128, j0 = jh * 256 + (int)rank * 128;
+        const int v0 = vt * 256 + (int)rank * 128, j0 = jh * p.N + (int)rank * (p.N / 2);
         for (int k = k0; k < k1; ++k) {
           mbar_wait(&ctl->empty[stage], phase ^ 1);
           const uint32_t full = mapa_u32(smem_u32(&ctl->full[stage]), 0);
@@ -123,13 +124,14 @@ dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
             if (++stage == GW_STAGES) { stage = 0; phase ^= 1; }
             continue;
           }
-          if (rank == 0) mbar_arrive_expect_tx(&ctl->full[stage], GW_STAGE);  // this operand, both CTAs
+          const int nbox = is_a ? 2 : p.N / 128;  // 64-wide boxes of this operand per CTA
+          if (rank == 0) mbar_arrive_expect_tx(&ctl->full[stage], 2 * nbox * GW_BLOCK);  // both CTAs
           else mbar_arrive_cluster(full);
           uint8_t* st = smem + stage * GW_STAGE + (is_a ? 0 : 2 * GW_BLOCK);
           const CUtensorMap* map = is_a ? &map_ds : &map_h;
           const int c0 = is_a ? v0 : j0;
           tma_load_2d_pair(st, map, full, c0, k * 64);
-          tma_load_2d_pair(st + GW_BLOCK, map, full, c0 + 64, k * 64);
+          if (nbox == 2) tma_load_2d_pair(st + GW_BLOCK, map, full, c0 + 64, k * 64);
           if (++stage == GW_STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -137,7 +139,7 @@ dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
   } else if (warp == 1) {
     // =========================== MMA ISSUER (leader CTA) ===========================
     if (rank == 0) {
-      constexpr uint32_t idesc_main = umma_idesc_bf16_mn(256, 256);
+      const uint32_t idesc_main = umma_idesc_bf16_mn(256, p.N);
       constexpr uint32_t idesc_ones = umma_idesc_bf16_mn(256, 16);
       const uint32_t s0 = smem_u32(smem);
       const uint64_t ones_desc = umma_desc_mn128(smem_u32(ones), GW_BLOCK);
@@ -187,9 +189,9 @@ dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
         mbar_wait(&ctl->acc_full, it & 1);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-        float* dst = p.dw2 + (size_t)v * p.H + jh * 256;
+        float* dst = p.dw2 + (size_t)v * p.H + jh * p.N;
 #pragma unroll 1
-        for (int c = 0; c < 16; ++c) {
+        for (int c = 0; c < p.N / 16; ++c) {
           float z[16];
           tmem_ld_32x16(taddr + c * 16, z);
           tmem_ld_wait();
@@ -223,7 +225,7 @@ dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
 extern "C" int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long long rows, int V, int H,
                                   float* dw2, float* db2, void* stream) {
   if (!ds_bf16 || !h_rows || !dw2 || !db2) return RNNT_B200_E_NULL;
-  if (rows < 0 || (rows & 63) || V <= 0 || H < 256 || H > 512 || (H & 255)) return RNNT_B200_E_SHAPE;
+  if (rows < 0 || (rows & 63) || V <= 0 || !(H == 128 || H == 256 || H == 512)) return RNNT_B200_E_SHAPE;
   if ((reinterpret_cast<uintptr_t>(ds_bf16) & 127u) || (reinterpret_cast<uintptr_t>(h_rows) & 15u) ||
       (reinterpret_cast<uintptr_t>(dw2) & 15u))
     return RNNT_B200_E_ALIGN;
@@ -239,7 +241,8 @@ extern "C" int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long 
   GwParams p;
   p.dw2 = dw2; p.db2 = db2; p.Vds = Vds; p.H = H;
   p.nvt = (Vds + 255) / 256;
-  p.nj = H / 256;
+  p.N = H >= 256 ? 256 : 128;
+  p.nj = H / p.N;
   p.ksteps = (int)(rows / 64);
   const int pairs = sm_count() / 2;
   int splits = pairs / (p.nvt * p.nj);

@@ -285,6 +285,7 @@ def transducer_vs_reference_fixture():
     m2 = copy.deepcopy(model)
     m2.fold_projections = False
     loss2 = m2(*args)
+    loss3 = model(args[0], t("inputs_length"), args[2], t("targets_length"))   # lengths on the host
     sd = {k: v.detach().cpu().double() for k, v in model.joint.state_dict().items()}
     Umax = int(g["targets_length"].max())
     lo = O.joint_rnnt_loss(t("enc_state").double(), t("dec_state").double(), sd["forward_layer.weight"],
@@ -294,4 +295,5 @@ def transducer_vs_reference_fixture():
     torch.cuda.synchronize()
     return {"tokens_equal": tokens == want, "tokens": tokens, "want": want, "grads_finite": grads_finite,
             "loss_rel_oracle": float(abs(float(loss) - float(lo)) / abs(float(lo))),
-            "loss_rel_unfolded": float(abs(float(loss) - float(loss2)) / abs(float(loss2)))}
+            "loss_rel_unfolded": float(abs(float(loss) - float(loss2)) / abs(float(loss2))),
+            "loss_rel_host_lens": float(abs(float(loss) - float(loss3)) / abs(float(loss)))}

@@ -129,7 +129,7 @@ def test_dw2_gemm_rejects_bad_arguments():
     a = 256  # aligned fake pointer: argument checks run before anything is dereferenced
     assert L.rnnt_b200_dw2_gemm(None, a, 128, 100, 512, a, a, None) == -1
     assert L.rnnt_b200_dw2_gemm(a, a, 100, 100, 512, a, a, None) == -2      # rows % 64
-    assert L.rnnt_b200_dw2_gemm(a, a, 128, 100, 128, a, a, None) == -2      # H not a multiple of 256
+    assert L.rnnt_b200_dw2_gemm(a, a, 128, 100, 192, a, a, None) == -2      # H not in {128, 256, 512}
     assert L.rnnt_b200_dw2_gemm(a + 2, a, 128, 100, 512, a, a, None) == -4  # alignment
     assert L.rnnt_b200_dw2_gemm(a, a, 0, 100, 512, a, a, None) == 0         # nothing to do
 
