@@ -297,3 +297,28 @@ def transducer_vs_reference_fixture():
             "loss_rel_oracle": float(abs(float(loss) - float(lo)) / abs(float(lo))),
             "loss_rel_unfolded": float(abs(float(loss) - float(loss2)) / abs(float(loss2))),
             "loss_rel_host_lens": float(abs(float(loss) - float(loss3)) / abs(float(loss)))}
+
+
+def dw2_gemm_guard_bands(rows=192, V=300, H=128):
+    """compute-sanitizer is not available on the GPU pool: run the GEMM with its outputs embedded
+    in larger poisoned buffers and check that nothing outside (Vds x H) / (Vds) was touched."""
+    from rnnt_transducer_b200 import _lib
+    L = _lib.lib()
+    Vds, hp = L.rnnt_b200_ds_pitch(V), L.rnnt_b200_h_pitch(H)
+    g = torch.Generator().manual_seed(1)
+    ds = (torch.randn(rows, Vds, generator=g) * 0.05).to(torch.bfloat16).to(DEV)
+    h = torch.tanh(torch.randn(rows, hp, generator=g)).to(torch.bfloat16).to(DEV)
+    pad = 4096
+    big = torch.full((pad + Vds * H + pad,), 7.0, device=DEV)
+    bigb = torch.full((pad + Vds + pad,), 7.0, device=DEV)
+    big[pad:pad + Vds * H] = 0
+    bigb[pad:pad + Vds] = 0
+    st = torch.cuda.current_stream().cuda_stream
+    rc = L.rnnt_b200_dw2_gemm(ds.data_ptr(), h.data_ptr(), rows, V, H, big.data_ptr() + pad * 4,
+                              bigb.data_ptr() + pad * 4, st)
+    torch.cuda.synchronize()
+    ok = bool((big[:pad] == 7).all() and (big[pad + Vds * H:] == 7).all() and
+              (bigb[:pad] == 7).all() and (bigb[pad + Vds:] == 7).all())
+    ref = ds.double().t() @ h[:, :H].double()
+    return {"rc": rc, "guards_intact": ok,
+            "dw2_rel_l2": rel_l2(big[pad:pad + Vds * H].view(Vds, H).cpu(), ref.cpu())}

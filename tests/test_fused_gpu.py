@@ -108,3 +108,9 @@ def test_transducer_with_reference_weights():
     assert m["grads_finite"], m
     assert m["loss_rel_oracle"] < 2e-3 and m["loss_rel_unfolded"] < 2e-3, m
     assert m["loss_rel_host_lens"] < 1e-6, m
+
+
+@pytest.mark.parametrize("rows,V,H", [(192, 300, 128), (128, 4232, 512), (64, 70, 256)])
+def test_dw2_gemm_writes_only_its_outputs(rows, V, H):
+    m = G.dw2_gemm_guard_bands(rows, V, H)
+    assert m["rc"] == 0 and m["guards_intact"] and m["dw2_rel_l2"] < 1e-5, m
