@@ -195,6 +195,45 @@ int rnnt_b200_joint_step_argmax(const float* pe_t, long long pe_stride, const fl
                                 const float* w2, const float* b2, int B, int H, int V,
                                 unsigned long long* work, long long* pred, void* stream);
 
+/* Feature front end of one batch (replaces the per-utterance numpy
+ * work of rnnt/dataset.py:72-109,143-155 and the Kaldi matrix decode of rnnt/kaldi_io.py:467-554):
+ * Kaldi matrix payloads as they lie in the ark file -> decompress -> CMVN -> splice context
+ * frames -> subsample -> zero-pad, one launch for B utterances, results identical to the numpy
+ * path bit for bit.
+ *   payload     device bytes; utterance b's matrix data starts at payload + desc[b].payload_off
+ *               (16-byte aligned): rows x F float32 / float64 row-major, or the CM byte matrix
+ *               (F x rows, column-major as Kaldi stores it).
+ *   desc        device array of B descriptors (below).
+ *   col_params  device floats, CM only: six per column {p0, (p25-p0)/64, p25, (p75-p25)/128,
+ *               p75, (p100-p75)/63} at col_params + desc[b].col_off + 6*f (kaldi_io.py:531-549).
+ *   cmvn_mean / cmvn_sd   (n_speakers, F) tables of mean and sqrt(variance) (dataset.py:72-75),
+ *               float64 when cmvn_f64 != 0 else float32; row desc[b].spk, spk < 0 = no CMVN.
+ *               out = float32((x - mean) / sd), evaluated in float64 when cmvn_f64 (numpy's
+ *               promotion for float64 statistics or float64 features), else in float32.
+ *   blk_primary / blk_override   HOST arrays of nblk <= 32 frame shifts: output block j of frame t
+ *               holds raw frame t*interval + shift. The override shift wins where its source
+ *               frame exists, else the primary, else zeros (dataset.py:77-98 writes the centre,
+ *               then the left, then the right context blocks over one zeroed array).
+ *               RNNT_B200_FEAT_NO_SHIFT marks "no writer".
+ *   out         (B, t_pad, nblk*F) float32; rows at and beyond desc[b].out_rows are zeroed.
+ * No allocation, no host read-back; everything on `stream`. */
+#define RNNT_B200_FEAT_F32 0
+#define RNNT_B200_FEAT_F64 1
+#define RNNT_B200_FEAT_CM8 2
+#define RNNT_B200_FEAT_NO_SHIFT (-2147483647 - 1)
+typedef struct {
+  long long payload_off; /* byte offset of the matrix data in `payload`, multiple of 16 */
+  long long col_off;     /* CM8: offset in floats of the 6*F column parameters; else unused */
+  int rows;              /* raw frames in the ark matrix */
+  int format;            /* RNNT_B200_FEAT_* */
+  int out_rows;          /* frames after subsampling = ceil(rows / interval) */
+  int spk;               /* CMVN table row, -1 = none */
+} rnnt_b200_utt_desc;
+int rnnt_b200_features_batch(const void* payload, const rnnt_b200_utt_desc* desc, const float* col_params,
+                             const void* cmvn_mean, const void* cmvn_sd, int cmvn_f64, int B, int F,
+                             int nblk, const int* blk_primary, const int* blk_override, int interval,
+                             int t_pad, float* out, void* stream);
+
 /* Plain bf16 tensor-core GEMM used to validate the tcgen05/TMA plumbing on its own:
  * C (M,N) float32 = A (M,K) bf16 . B (N,K)^T bf16; M%128==0, N%64==0, K%64==0. */
 int rnnt_b200_selftest_gemm(const void* a_bf16, const void* b_bf16, float* c,

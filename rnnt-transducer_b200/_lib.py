@@ -36,6 +36,7 @@ SIGNATURES = {
     "rnnt_b200_joint_bwd_ds": (_i, [_p] * 15 + [_i] * 9 + [_p, _p]),
     "rnnt_b200_joint_step_argmax": (_i, [_p, ctypes.c_longlong, _p, _p, _p, _i, _i, _i, _p, _p, _p]),
     "rnnt_b200_dw2_gemm": (_i, [_p, _p, ctypes.c_longlong, _i, _i, _p, _p, _p]),
+    "rnnt_b200_features_batch": (_i, [_p] * 5 + [_i] * 4 + [_p, _p, _i, _i, _p, _p]),
     "rnnt_b200_dh_reduce": (_i, [_p] * 4 + [_i] * 6 + [ctypes.c_float] + [_p, _p, _p]),
     "rnnt_b200_selftest_gemm": (_i, [_p, _p, _p, _i, _i, _i, _p]),
 }
