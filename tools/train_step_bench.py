@@ -23,18 +23,37 @@ if world > 1:
 torch.manual_seed(2019)
 model = R.Transducer(CFG).to(dev).train()
 ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local]) if world > 1 else model
-opt = torch.optim.SGD(model.parameters(), lr=1e-4, momentum=0.9)
+LOOP = os.environ.get("LOOP", "ours")  # "reference": the per-step host work of train.py:26-50 as written there
+if LOOP == "reference":
+    opt = torch.optim.SGD(model.parameters(), lr=1e-4, momentum=0.9, foreach=False)
+else:
+    opt = R.Optimizer(model.parameters(), dict(type="sgd", lr=1e-4, momentum=0.9)).optimizer  # fused update
 g = torch.Generator().manual_seed(rank)
 x = torch.randn(B, T, CFG["feature_dim"], generator=g).to(dev)
-xl = torch.full((B,), T, dtype=torch.long, device=dev)
+xl = torch.full((B,), T, dtype=torch.long)
 y = torch.randint(1, CFG["vocab_size"], (B, U), generator=g).to(dev)
-yl = torch.full((B,), U, dtype=torch.long, device=dev)
+yl = torch.full((B,), U, dtype=torch.long)
+xp, yp = torch.zeros(B, T + 100, CFG["feature_dim"]).pin_memory(), torch.zeros(B, U + 10, dtype=torch.long).pin_memory()
+xp[:, :T], yp[:, :U] = x.cpu(), y.cpu()
+total = torch.zeros((), device=dev)
 
 def step():
+    global total
+    if LOOP == "reference":  # train.py:26-33: everything to the device, two read-backs, trim
+        xi, xli, yi, yli = xp.cuda(), xl.cuda(), yp.cuda(), yl.cuda()
+        xi, yi = xi[:, :xli.max().item(), :], yi[:, :yli.max().item()]
+    else:                    # lengths stay on the host; padded batch from pinned memory, trimmed there
+        xli, yli = xl, yl
+        xi, yi = R.trim_batch(xp.to(dev, non_blocking=True), xl, yp.to(dev, non_blocking=True), yl)
     opt.zero_grad(set_to_none=True)
-    loss = ddp(x, xl, y, yl)
+    loss = ddp(xi, xli, yi, yli)
     loss.backward()
-    torch.nn.utils.clip_grad_norm_(model.parameters(), 200.0)   # train.py:49-50, max_grad_norm 200
+    if LOOP == "reference":
+        total_host = loss.item()                                 # train.py:47
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 200.0, foreach=False)
+    else:
+        total += loss.detach()
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 200.0, foreach=True)   # train.py:49-50, max_grad_norm 200
     opt.step()
     return loss
 
@@ -55,7 +74,7 @@ if world > 1:
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
 if rank == 0:
     cells = world * B * T * (U + 1)
-    print(json.dumps({"workload": f"aishell_train_step_B{B}_T{T}_U{U}_per_gpu", "n_gpus": world,
+    print(json.dumps({"workload": f"aishell_train_step_B{B}_T{T}_U{U}_per_gpu", "n_gpus": world, "loop": LOOP,
                       "ms_per_step": round(float(ms), 3), "cells_per_s": round(cells / float(ms) * 1e3),
                       "utterances_per_s": round(world * B / float(ms) * 1e3, 1), "loss": float(loss)}))
 if world > 1:
