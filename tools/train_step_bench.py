@@ -52,7 +52,7 @@ def step():
         total_host = loss.item()                                 # train.py:47
         torch.nn.utils.clip_grad_norm_(model.parameters(), 200.0, foreach=False)
     else:
-        total += loss.detach()
+        total += loss.detach().sum()
         torch.nn.utils.clip_grad_norm_(model.parameters(), 200.0, foreach=True)   # train.py:49-50, max_grad_norm 200
     opt.step()
     return loss
