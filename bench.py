@@ -301,7 +301,12 @@ def main():
     total_alg = 6.0 * H * V * cells
     path = {"algorithmic_tflops": total_alg / (ms_step * 1e-3) / 1e12,
             "frac_of_sustained_peak": total_alg / (ms_step * 1e-3) / 1e12 / peak,
-            "kernel_ms_one_step": {k: round(v, 4) for k, v in kern_ms.items()}}
+            "kernel_ms_one_step": {k: round(v, 4) for k, v in kern_ms.items()},
+            # every vocabulary-sized GEMM of the step against the same peak (2*H*V flop per cell each;
+            # joint_bwd_ds is the recompute: hardware work, not counted in the algorithmic 6*H*V)
+            "gemm_frac_of_sustained_peak": {k: round(flops_fwd / (kern_ms[k] * 1e-3) / 1e12 / peak, 4)
+                                            for k in ("joint_fwd", "joint_bwd_ds", "lib_gemm_dh", "dw2_gemm")
+                                            if kern_ms.get(k, 0.0) > 0}}
 
     line = {
         "metric": METRIC, "value": cells * world / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
