@@ -182,3 +182,17 @@ def test_gpu_features_match_oracle_at_aishell_sizes(tmp_path, fmt, F, left, righ
         want, n = FO.utterance_features(rx[k], stats[spk[b]], left, right, rate, out.shape[1])
         assert n == int(lens[b])
         assert _same_bits(out[b], want), (fmt, k, rows[b])
+
+
+def test_loader_sharding_covers_every_utterance_once():
+    """rank r of world_size N takes utterances r::N of every global batch (train.py:136 sizes the
+    global batch as batch_size x num_gpu); checked on the index level, no device needed."""
+    ds = R.KaldiFeatureSet(data_config("fm", "f64", VARIANTS["fm"][2]), "train", root=FIX)
+    ds.batch = lambda idx, device=None, pad_to_max=False: list(idx)
+    one = [b for b in ds.loader(batch_size=4)]
+    assert one == [[0, 1, 2, 3], [4, 5]]
+    parts = [[b for b in ds.loader(batch_size=2, rank=r, world_size=2)] for r in range(2)]
+    assert parts[0] == [[0, 2], [4]] and parts[1] == [[1, 3], [5]]
+    g = torch.Generator().manual_seed(3)
+    shuffled = [i for b in ds.loader(batch_size=4, shuffle=True, generator=g) for i in b]
+    assert sorted(shuffled) == list(range(6))
