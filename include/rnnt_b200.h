@@ -238,6 +238,11 @@ int rnnt_b200_features_batch(const void* payload, const rnnt_b200_utt_desc* desc
  * C (M,N) float32 = A (M,K) bf16 . B (N,K)^T bf16; M%128==0, N%64==0, K%64==0. */
 int rnnt_b200_selftest_gemm(const void* a_bf16, const void* b_bf16, float* c,
                             int M, int N, int K, void* stream);
+/* The same product with the A operand taken from tensor memory (the TS form of tcgen05.mma):
+ * ts = 1 stages A shared -> TMEM with tcgen05.cp, ts = 2 writes it from registers (tcgen05.st),
+ * ts = 0 is rnnt_b200_selftest_gemm. K <= 512 for ts != 0. */
+int rnnt_b200_selftest_gemm_ts(const void* a_bf16, const void* b_bf16, float* c,
+                               int M, int N, int K, int ts, void* stream);
 
 #ifdef __cplusplus
 }

@@ -574,12 +574,13 @@ class GreedyDecoder:
         return out
 
 
-def selftest_gemm(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
-    """C = A . B^T through the bare tcgen05/TMA plumbing (bf16 in, fp32 out)."""
+def selftest_gemm(a: torch.Tensor, b: torch.Tensor, ts: int = 0) -> torch.Tensor:
+    """C = A . B^T through the bare tcgen05/TMA plumbing (bf16 in, fp32 out); ts = 1 / 2 takes the A
+    operand from tensor memory (staged by tcgen05.cp / written by tcgen05.st)."""
     M, K = a.shape
     N = b.shape[0]
     c = torch.empty(M, N, dtype=torch.float32, device=a.device)
     with torch.cuda.device(a.device):
-        _lib.check(_lib.lib().rnnt_b200_selftest_gemm(_ptr(a), _ptr(b), _ptr(c), M, N, K, _stream()),
-                   "rnnt_b200_selftest_gemm")
+        _lib.check(_lib.lib().rnnt_b200_selftest_gemm_ts(_ptr(a), _ptr(b), _ptr(c), M, N, K, int(ts), _stream()),
+                   "rnnt_b200_selftest_gemm_ts")
     return c

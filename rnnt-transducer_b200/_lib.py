@@ -39,6 +39,7 @@ SIGNATURES = {
     "rnnt_b200_features_batch": (_i, [_p] * 5 + [_i] * 4 + [_p, _p, _i, _i, _p, _p]),
     "rnnt_b200_dh_reduce": (_i, [_p] * 4 + [_i] * 6 + [ctypes.c_float] + [_p, _p, _p]),
     "rnnt_b200_selftest_gemm": (_i, [_p, _p, _p, _i, _i, _i, _p]),
+    "rnnt_b200_selftest_gemm_ts": (_i, [_p, _p, _p, _i, _i, _i, _i, _p]),
 }
 
 

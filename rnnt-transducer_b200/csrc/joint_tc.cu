@@ -53,7 +53,7 @@ constexpr int kSmemLimit = 232448;       // 227 KB opt-in maximum per CTA
 struct SharedCtl {
   uint64_t a_full[8], a_empty[8];        // per group of KSUB K blocks of the h tile
   uint64_t b_full[kMaxSlots], b_empty[kMaxSlots];
-  uint64_t acc_full[2], acc_empty[2];
+  uint64_t acc_full[4], acc_empty[4];
   uint32_t tmem_base;
   uint32_t pad[3];
 };
@@ -83,6 +83,7 @@ struct JointParams {
   int B, T, U1, V, Vpad, Vds, H, blank;  // Vpad: rows of the packed W2 (NV*BN); Vds: dS pitch
   int tile_lo, tile_hi;  // tile range of this launch
   int slots;             // W2 ring depth
+  int kts, nacc;         // V2 kernel: K blocks of the h tile multiplied out of TMEM; accumulator buffers
   long long* trace;  // RNNT_B200_TRACE: clock64 stamps of cluster 0 / rank 0 (debug only)
   int trace_cta;  // RNNT_B200_TRACE_CTA: the CTA whose stamps are recorded (default 0)
   int debug;  // RNNT_B200_DEBUG bitmask (timing experiments only): 1 skip epilogue math, 4 skip MMA issue,
@@ -99,8 +100,8 @@ constexpr int kRedBytes = RNNT_TILE_M * 16;
 // one wait/fence/elect round per 8 MMAs -- the one-slot loop spent ~620 clk per K block against
 // 512 clk of MMA); the slots themselves are filled and released one K block at a time.
 __host__ __device__ inline int ksub_for(int H) { return (H % 128 == 0) ? 2 : 1; }
-__host__ __device__ inline int smem_bytes_for(int H, int BN, int slots, int mode) {
-  return (H / kKBlock) * kABlockBytes + slots * (BN / 2) * 128 + (mode == 1 ? kDsStageBytes : kRedBytes) +
+__host__ __device__ inline int smem_bytes_for(int H, int BN, int slots, int mode, int kslot = 1) {
+  return (H / kKBlock) * kABlockBytes + slots * kslot * (BN / 2) * 128 + (mode == 1 ? kDsStageBytes : kRedBytes) +
          (int)sizeof(SharedCtl) + 2 * 2 * (BN / 2) * 4;
 }
 
@@ -154,22 +155,29 @@ __device__ __forceinline__ RowCoord locate_row(const JointParams& p, int tile, i
 
 // ---------------------------------------------------------------------------------------
 // MODE 0 = forward (online LSE epilogue), MODE 1 = backward dS.
+// V2 (experiment, RNNT_B200_V2=<kts>; backward only, BN = 128): the first `kts` K blocks of the h
+// tile are copied shared -> TMEM once per lattice tile (tcgen05.cp) and multiplied from there (TS
+// form: no shared-memory read of A for them); the accumulator is `nacc` buffers of 128 columns next
+// to the 32*kts columns of A; a W2 ring slot holds two K blocks (two TMA boxes, one barrier).
 // ---------------------------------------------------------------------------------------
-template <int BN, int MODE>
+template <int BN, int MODE, int V2 = 0>
 __global__ void __launch_bounds__(kThreads, 1)
 joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__ CUtensorMap map_h,
              const __grid_constant__ CUtensorMap map_ds, const JointParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];  // no static smem in this kernel: base is 1024-aligned
   if ((smem_u32(smem) & 1023u) != 0) __trap();       // the 128B-swizzle atoms need it
   const int KB = p.H / kKBlock;      // K blocks of 64
-  const int KSUB = ksub_for(p.H);    // K blocks (ring slots) per MMA-issue iteration
-  const int KS = KB / KSUB;          // MMA-issue iterations per vocabulary tile
-  const int NV = p.Vpad / BN;        // vocabulary tiles
+  constexpr int KSLOT = V2 ? 2 : 1;  // K blocks per W2 ring slot
+  const int KSUB = V2 ? ((p.H % 256 == 0) ? 2 : 1) : ksub_for(p.H);  // ring slots per MMA-issue iteration
+  const int KPI = KSUB * KSLOT;      // K blocks per MMA-issue iteration
+  const int KS = KB / KPI;           // MMA-issue iterations per vocabulary tile
+  const int NV = V2 ? (p.Vds + BN - 1) / BN : p.Vpad / BN;  // vocabulary tiles
   // The last vocabulary tile is issued with UMMA N = n_last (multiple of 16) instead of BN:
   // V=4232 -> 16 tiles of 256 + one of 192 (4288 columns instead of 4352).
   const int n_last = p.Vds - (NV - 1) * BN;
   constexpr int HALF = BN / 2;
-  constexpr int kSlotBytes = HALF * 128;  // this CTA's half of one W2 K block: BN/2 rows x 64 k
+  constexpr int kSubBytes = HALF * 128;   // this CTA's half of one W2 K block: BN/2 rows x 64 k
+  constexpr int kSlotBytes = KSLOT * kSubBytes;
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + KB * kABlockBytes;
   uint8_t* smem_ds = smem_b + p.slots * kSlotBytes;  // MODE 1: 8 warps x 2 x 2 KB dS staging tiles
@@ -199,7 +207,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       mbar_init(&ctl->b_full[i], 2);
       mbar_init(&ctl->b_empty[i], 1);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < 4; ++i) {
       mbar_init(&ctl->acc_full[i], 1);
       mbar_init(&ctl->acc_empty[i], 2 * kEpiWarps);
     }
@@ -225,6 +233,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
     const int row = q * 32 + lane;
     constexpr int NCH = HALF / 16;  // 16-column chunks per half tile
     uint32_t acc_it = 0;
+    uint32_t acc_buf = 0, acc_par = 0;  // V2: buffer acc_it % nacc and its phase
     uint32_t gp_hold[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};  // MODE 1: packed even chunk waiting for its odd partner
     (void)gp_hold;
     // Bias ring of this column half: buffer (acc_it & 1) holds b2*log2(e) of the current
@@ -281,9 +290,10 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       }
       for (int vi = 0; vi < NV; ++vi, ++acc_it) {
         const int vt = (vi + cid) % NV;
-        const uint32_t buf = acc_it & 1;
+        const uint32_t buf = V2 ? acc_buf : (acc_it & 1);
         const long long tr0 = p.trace ? clock64() : 0;
-        mbar_wait(&ctl->acc_full[buf], (acc_it >> 1) & 1);
+        mbar_wait(&ctl->acc_full[buf], V2 ? acc_par : ((acc_it >> 1) & 1));
+        if (V2 && ++acc_buf == (uint32_t)p.nacc) { acc_buf = 0; acc_par ^= 1; }
         const long long tr1 = p.trace ? clock64() : 0;
         tc_fence_after();
         if (bias_loader) {  // next tile's slice -> the buffer nobody reads during this tile
@@ -398,7 +408,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
           }
         };
 
-        if (NCH == 8 && nch == NCH) {
+        if ((NCH == 8 || (V2 && NCH == 4)) && nch == NCH) {
           // Software pipeline over the eight 16-column chunks, three register buffers deep:
           // while chunk c goes through the MUFU-bound exponential stage, chunk c+1 gets its bias
           // FMA (+ running max) in the same basic block and the TMEM load of chunk c+2 is in
@@ -410,15 +420,15 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
           tmem_ld_wait();
           float cmax = bias_stage(z[0], 0);
 #pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            if (c + 2 < 8) tmem_ld_32x16(taddr0 + (c + 2) * 16, z[(c + 2) % 3]);
+          for (int c = 0; c < NCH; ++c) {
+            if (c + 2 < NCH) tmem_ld_32x16(taddr0 + (c + 2) * 16, z[(c + 2) % 3]);
             float cmax_next = -INFINITY;
-            if (c + 1 < 8) cmax_next = bias_stage(z[(c + 1) % 3], c + 1);
-            exp_stage(z[c % 3], c, cmax, 8);
+            if (c + 1 < NCH) cmax_next = bias_stage(z[(c + 1) % 3], c + 1);
+            exp_stage(z[c % 3], c, cmax, NCH);
             cmax = cmax_next;
-            if (c + 2 < 8) {
+            if (c + 2 < NCH) {
               tmem_ld_wait();  // chunk c+2 has landed (it had this whole iteration to do so)
-              if (c + 3 == 8) release_acc();
+              if (c + 3 == NCH) release_acc();
             }
           }
         } else {
@@ -477,7 +487,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       const int parity = (warp == 8) ? 0 : 1;
       const uint32_t nslot = (uint32_t)p.slots;
       uint32_t slot = (uint32_t)parity % nslot, phase = ((uint32_t)parity / nslot) & 1;
-      int kb = parity, pt = cid, vt = cid % NV, vleft = NV;  // vleft: vocabulary tiles left in this lattice tile
+      int kb = parity * KSLOT, pt = cid, vt = cid % NV, vleft = NV;  // vleft: vocabulary tiles left in this lattice tile
       while (kb >= KB) { kb -= KB; vt = (vt + 1 == NV) ? 0 : vt + 1; if (--vleft == 0) { vleft = NV; pt += ncl; } }
       int tr_n = 0;
       while (pt < n_pairs) {
@@ -488,7 +498,9 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         const uint32_t full = mapa_u32(smem_u32(&ctl->b_full[slot]), 0);
         if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[slot], 2 * kSlotBytes);
         else mbar_arrive_cluster(full);
-        tma_load_2d_pair(smem_b + slot * kSlotBytes, &map_w2, full, kb * kKBlock, row0);
+#pragma unroll
+        for (int j = 0; j < KSLOT; ++j)
+          tma_load_2d_pair(smem_b + slot * kSlotBytes + j * kSubBytes, &map_w2, full, (kb + j) * kKBlock, row0);
         if (p.trace && blockIdx.x == p.trace_cta && parity == 0 && tr_n < 4096) {
           long long* t = p.trace + 3 * 4096;
           t[3 * tr_n + 0] = tr0; t[3 * tr_n + 1] = tr1; t[3 * tr_n + 2] = clock64();
@@ -496,7 +508,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         }
         slot += 2;
         while (slot >= nslot) { slot -= nslot; phase ^= 1; }
-        kb += 2;
+        kb += 2 * KSLOT;
         while (kb >= KB) { kb -= KB; vt = (vt + 1 == NV) ? 0 : vt + 1; if (--vleft == 0) { vleft = NV; pt += ncl; } }
       }
     }
@@ -509,10 +521,10 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         for (int ks = 0; ks < KS; ++ks) {  // one barrier pair per group of KSUB K blocks
           mbar_wait(&ctl->a_empty[ks], (it & 1) ^ 1);
           const uint32_t full = mapa_u32(smem_u32(&ctl->a_full[ks]), 0);
-          if (rank == 0) mbar_arrive_expect_tx(&ctl->a_full[ks], 2 * KSUB * kABlockBytes);
+          if (rank == 0) mbar_arrive_expect_tx(&ctl->a_full[ks], 2 * KPI * kABlockBytes);
           else mbar_arrive_cluster(full);
-          for (int sub = 0; sub < KSUB; ++sub) {
-            const int kb = ks * KSUB + sub;
+          for (int sub = 0; sub < KPI; ++sub) {
+            const int kb = ks * KPI + sub;
             tma_load_2d_pair(smem_a + kb * kABlockBytes, &map_h, full, kb * kKBlock, tile * RNNT_TILE_M);
           }
         }
@@ -528,6 +540,9 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       constexpr uint32_t idesc_full = umma_idesc_bf16(2 * RNNT_TILE_M, BN);
       const uint32_t idesc_last = umma_idesc_bf16(2 * RNNT_TILE_M, n_last);
       uint32_t slot = 0, phase = 0, acc_it = 0;
+      uint32_t abuf = 0, apar = 0;  // V2: accumulator buffer acc_it % nacc and its phase
+      const uint32_t tmem_a = tmem_base + (uint32_t)p.nacc * BN;  // V2: the h tile's K blocks in TMEM
+      (void)tmem_a;
       int it = 0, tr_n = 0;
       const uint32_t a0 = smem_u32(smem_a), b0 = smem_u32(smem_b);
       const bool tracing = p.trace != nullptr && blockIdx.x == p.trace_cta;
@@ -535,8 +550,9 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         for (int vi = 0; vi < NV; ++vi, ++acc_it) {
           const int vt = (vi + cid) % NV;  // same rotated order as the producer and the epilogue
           const uint32_t idesc = (vt == NV - 1) ? idesc_last : idesc_full;
-          const uint32_t buf = acc_it & 1;
-          mbar_wait(&ctl->acc_empty[buf], ((acc_it >> 1) & 1) ^ 1);
+          const uint32_t buf = V2 ? abuf : (acc_it & 1);
+          mbar_wait(&ctl->acc_empty[buf], (V2 ? apar : ((acc_it >> 1) & 1)) ^ 1);
+          if (V2 && ++abuf == (uint32_t)p.nacc) { abuf = 0; apar ^= 1; }
           tc_fence_after();
           const uint32_t tmem_d = tmem_base + buf * BN;
           for (int ks = 0; ks < KS; ++ks) {
@@ -558,11 +574,23 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
               for (int sub = 0; sub < KSUB; ++sub) {
                 const uint32_t sl = sub ? s1 : s0;
                 if (!(p.debug & 4)) {
-                  const uint64_t adesc = umma_desc_kmajor<128>(a0 + (ks * KSUB + sub) * kABlockBytes);
-                  const uint64_t bdesc = umma_desc_kmajor<128>(b0 + sl * kSlotBytes);
 #pragma unroll
-                  for (int k = 0; k < kKBlock / 16; ++k)
-                    umma_bf16_ss_pair(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | sub | k) != 0);
+                  for (int j = 0; j < KSLOT; ++j) {
+                    const int kb = (ks * KSUB + sub) * KSLOT + j;
+                    const uint64_t adesc = umma_desc_kmajor<128>(a0 + kb * kABlockBytes);
+                    const uint64_t bdesc = umma_desc_kmajor<128>(b0 + sl * kSlotBytes + j * kSubBytes);
+                    const bool a_tmem = V2 && kb < p.kts;
+                    const uint32_t ta = tmem_a + (uint32_t)kb * 32;
+                    if (a_tmem && vi == 0) {  // this lattice tile's K block -> TMEM (in order with the MMAs)
+#pragma unroll
+                      for (int k = 0; k < kKBlock / 16; ++k) tmem_cp_128x256b_pair(ta + 8 * k, adesc + 2 * k);
+                    }
+#pragma unroll
+                    for (int k = 0; k < kKBlock / 16; ++k) {
+                      if (a_tmem) umma_bf16_ts_pair(tmem_d, ta + 8 * k, bdesc + 2 * k, idesc, (ks | sub | j | k) != 0);
+                      else umma_bf16_ss_pair(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | sub | j | k) != 0);
+                    }
+                  }
                 }
                 umma_commit_pair_mc(&ctl->b_empty[sl], 3);
               }
@@ -665,7 +693,10 @@ hidden_kernel(const JointParams p, int max_tiles) {
 template <int BN>
 __global__ void __launch_bounds__(192, 1)
 selftest_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                     float* __restrict__ C, int N, int K) {
+                     float* __restrict__ C, int N, int K, int ts, const __nv_bfloat16* __restrict__ A) {
+  // ts: 0 = both operands from shared memory; 1 = A copied shared -> TMEM with tcgen05.cp and multiplied
+  // from there (the form the TS variant of joint_kernel uses); 2 = A written to TMEM from registers
+  // (tcgen05.st) -- tells a TMEM operand-layout error from a tcgen05.cp descriptor error. K <= 512 for ts.
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   constexpr int STAGES = 4;
@@ -683,11 +714,27 @@ selftest_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     mbar_init(&ctl->acc, 1);
     fence_barrier_init();
   }
-  if (warp == 2) { tmem_alloc(&ctl->tmem, 256); tmem_relinquish(); }
+  if (warp == 2) { tmem_alloc(&ctl->tmem, 512); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = ctl->tmem;
+  const uint32_t tmem_a = tmem + 256;  // A operand: K/2 columns behind the accumulator
+  if (ts == 2) {
+    if (warp >= 2) {
+      const int q = warp & 3;
+      const uint4* src = reinterpret_cast<const uint4*>(A + (size_t)(m0 + q * 32 + lane) * K);
+      for (int kk = 0; kk < K / 16; ++kk) {
+        const uint4 v0 = src[2 * kk], v1 = src[2 * kk + 1];
+        const uint32_t r[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+        tmem_st_32x8(tmem_a + ((uint32_t)(q * 32) << 16) + kk * 8, r);
+      }
+      tmem_st_wait();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+  }
   if (warp == 0) {
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
@@ -710,8 +757,12 @@ selftest_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         for (int h2 = 0; h2 < 2; ++h2) {
           const uint64_t adesc = umma_desc_kmajor<128>(smem_u32(sa + stage * kAStage) + h2 * 64);
           const uint64_t bdesc = umma_desc_kmajor<64>(smem_u32(sb + (stage * 2 + h2) * kBStage));
-          for (int k = 0; k < 2; ++k)
-            umma_bf16_ss(tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | h2 | k) != 0);
+          for (int k = 0; k < 2; ++k) {
+            const uint32_t ta = tmem_a + (uint32_t)((kb * 4 + h2 * 2 + k) * 8);
+            if (ts == 1) tmem_cp_128x256b(ta, adesc + 2 * k);
+            if (ts) umma_bf16_ts(tmem, ta, bdesc + 2 * k, idesc, (kb | h2 | k) != 0);
+            else umma_bf16_ss(tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | h2 | k) != 0);
+          }
         }
         umma_commit(&ctl->empty[stage]);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -734,22 +785,23 @@ selftest_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem, 256);
+  if (warp == 2) tmem_dealloc(tmem, 512);
 }
 
 // ------------------------------------------------------------------ host side
-int pick_slots(int H, int BN, int mode) {
+int pick_slots(int H, int BN, int mode, int kslot = 1) {
   int s = kMaxSlots;
-  while (s > 2 && smem_bytes_for(H, BN, s, mode) > kSmemLimit) --s;
+  while (s > 2 && smem_bytes_for(H, BN, s, mode, kslot) > kSmemLimit) --s;
   return s;
 }
 
-template <int BN, int MODE>
+template <int BN, int MODE, int V2 = 0>
 int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap& md, JointParams& p,
                  cudaStream_t st) {
   // the bias table goes to shared memory when it leaves room for >= 3 ring stages, else it is
   // read through L1 (very large vocabularies)
-  p.slots = pick_slots(p.H, BN, MODE);
+  constexpr int kslot = V2 ? 2 : 1;
+  p.slots = pick_slots(p.H, BN, MODE, kslot);
   {
     const char* dbg = getenv("RNNT_B200_DEBUG");
     p.debug = dbg ? atoi(dbg) : 0;
@@ -758,9 +810,9 @@ int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap
     const char* stg = getenv("RNNT_B200_SLOTS");
     if (stg && atoi(stg) >= 2 && atoi(stg) < p.slots) p.slots = atoi(stg);
   }
-  const int smem = smem_bytes_for(p.H, BN, p.slots, MODE);
+  const int smem = smem_bytes_for(p.H, BN, p.slots, MODE, kslot);
   if (smem > kSmemLimit) return RNNT_B200_E_SHAPE;
-  cudaError_t e = cudaFuncSetAttribute(joint_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  cudaError_t e = cudaFuncSetAttribute(joint_kernel<BN, MODE, V2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return (int)e;
   int grid = sm_count() & ~1;
   const int ntile = p.tile_hi - p.tile_lo;
@@ -795,7 +847,7 @@ int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap
     if (cudaMalloc(&p.trace, trace_bytes) != cudaSuccess) p.trace = nullptr;
     else cudaMemsetAsync(p.trace, 0, trace_bytes, st);
   }
-  e = cudaLaunchKernelEx(&cfg, joint_kernel<BN, MODE>, mw, mh, md, p);
+  e = cudaLaunchKernelEx(&cfg, joint_kernel<BN, MODE, V2>, mw, mh, md, p);
   if (e != cudaSuccess) return (int)e;
   if (p.trace) {
     long long* host = (long long*)malloc(trace_bytes);
@@ -812,7 +864,18 @@ int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap
 
 template <int MODE>
 int dispatch_joint(JointParams& p, const void* w2q, const void* h_stash, int max_tiles, cudaStream_t st) {
-  const int BN = rnnt_b200_vocab_tile(p.V);
+  int BN = rnnt_b200_vocab_tile(p.V);
+  p.kts = 0; p.nacc = 2;
+  bool v2 = false;
+  if (MODE == 1 && BN == 256 && p.H % 128 == 0) {  // experiment: A operand (partly) from TMEM, 128-column tiles
+    const char* e = getenv("RNNT_B200_V2");
+    if (e && atoi(e) >= 0) {
+      v2 = true;
+      BN = 128;
+      p.kts = atoi(e) < p.H / kKBlock ? atoi(e) : p.H / kKBlock;
+      p.nacc = (512 - 32 * p.kts) / 128 < 4 ? (512 - 32 * p.kts) / 128 : 4;
+    }
+  }
   CUtensorMap mw, mh;
   int rc = make_map_bf16(&mw, w2q, p.Vpad, p.H, p.H, kKBlock, BN / 2, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
@@ -824,6 +887,9 @@ int dispatch_joint(JointParams& p, const void* w2q, const void* h_stash, int max
     rc = make_map_bf16(&md, p.ds, (uint64_t)(p.tile_hi - p.tile_lo) * RNNT_TILE_M, p.Vds, p.Vds, 32, 32,
                        CU_TENSOR_MAP_SWIZZLE_64B);
     if (rc) return rc;
+  }
+  if (v2) {
+    if constexpr (MODE == 1) return launch_joint<128, 1, 1>(mw, mh, md, p, st);
   }
   switch (BN) {
     case 64: return launch_joint<64, MODE>(mw, mh, md, p, st);
@@ -923,8 +989,15 @@ extern "C" int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, 
 
 extern "C" int rnnt_b200_selftest_gemm(const void* a_bf16, const void* b_bf16, float* c, int M, int N,
                                        int K, void* stream) {
+  return rnnt_b200_selftest_gemm_ts(a_bf16, b_bf16, c, M, N, K, 0, stream);
+}
+
+extern "C" int rnnt_b200_selftest_gemm_ts(const void* a_bf16, const void* b_bf16, float* c, int M, int N,
+                                          int K, int ts, void* stream) {
   if (!a_bf16 || !b_bf16 || !c) return RNNT_B200_E_NULL;
   if (M <= 0 || N <= 0 || K <= 0 || (M % 128) || (N % 64) || (K % 64)) return RNNT_B200_E_SHAPE;
+  if (ts < 0 || ts > 2 || (ts && K > 512)) return RNNT_B200_E_SHAPE;
+  if (((uintptr_t)a_bf16 & 15)) return RNNT_B200_E_ALIGN;
   const int BN = (N % 256 == 0) ? 256 : 64;
   CUtensorMap ma, mb;
   int rc = make_map_bf16(&ma, a_bf16, M, K, K, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
@@ -937,11 +1010,13 @@ extern "C" int rnnt_b200_selftest_gemm(const void* a_bf16, const void* b_bf16, f
   if (BN == 256) {
     e = cudaFuncSetAttribute(selftest_gemm_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return (int)e;
-    selftest_gemm_kernel<256><<<dim3(M / 128, N / 256), 192, smem, st>>>(ma, mb, c, N, K);
+    selftest_gemm_kernel<256><<<dim3(M / 128, N / 256), 192, smem, st>>>(ma, mb, c, N, K, ts,
+                                                                          (const __nv_bfloat16*)a_bf16);
   } else {
     e = cudaFuncSetAttribute(selftest_gemm_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return (int)e;
-    selftest_gemm_kernel<64><<<dim3(M / 128, N / 64), 192, smem, st>>>(ma, mb, c, N, K);
+    selftest_gemm_kernel<64><<<dim3(M / 128, N / 64), 192, smem, st>>>(ma, mb, c, N, K, ts,
+                                                                        (const __nv_bfloat16*)a_bf16);
   }
   RNNT_CUDA_RETURN_IF_ERROR();
   return RNNT_B200_OK;

@@ -12,11 +12,11 @@ from tests.helpers import load_golden, max_abs, rel_l2, synth_labels, synth_leng
 DEV = "cuda:0"
 
 
-def selftest_gemm(M, N, K, seed=0):
+def selftest_gemm(M, N, K, seed=0, ts=0):
     g = torch.Generator().manual_seed(seed)
     a = torch.randn(M, K, generator=g).to(torch.bfloat16)
     b = torch.randn(N, K, generator=g).to(torch.bfloat16)
-    c = R.selftest_gemm(a.to(DEV), b.to(DEV)).cpu()
+    c = R.selftest_gemm(a.to(DEV), b.to(DEV), ts).cpu()
     ref = a.double() @ b.double().t()
     return {"max_abs": max_abs(c, ref), "rel_l2": rel_l2(c, ref), "ref_absmax": float(ref.abs().max())}
 

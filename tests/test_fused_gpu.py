@@ -29,6 +29,23 @@ def test_tcgen05_plumbing_gemm(M, N, K):
     assert m["rel_l2"] < 1e-5, m
 
 
+@pytest.mark.parametrize("ts", [1, 2])
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 512, 512), (384, 192, 512)])
+def test_tcgen05_a_operand_from_tmem(M, N, K, ts):
+    m = G.selftest_gemm(M, N, K, ts=ts)
+    assert m["rel_l2"] < 1e-5, m
+
+
+@pytest.mark.parametrize("kts", ["0", "4", "8"])
+def test_backward_variant_with_a_operand_from_tmem(kts, monkeypatch):
+    # RNNT_B200_V2 (read per launch by the C side): 128-column vocabulary tiles, `kts` K blocks of the
+    # hidden tile multiplied out of tensor memory, 4 / 3 / 2 accumulator buffers -- same parity bar
+    monkeypatch.setenv("RNNT_B200_V2", kts)
+    _assert_fused(G.fused_synth(2, 20, 8, 320, 320, 512, 4232, mode="ragged", host_lens=True))
+    _assert_fused(G.fused_synth(3, 23, 9, 64, 64, 128, 300, mode="edge"))
+    _assert_fused(G.fused_synth(2, 14, 6, 96, 96, 256, 600, mode="ragged"))
+
+
 @pytest.mark.parametrize("name", ["timit_like", "aishell_like", "edge_u0_t1"])
 def test_golden(name):
     _assert_fused(G.fused_golden(name))
