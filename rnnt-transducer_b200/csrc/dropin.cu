@@ -15,13 +15,31 @@ namespace {
 
 constexpr int WARPS_PER_BLOCK = 8;
 
-__device__ __forceinline__ void online_merge(float& m, float& s, float m2, float s2) {
+// Online log-sum-exp state of a row: m = running maximum (natural domain, exact), sp = sum of
+// exp(x_i - m) over the elements seen EXCEPT one occurrence of the maximum, so that
+// lse = m + log1p(sp) and lp_k = (x_k - m) - log1p(sp) keep their relative accuracy when one logit
+// dominates (trained-like inputs: lp of the dominant symbol ~ -sp, which m + log(1 + sp) - x_k would
+// return with the absolute error of fp32 at |x| ~ 10: 1e-6 against per-utterance losses of 1e-3).
+__device__ __forceinline__ void online_merge(float& m, float& sp, float m2, float sp2) {
   const float mn = fmaxf(m, m2);
-  // exp2f(-inf - finite) = 0; both -inf only before any element was seen.
-  const float a = (m == -INFINITY) ? 0.f : s * exp2f(m - mn);
-  const float b = (m2 == -INFINITY) ? 0.f : s2 * exp2f(m2 - mn);
+  float r;
+  if (mn == -INFINITY) r = 0.f;                                                  // both empty
+  else if (m == m2) r = sp + sp2 + 1.f;                                          // one of the two maxima turns ordinary
+  else if (m > m2) r = sp + (sp2 + 1.f) * exp2f((m2 - m) * RNNT_LOG2E);          // exp2f(-inf) = 0: empty side adds nothing
+  else r = sp2 + (sp + 1.f) * exp2f((m - m2) * RNNT_LOG2E);
   m = mn;
-  s = a + b;
+  sp = r;
+}
+// one more element x into (m, sp)
+__device__ __forceinline__ void online_push(float& m, float& sp, float x) {
+  if (x <= m) {
+    sp += exp2f((x - m) * RNNT_LOG2E);        // ordinary term (x = -inf adds 0)
+  } else if (x > m) {                         // new maximum: the old one turns ordinary (m = -inf: (0 + 1) * 0)
+    sp = (sp + 1.f) * exp2f((m - x) * RNNT_LOG2E);
+    m = x;
+  } else {                                    // NaN logit: poison the row like the plain formulation does
+    sp = x;
+  }
 }
 
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
@@ -43,42 +61,48 @@ logits_to_planes_kernel(const float* __restrict__ logits, const int32_t* __restr
     const int Ub = clamp_int(label_lens[b], 0, U);
     if (t >= Tb || u > Ub) continue;  // warp-uniform
     const float* x = logits + (size_t)cell * V;
-    // work in the log2 domain: z = x*log2(e)
-    float m = -INFINITY, s = 0.f;
+    float m = -INFINITY, sp = 0.f;
     if ((V & 3) == 0) {
       const float4* x4 = reinterpret_cast<const float4*>(x);
       const int n4 = V >> 2;
       for (int i = lane; i < n4; i += 32) {
         const float4 v = __ldcs(x4 + i);
-        const float z0 = v.x * RNNT_LOG2E, z1 = v.y * RNNT_LOG2E, z2 = v.z * RNNT_LOG2E, z3 = v.w * RNNT_LOG2E;
-        const float cm = fmaxf(fmaxf(z0, z1), fmaxf(z2, z3));
-        const float mn = fmaxf(m, cm);
-        s = s * exp2f(m - mn) + exp2f(z0 - mn) + exp2f(z1 - mn) + exp2f(z2 - mn) + exp2f(z3 - mn);
+        const float mn = fmaxf(fmaxf(m, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
+        if (mn == -INFINITY) continue;  // only masked (-inf) logits so far
+        // five candidates (old maximum, four new logits): the first one equal to mn is the excluded
+        // occurrence, the others are ordinary terms exp(c - mn): five exponentials per four logits,
+        // branch free (a fast path for "maximum unchanged" diverges within the warp and was slower)
+        bool taken = (m == mn);
+        float acc = taken ? sp : (sp + 1.f) * exp2f((m - mn) * RNNT_LOG2E);  // m = -inf: (0 + 1) * 0
+        const float c[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const bool is = !taken && (c[j] == mn);
+          taken = taken || is;
+          const float e = exp2f((c[j] - mn) * RNNT_LOG2E);
+          acc += is ? 0.f : e;
+        }
+        sp = acc;
         m = mn;
       }
     } else {
-      for (int i = lane; i < V; i += 32) {
-        const float z = __ldcs(x + i) * RNNT_LOG2E;
-        const float mn = fmaxf(m, z);
-        s = s * exp2f(m - mn) + exp2f(z - mn);
-        m = mn;
-      }
+      for (int i = lane; i < V; i += 32) online_push(m, sp, __ldcs(x + i));
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       const float m2 = __shfl_xor_sync(0xffffffffu, m, o);
-      const float s2 = __shfl_xor_sync(0xffffffffu, s, o);
-      online_merge(m, s, m2, s2);
+      const float s2 = __shfl_xor_sync(0xffffffffu, sp, o);
+      online_merge(m, sp, m2, s2);
     }
     if (lane == 0) {
-      const float lse = (m + log2f(s)) * RNNT_LN2;
+      const float lg = log1pf(sp);
       const size_t idx = plane_index(b, t, u, T, U1);
-      lse_out[idx] = lse;
-      lpb_out[idx] = x[blank] - lse;
+      lse_out[idx] = m + lg;
+      lpb_out[idx] = (x[blank] - m) - lg;
       float ll = -INFINITY;
       if (u < Ub) {
         const int y = clamp_int(labels[(size_t)b * U + u], 0, V - 1);
-        ll = x[y] - lse;
+        ll = (x[y] - m) - lg;
       }
       lpl_out[idx] = ll;
     }

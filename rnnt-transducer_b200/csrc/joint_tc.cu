@@ -458,10 +458,12 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
           const float4 o = red4[row];
           const float mn = fmaxf(m, o.x);
           const float st = s * ex2_approx(m - mn) + o.y * ex2_approx(o.x - mn);
-          const float lse2 = mn + log2f(st);
-          p.lse[pidx] = lse2 * RNNT_LN2;
-          p.lpb[pidx] = (zb + o.z - lse2) * RNNT_LN2;
-          p.lpl[pidx] = (label >= 0) ? (zl + o.w - lse2) * RNNT_LN2 : -INFINITY;
+          const float lg = log2f(st);
+          p.lse[pidx] = (mn + lg) * RNNT_LN2;
+          // (z - max) - log2(sum), not z - lse: exact difference first, so that a dominant blank / label
+          // (z == max) keeps lp = -log2(sum) instead of the rounding of two numbers of size |lse|
+          p.lpb[pidx] = ((zb + o.z - mn) - lg) * RNNT_LN2;
+          p.lpl[pidx] = (label >= 0) ? ((zl + o.w - mn) - lg) * RNNT_LN2 : -INFINITY;
         }
         named_bar_sync(1, kEpiWarps * 32);  // red4[] is free again
       }

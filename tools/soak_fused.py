@@ -1,0 +1,43 @@
+"""Soak run of boundary 2 against the float64 oracle on randomly drawn shapes (GPU box only).
+Usage: python tools/soak_fused.py [N=60] [seed=0]. Prints one line per failing case and a summary;
+exit code 1 when any case misses the tolerances of tests/test_fused_gpu.py."""
+import os, random, sys, traceback
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from tests import gpu_checks as G
+from tests.test_fused_gpu import _assert_fused
+
+N = int(sys.argv[1]) if len(sys.argv) > 1 else 60
+rng = random.Random(int(sys.argv[2]) if len(sys.argv) > 2 else 0)
+VS = [2, 3, 16, 17, 63, 64, 65, 127, 128, 129, 200, 255, 256, 257, 300, 448, 449, 511, 513, 600, 1000, 1025, 4232, 5000]
+HS = [64, 128, 192, 256, 320, 384, 448, 512]
+bad = 0
+for i in range(N):
+    B = rng.randint(1, 5)
+    T = rng.choice([1, 2, 3, 7, 16, 25, 40, 64])
+    U = rng.choice([0, 1, 2, 5, 11, 31, 63, 127, 130])
+    if T * (U + 1) * B > 9000:  # keep the float64 oracle in seconds
+        U = min(U, 11)
+    H = rng.choice(HS)
+    E = rng.choice([8, 24, 64, 128, 320])
+    D = rng.choice([8, 16, 64, 128, 320])
+    V = rng.choice(VS)
+    mode = rng.choice(["ragged", "edge", "full"])
+    host = rng.random() < 0.5
+    v2 = rng.choice([None, None, "0", "4", "8"])
+    if v2 is None:
+        os.environ.pop("RNNT_B200_V2", None)
+    else:
+        os.environ["RNNT_B200_V2"] = v2
+    case = dict(B=B, T=T, U=U, E=E, D=D, H=H, V=V, mode=mode, host_lens=host, v2=v2, seed=1000 + i)
+    try:
+        m = G.fused_synth(B, T, U, E, D, H, V, mode=mode, seed=1000 + i, host_lens=host)
+        _assert_fused(m)
+    except AssertionError as e:
+        bad += 1
+        print("FAIL", case, str(e)[:400], flush=True)
+    except Exception:
+        bad += 1
+        print("ERROR", case, traceback.format_exc()[-600:], flush=True)
+        break  # a CUDA error poisons the context
+print(f"soak: {N} cases, {bad} failed", flush=True)
+sys.exit(1 if bad else 0)
