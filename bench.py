@@ -53,13 +53,21 @@ class ClockSampler:
     def __init__(self, index):
         self.index = index
         self.proc = None
-        self.lines = []
+        self.lines = []      # (receive time, csv line)
+        self.windows = []    # [t0, t1] of the timed regions; only samples received inside them count
+
+    def window_begin(self):
+        self.windows.append([time.monotonic(), None])
+
+    def window_end(self):
+        if self.windows and self.windows[-1][1] is None:
+            self.windows[-1][1] = time.monotonic()
 
     def start(self):
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
         except Exception:
@@ -67,7 +75,7 @@ class ClockSampler:
 
     def _pump(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.monotonic(), line.strip()))
 
     def stop(self):
         if self.proc is None:
@@ -79,7 +87,10 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], None, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        for tr, ln in self.lines:
+            # a sample is the state ~one polling period before it is received
+            if not any(t0 <= tr and (t1 is None or tr <= t1 + 0.05) for t0, t1 in self.windows):
+                continue
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
                 continue
@@ -233,16 +244,19 @@ def main():
     def step_resident():
         return step(d_enc.detach(), d_dec.detach(), d_y, d_tl, d_ul)
 
-    for _ in range(args.warmup):
-        step_resident()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
-        sampler.start()
+        sampler.start()      # started ahead of the warm-up so that it is polling when the timed region begins
+    for _ in range(args.warmup):
+        step_resident()
+    if sampler:
+        sampler.window_begin()
     # per-kernel CUDA events (on the launching stream, no synchronisation) ride along in the timed
     # region: the roofline numbers below are averages over exactly these K steps
     with R.KernelTimer() as kt:
         ms_step, loss = timed(step_resident, args.steps)
-    clocks = sampler.stop() if sampler else None
+    if sampler:
+        sampler.window_end()
     ks = kt.summary()
     launches = kt.launches // args.steps
 
@@ -278,7 +292,12 @@ def main():
     step_e2e()
     torch.cuda.synchronize()
     pending.clear()                          # the timed region starts with no copy in flight
+    if sampler:
+        sampler.window_begin()               # second timed region (same work per step)
     ms_e2e, _ = timed(step_e2e, args.steps)
+    if sampler:
+        sampler.window_end()
+    clocks = sampler.stop() if sampler else None
     h2d = sum(t.numel() * t.element_size() for t in (h_enc, h_dec, h_y, h_tl, h_ul))
 
     # ---------------- roofline of the dominant kernel ----------------
@@ -294,8 +313,10 @@ def main():
             traffic_tab = json.load(f).get(args.workload, {})
     except Exception:
         traffic_tab = {}
-    own = {"joint_fwd": ("joint_kernel<256,0,0> (tcgen05 vocab GEMM + online LSE)", "joint_kernel_fwd_dram_bytes"),
-           "joint_bwd_ds": ("joint_kernel<256,1,0> (tcgen05 vocab GEMM recompute + dS epilogue)",
+    from rnnt_transducer_b200 import _lib
+    bn = _lib.lib().rnnt_b200_vocab_tile(V)                          # UMMA N of the vocabulary tiles (64 / 128 / 256)
+    own = {"joint_fwd": (f"joint_kernel<{bn},0,0> (tcgen05 vocab GEMM + online LSE)", "joint_kernel_fwd_dram_bytes"),
+           "joint_bwd_ds": (f"joint_kernel<{bn},1,0> (tcgen05 vocab GEMM recompute + dS epilogue)",
                             "joint_kernel_bwd_dram_bytes_per_chunk"),
            "dw2_gemm": ("dw2_gemm_kernel (tcgen05 dS^T.[h|1], MN-major operands)", "dw2_gemm_dram_bytes_per_chunk")}
 
