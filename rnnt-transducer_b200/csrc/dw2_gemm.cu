@@ -46,7 +46,7 @@ struct GwParams {
   int N;           // UMMA N of a unit: 256 (H a multiple of 256) or 128 (H = 128)
   int ksteps;      // 64-row K blocks in the chunk
   int splits, ks_per_split;
-  int debug;  // RNNT_B200_DW2_DEBUG (timing experiments): 1 no ones-MMA, 2 no main MMA, 4 no epilogue adds, 8 no TMA loads
+  int debug;  // RNNT_B200_DW2_DEBUG (timing experiments): 1 no ones-MMA, 2 no main MMA, 4 no epilogue adds, 8 no TMA loads, 16 no A reuse through the collector
 };
 
 // MN-major operand, SWIZZLE_128B (see the header comment); version 1 = sm_100.
@@ -164,9 +164,16 @@ dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
               const uint64_t adesc = umma_desc_mn128(a0 + kk * 2048, GW_BLOCK);
               const uint64_t bdesc = umma_desc_mn128(b0 + kk * 2048, GW_BLOCK);
               const uint32_t acc = (k > k0 || kk > 0) ? 1u : 0u;
-              if (!(p.debug & 2)) umma_bf16_ss_pair(tmem_base, adesc, bdesc, idesc_main, acc);
-              if ((p.nj == 1 || ((k + jh) & 1) == 0) && !(p.debug & 1))
-                umma_bf16_ss_pair(tmem_base + 256, adesc, ones_desc, idesc_ones, (k > k_ones0 || kk > 0) ? 1u : 0u);
+              const bool with_ones = (p.nj == 1 || ((k + jh) & 1) == 0) && !(p.debug & 1);
+              // the ones-UMMA multiplies the same A slice: kept in the collector by the main UMMA, so
+              // shared memory is read for it once (without this the db2 UMMAs added 25 % to the A reads)
+              if (with_ones && !(p.debug & (2 | 16))) {
+                umma_bf16_ss_pair_areuse<1>(tmem_base, adesc, bdesc, idesc_main, acc);
+                umma_bf16_ss_pair_areuse<0>(tmem_base + 256, adesc, ones_desc, idesc_ones, (k > k_ones0 || kk > 0) ? 1u : 0u);
+              } else {
+                if (!(p.debug & 2)) umma_bf16_ss_pair(tmem_base, adesc, bdesc, idesc_main, acc);
+                if (with_ones) umma_bf16_ss_pair(tmem_base + 256, adesc, ones_desc, idesc_ones, (k > k_ones0 || kk > 0) ? 1u : 0u);
+              }
             }
             umma_commit_pair_mc(&ctl->empty[stage], 3);
             if (k == k1 - 1) umma_commit_pair_mc(&ctl->acc_full, 3);
@@ -245,8 +252,15 @@ extern "C" int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long 
   p.nj = H / p.N;
   p.ksteps = (int)(rows / 64);
   const int pairs = sm_count() / 2;
+  // One wave of units: splits = pairs / (nvt * nj) leaves 6 of the 74 pairs idle at the AISHELL shape
+  // (68 units). Filling them (13 splits = 442 units = 5.97 waves) made this kernel 3 % faster inside the
+  // step and the step no faster (24.7 / 25.1 against 24.3 / 24.8 ms in the same call): the chip sits at its
+  // power cap, the extra SMs only lower the clock of everything else; alone, 1.455 against 1.431 ms.
   int splits = pairs / (p.nvt * p.nj);
   if (splits < 1) splits = 1;
+  if (const char* e = getenv("RNNT_B200_DW2_SPLITS")) {  // timing experiments only
+    if (atoi(e) >= 1) splits = atoi(e);
+  }
   if (splits > p.ksteps) splits = p.ksteps;
   p.ks_per_split = (p.ksteps + splits - 1) / splits;
   p.splits = (p.ksteps + p.ks_per_split - 1) / p.ks_per_split;  // every unit has K blocks

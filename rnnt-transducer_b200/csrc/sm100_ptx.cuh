@@ -218,6 +218,32 @@ __device__ __forceinline__ void umma_bf16_ss_pair(uint32_t tmem_d, uint64_t ades
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// The same with the A operand kept in / taken from the tensor core's collector buffer: two consecutive
+// MMAs of one thread that share their A tile read it from shared memory once (SASS: gdesc.A_KEEP on the
+// first, gdesc.A_REUSE on the second). KEEP = 1: collector::a::fill, KEEP = 0: collector::a::lastuse.
+template <int KEEP>
+__device__ __forceinline__ void umma_bf16_ss_pair_areuse(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                                         uint32_t idesc, uint32_t accumulate) {
+  if (KEEP) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16.collector::a::fill [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16.collector::a::lastuse [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  }
+}
 // commit -> arrive on the barrier at this smem offset in every CTA of `mask`
 __device__ __forceinline__ void umma_commit_pair_mc(uint64_t* bar, uint16_t mask) {
   asm volatile(
