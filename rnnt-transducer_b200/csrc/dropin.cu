@@ -10,6 +10,7 @@
 // One warp per lattice cell; 16-byte vector loads/stores when V % 4 == 0; grid sized to a
 // multiple of the SM count with a grid-stride loop over cells.
 #include "common.cuh"
+#include "sm100_ptx.cuh"
 
 namespace {
 
@@ -25,17 +26,17 @@ __device__ __forceinline__ void online_merge(float& m, float& sp, float m2, floa
   float r;
   if (mn == -INFINITY) r = 0.f;                                                  // both empty
   else if (m == m2) r = sp + sp2 + 1.f;                                          // one of the two maxima turns ordinary
-  else if (m > m2) r = sp + (sp2 + 1.f) * exp2f((m2 - m) * RNNT_LOG2E);          // exp2f(-inf) = 0: empty side adds nothing
-  else r = sp2 + (sp + 1.f) * exp2f((m - m2) * RNNT_LOG2E);
+  else if (m > m2) r = sp + (sp2 + 1.f) * sm100::ex2_approx((m2 - m) * RNNT_LOG2E);          // sm100::ex2_approx(-inf) = 0: empty side adds nothing
+  else r = sp2 + (sp + 1.f) * sm100::ex2_approx((m - m2) * RNNT_LOG2E);
   m = mn;
   sp = r;
 }
 // one more element x into (m, sp)
 __device__ __forceinline__ void online_push(float& m, float& sp, float x) {
   if (x <= m) {
-    sp += exp2f((x - m) * RNNT_LOG2E);        // ordinary term (x = -inf adds 0)
+    sp += sm100::ex2_approx((x - m) * RNNT_LOG2E);        // ordinary term (x = -inf adds 0)
   } else if (x > m) {                         // new maximum: the old one turns ordinary (m = -inf: (0 + 1) * 0)
-    sp = (sp + 1.f) * exp2f((m - x) * RNNT_LOG2E);
+    sp = (sp + 1.f) * sm100::ex2_approx((m - x) * RNNT_LOG2E);
     m = x;
   } else {                                    // NaN logit: poison the row like the plain formulation does
     sp = x;
@@ -73,13 +74,13 @@ logits_to_planes_kernel(const float* __restrict__ logits, const int32_t* __restr
         // occurrence, the others are ordinary terms exp(c - mn): five exponentials per four logits,
         // branch free (a fast path for "maximum unchanged" diverges within the warp and was slower)
         bool taken = (m == mn);
-        float acc = taken ? sp : (sp + 1.f) * exp2f((m - mn) * RNNT_LOG2E);  // m = -inf: (0 + 1) * 0
+        float acc = taken ? sp : (sp + 1.f) * sm100::ex2_approx((m - mn) * RNNT_LOG2E);  // m = -inf: (0 + 1) * 0
         const float c[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const bool is = !taken && (c[j] == mn);
           taken = taken || is;
-          const float e = exp2f((c[j] - mn) * RNNT_LOG2E);
+          const float e = sm100::ex2_approx((c[j] - mn) * RNNT_LOG2E);
           acc += is ? 0.f : e;
         }
         sp = acc;
@@ -106,6 +107,83 @@ logits_to_planes_kernel(const float* __restrict__ logits, const int32_t* __restr
       }
       lpl_out[idx] = ll;
     }
+  }
+}
+
+// Exact n / d for n < 2^31 by one multiply-high and a shift (d fixed per launch; the two per-cell
+// divisions by T*U1 and U1 were 10 % of the issued instructions at small V).
+struct FastDiv {
+  uint32_t mul, shr, d;
+};
+__host__ inline FastDiv make_fastdiv(uint32_t d) {
+  FastDiv f;
+  f.d = d;
+  if (d == 1) { f.mul = 0; f.shr = 0; return f; }
+  uint32_t lg = 0;
+  while ((1ull << lg) < d) ++lg;  // ceil(log2 d)
+  const uint32_t pw = 31 + lg;
+  f.mul = (uint32_t)(((1ull << pw) + d - 1) / d);
+  f.shr = pw - 32;
+  return f;
+}
+__device__ __forceinline__ uint32_t fastdiv(uint32_t n, const FastDiv& f) {
+  return f.d == 1 ? n : (__umulhi(n, f.mul) >> f.shr);
+}
+
+// Small vocabularies (V <= 256, e.g. TIMIT's 49): G lanes per lattice cell, 32/G cells per warp. With one
+// warp per cell the kernel was bound by issued instructions (83 % issue-active, 5 % of the HBM peak: the
+// per-cell index arithmetic, five shuffle-merge rounds and the tail are paid per WARP); packing 2 or 4
+// cells into a warp divides them. Same (m, sp) formulation as above, scalar loads (rows of V floats
+// are only 4-byte aligned). Cell count < 2^31 (the host falls back to the kernel above otherwise).
+template <int G>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+logits_to_planes_small_kernel(const float* __restrict__ logits, const int32_t* __restrict__ labels,
+                              const int32_t* __restrict__ act_lens, const int32_t* __restrict__ label_lens,
+                              int B, int T, int U1, int V, int blank, FastDiv dTU, FastDiv dU1,
+                              float* __restrict__ lse_out, float* __restrict__ lpb_out,
+                              float* __restrict__ lpl_out) {
+  constexpr int CPW = 32 / G;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / G, gl = lane % G;
+  const uint32_t ncell = (uint32_t)B * (uint32_t)T * (uint32_t)U1;
+  const uint32_t stride = gridDim.x * WARPS_PER_BLOCK * CPW;
+  const int U = U1 - 1;
+  for (uint32_t c0 = (blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5)) * CPW; c0 < ncell; c0 += stride) {
+    const uint32_t cell = c0 + sub;
+    bool valid = cell < ncell;
+    int b = 0, t = 0, u = 0, Ub = 0;
+    if (valid) {
+      b = (int)fastdiv(cell, dTU);
+      const uint32_t r = cell - (uint32_t)b * dTU.d;
+      t = (int)fastdiv(r, dU1);
+      u = (int)(r - (uint32_t)t * dU1.d);
+      const int Tb = clamp_int(__ldg(act_lens + b), 1, T);
+      Ub = clamp_int(__ldg(label_lens + b), 0, U);
+      valid = t < Tb && u <= Ub;
+    }
+    const float* x = logits + (size_t)cell * V;
+    float m = -INFINITY, sp = 0.f, xb = 0.f, xl = 0.f;
+    int y = -1;
+    if (valid) {
+      if (u < Ub) y = clamp_int(__ldg(labels + (size_t)b * U + u), 0, V - 1);
+      xb = __ldg(x + blank);
+      for (int i = gl; i < V; i += G) online_push(m, sp, __ldcs(x + i));
+      if (y >= 0) xl = __ldg(x + y);
+    }
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) {  // stays inside the group of G lanes; every lane takes part
+      const float m2 = __shfl_xor_sync(0xffffffffu, m, o);
+      const float s2 = __shfl_xor_sync(0xffffffffu, sp, o);
+      online_merge(m, sp, m2, s2);
+    }
+    if (valid && gl == 0) {
+      const float lg = log1pf(sp);
+      const size_t idx = plane_index(b, t, u, T, U1);
+      lse_out[idx] = m + lg;
+      lpb_out[idx] = (xb - m) - lg;
+      lpl_out[idx] = (y >= 0) ? (xl - m) - lg : -INFINITY;
+    }
+    if (c0 > 0xffffffffu - stride) break;  // 32-bit wrap guard
   }
 }
 
@@ -197,8 +275,18 @@ extern "C" int rnnt_b200_logits_to_planes(const float* logits, const int32_t* la
   if (blank < 0 || blank >= V) return RNNT_B200_E_BLANK;
   if ((V & 3) == 0 && ((uintptr_t)logits & 15)) return RNNT_B200_E_ALIGN;
   const long long ncell = (long long)B * T * U1;
-  logits_to_planes_kernel<<<grid_for_cells(ncell), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
-      logits, labels, act_lens, label_lens, B, T, U1, V, blank, lse, lp_blank, lp_label);
+  if (V <= 256 && ncell < 0x7fffffffLL) {  // several cells per warp
+    const FastDiv dTU = make_fastdiv((uint32_t)T * (uint32_t)U1), dU1 = make_fastdiv((uint32_t)U1);
+    if (V <= 64)
+      logits_to_planes_small_kernel<8><<<grid_for_cells((ncell + 3) / 4), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
+          logits, labels, act_lens, label_lens, B, T, U1, V, blank, dTU, dU1, lse, lp_blank, lp_label);
+    else
+      logits_to_planes_small_kernel<16><<<grid_for_cells((ncell + 1) / 2), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
+          logits, labels, act_lens, label_lens, B, T, U1, V, blank, dTU, dU1, lse, lp_blank, lp_label);
+  } else {
+    logits_to_planes_kernel<<<grid_for_cells(ncell), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
+        logits, labels, act_lens, label_lens, B, T, U1, V, blank, lse, lp_blank, lp_label);
+  }
   RNNT_CUDA_RETURN_IF_ERROR();
   return RNNT_B200_OK;
 }
