@@ -255,6 +255,53 @@ planes_to_dlogits_kernel(const float* __restrict__ logits, const int32_t* __rest
   }
 }
 
+// Small vocabularies: G lanes per cell, 32/G cells per warp (see logits_to_planes_small_kernel).
+template <int G>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+planes_to_dlogits_small_kernel(const float* __restrict__ logits, const int32_t* __restrict__ labels,
+                               const int32_t* __restrict__ act_lens, const int32_t* __restrict__ label_lens,
+                               int B, int T, int U1, int V, int blank, FastDiv dTU, FastDiv dU1,
+                               const float* __restrict__ lse_p, const float* __restrict__ cb_p,
+                               const float* __restrict__ cl_p, const float* __restrict__ scale,
+                               float* __restrict__ dlogits) {
+  constexpr int CPW = 32 / G;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / G, gl = lane % G;
+  const uint32_t ncell = (uint32_t)B * (uint32_t)T * (uint32_t)U1;
+  const uint32_t stride = gridDim.x * WARPS_PER_BLOCK * CPW;
+  const int U = U1 - 1;
+  for (uint32_t c0 = (blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5)) * CPW; c0 < ncell; c0 += stride) {
+    const uint32_t cell = c0 + sub;
+    if (cell < ncell) {
+      const int b = (int)fastdiv(cell, dTU);
+      const uint32_t r = cell - (uint32_t)b * dTU.d;
+      const int t = (int)fastdiv(r, dU1);
+      const int u = (int)(r - (uint32_t)t * dU1.d);
+      const int Tb = clamp_int(__ldg(act_lens + b), 1, T);
+      const int Ub = clamp_int(__ldg(label_lens + b), 0, U);
+      float* g = dlogits + (size_t)cell * V;
+      if (t >= Tb || u > Ub) {  // outside the valid window: exact zeros
+        for (int i = gl; i < V; i += G) __stcs(g + i, 0.f);
+      } else {
+        const float* x = logits + (size_t)cell * V;
+        const size_t idx = plane_index(b, t, u, T, U1);
+        const float sc = __ldg(scale + b);
+        const float cb = __ldg(cb_p + idx) * sc, cl = __ldg(cl_p + idx) * sc;
+        const float c0f = cb + cl;
+        const float nl = -__ldg(lse_p + idx) * RNNT_LOG2E;
+        const int y = (u < Ub) ? clamp_int(__ldg(labels + (size_t)b * U + u), 0, V - 1) : -1;
+        for (int i = gl; i < V; i += G) {
+          float o = exp2f(fmaf(__ldcs(x + i), RNNT_LOG2E, nl)) * c0f;
+          if (i == blank) o -= cb;
+          if (i == y) o -= cl;
+          __stcs(g + i, o);
+        }
+      }
+    }
+    if (c0 > 0xffffffffu - stride) break;  // 32-bit wrap guard
+  }
+}
+
 int grid_for_cells(long long ncell) {
   long long blocks = (ncell + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK;
   const long long cap = 148LL * 8 * 4;  // 4 waves of 8 resident CTAs per SM
@@ -303,8 +350,18 @@ extern "C" int rnnt_b200_planes_to_dlogits(const float* logits, const int32_t* l
   if (blank < 0 || blank >= V) return RNNT_B200_E_BLANK;
   if ((V & 3) == 0 && (((uintptr_t)logits & 15) || ((uintptr_t)dlogits & 15))) return RNNT_B200_E_ALIGN;
   const long long ncell = (long long)B * T * U1;
-  planes_to_dlogits_kernel<<<grid_for_cells(ncell), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
-      logits, labels, act_lens, label_lens, B, T, U1, V, blank, lse, c_blank, c_label, scale, dlogits);
+  if (V <= 256 && ncell < 0x7fffffffLL) {  // several cells per warp
+    const FastDiv dTU = make_fastdiv((uint32_t)T * (uint32_t)U1), dU1 = make_fastdiv((uint32_t)U1);
+    if (V <= 64)
+      planes_to_dlogits_small_kernel<8><<<grid_for_cells((ncell + 3) / 4), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
+          logits, labels, act_lens, label_lens, B, T, U1, V, blank, dTU, dU1, lse, c_blank, c_label, scale, dlogits);
+    else
+      planes_to_dlogits_small_kernel<16><<<grid_for_cells((ncell + 1) / 2), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
+          logits, labels, act_lens, label_lens, B, T, U1, V, blank, dTU, dU1, lse, c_blank, c_label, scale, dlogits);
+  } else {
+    planes_to_dlogits_kernel<<<grid_for_cells(ncell), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
+        logits, labels, act_lens, label_lens, B, T, U1, V, blank, lse, c_blank, c_label, scale, dlogits);
+  }
   RNNT_CUDA_RETURN_IF_ERROR();
   return RNNT_B200_OK;
 }
