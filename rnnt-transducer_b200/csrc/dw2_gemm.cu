@@ -227,6 +227,193 @@ dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
   if (warp == 1) tmem_dealloc_pair(tmem_base, 512);
 }
 
+// ---------------------------------------------------------------------------------------
+// H = 512: one CTA pair takes a 256-row vocabulary tile against ALL of H. Per K = 16 slice two UMMAs
+// (columns 0..255 and 256..511 of H, TMEM columns 0..255 / 256..511) share the dS^T slice through
+// the tensor core's collector (A_KEEP / A_REUSE): shared memory is read for it once, the dS boxes
+// are fetched once per tile instead of once per column half (48 + 48 instead of 64 + 64 B/clk of
+// shared-memory fill + operand reads, dS out of L2 once). TMEM is full, so db2 cannot ride along as
+// an N = 16 UMMA: the four epilogue warps, idle during the K loop, sum the columns of the dS boxes
+// from shared memory (16-byte loads along v, 8 row groups, +16 B/clk) once the stage's UMMAs have
+// retired, release the stage, and add their partial sums with red.global.add at the end of the unit.
+// Warps as above: 0 dS TMA, 6 h TMA, 1 MMA issuer, 2-5 column sums during the K loop + epilogue.
+// ---------------------------------------------------------------------------------------
+constexpr int GWW_STAGES = 4;
+constexpr int GWW_STAGE = 6 * GW_BLOCK;  // A: 2 boxes (128 v), B: 4 boxes (2 x 128 j)
+constexpr int GWW_SMEM = GWW_STAGES * GWW_STAGE + 256;
+
+struct GwwCtl {
+  uint64_t full[GWW_STAGES], mma_done[GWW_STAGES], empty[GWW_STAGES], acc_full, acc_empty;
+  uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(GW_THREADS, 1)
+dw2_wide_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constant__ CUtensorMap map_h,
+                const GwParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  GwwCtl* ctl = reinterpret_cast<GwwCtl*>(smem + GWW_STAGES * GWW_STAGE);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int cid = blockIdx.x >> 1, ncl = gridDim.x >> 1;
+  const int n_units = p.splits * p.nvt;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_ds);
+    tma_prefetch_desc(&map_h);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < GWW_STAGES; ++i) {
+      mbar_init(&ctl->full[i], 4);      // {dS, h} producer x {leader, peer}; lives in the leader CTA
+      mbar_init(&ctl->mma_done[i], 1);  // multicast commit behind the stage's UMMAs (both CTAs)
+      mbar_init(&ctl->empty[i], 4);     // this CTA's four column-sum warps, after they have read the dS boxes
+    }
+    mbar_init(&ctl->acc_full, 1);
+    mbar_init(&ctl->acc_empty, 2 * 4);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) {
+    tmem_alloc_pair(&ctl->tmem_base, 512);
+    tmem_relinquish_pair();
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = ctl->tmem_base;
+
+  if (warp == 0 || warp == 6) {
+    const bool is_a = warp == 0;
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int u = cid; u < n_units; u += ncl) {
+        const int vt = u % p.nvt, s = u / p.nvt;
+        const int k0 = s * p.ks_per_split, k1 = min(p.ksteps, k0 + p.ks_per_split);
+        const int v0 = vt * 256 + (int)rank * 128;
+        for (int k = k0; k < k1; ++k) {
+          mbar_wait(&ctl->empty[stage], phase ^ 1);
+          const uint32_t full = mapa_u32(smem_u32(&ctl->full[stage]), 0);
+          const int nbox = is_a ? 2 : 4;
+          if (rank == 0) mbar_arrive_expect_tx(&ctl->full[stage], 2 * nbox * GW_BLOCK);  // both CTAs
+          else mbar_arrive_cluster(full);
+          uint8_t* st = smem + stage * GWW_STAGE + (is_a ? 0 : 2 * GW_BLOCK);
+          if (is_a) {
+            tma_load_2d_pair(st, &map_ds, full, v0, k * 64);
+            tma_load_2d_pair(st + GW_BLOCK, &map_ds, full, v0 + 64, k * 64);
+          } else {
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {  // this CTA's 128 of the 256 columns of each half of H
+              const int j0 = hf * 256 + (int)rank * 128;
+              tma_load_2d_pair(st + (2 * hf) * GW_BLOCK, &map_h, full, j0, k * 64);
+              tma_load_2d_pair(st + (2 * hf + 1) * GW_BLOCK, &map_h, full, j0 + 64, k * 64);
+            }
+          }
+          if (++stage == GWW_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (rank == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16_mn(256, 256);
+      const uint32_t s0 = smem_u32(smem);
+      uint32_t stage = 0, phase = 0;
+      int it = 0;
+      for (int u = cid; u < n_units; u += ncl, ++it) {
+        const int s = u / p.nvt;
+        const int k0 = s * p.ks_per_split, k1 = min(p.ksteps, k0 + p.ks_per_split);
+        mbar_wait(&ctl->acc_empty, (it & 1) ^ 1);
+        tc_fence_after();
+        for (int k = k0; k < k1; ++k) {
+          mbar_wait(&ctl->full[stage], phase);
+          tc_fence_after();
+          if (elect_one_sync()) {
+            const uint32_t a0 = s0 + stage * GWW_STAGE, b0 = a0 + 2 * GW_BLOCK;
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+              const uint64_t adesc = umma_desc_mn128(a0 + kk * 2048, GW_BLOCK);
+              const uint64_t bdesc0 = umma_desc_mn128(b0 + kk * 2048, GW_BLOCK);
+              const uint64_t bdesc1 = umma_desc_mn128(b0 + 2 * GW_BLOCK + kk * 2048, GW_BLOCK);
+              const uint32_t acc = (k > k0 || kk > 0) ? 1u : 0u;
+              umma_bf16_ss_pair_areuse<1>(tmem_base, adesc, bdesc0, idesc, acc);
+              umma_bf16_ss_pair_areuse<0>(tmem_base + 256, adesc, bdesc1, idesc, acc);
+            }
+            umma_commit_pair_mc(&ctl->mma_done[stage], 3);
+            if (k == k1 - 1) umma_commit_pair_mc(&ctl->acc_full, 3);
+          }
+          __syncwarp();
+          if (++stage == GWW_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp < 6) {
+    const int q = warp & 3;          // TMEM lane quadrant this warp may read
+    const int tid = (warp - 2) * 32 + lane;
+    const int chunk = tid & 15;      // 8 consecutive v of this CTA's 128
+    const int rg = tid >> 4;         // rows 8*rg .. 8*rg+7 of a 64-row K block
+    const uint8_t* box = smem + (chunk >> 3) * GW_BLOCK;
+    uint32_t stage = 0, phase = 0;
+    int it = 0;
+    for (int u = cid; u < n_units; u += ncl, ++it) {
+      const int vt = u % p.nvt, s = u / p.nvt;
+      const int k0 = s * p.ks_per_split, k1 = min(p.ksteps, k0 + p.ks_per_split);
+      // ---- column sums of this CTA's dS boxes while the UMMAs run ----
+      float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int k = k0; k < k1; ++k) {
+        // The full barrier exists only in the leader CTA, so the column-sum warps of both CTAs take the
+        // stage behind its UMMAs (commit multicast) and hand it back to the producers themselves.
+        mbar_wait(&ctl->mma_done[stage], phase);
+        const uint8_t* a = box + stage * GWW_STAGE;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int r = rg * 8 + i;  // 128-byte row r of the box; 16-byte chunks XOR-swizzled with r % 8
+          const uint4 w = *reinterpret_cast<const uint4*>(a + r * 128 + (((chunk & 7) ^ (r & 7)) << 4));
+          const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            cs[2 * j] += __uint_as_float(ww[j] << 16);
+            cs[2 * j + 1] += __uint_as_float(ww[j] & 0xffff0000u);
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&ctl->empty[stage]);  // this warp is done with the stage
+        if (++stage == GWW_STAGES) { stage = 0; phase ^= 1; }
+      }
+      {
+        const int v = vt * 256 + (int)rank * 128 + chunk * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (v + j < p.Vds) atomicAdd(p.db2 + v + j, cs[j]);
+      }
+      // ---- accumulators -> dW2 ----
+      const int v = vt * 256 + (int)rank * 128 + q * 32 + lane;
+      mbar_wait(&ctl->acc_full, it & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+      float* dst = p.dw2 + (size_t)v * p.H;
+#pragma unroll 1
+      for (int c = 0; c < 512 / 16; ++c) {
+        float z[16];
+        tmem_ld_32x16(taddr + c * 16, z);
+        tmem_ld_wait();
+        if (v < p.Vds && !(p.debug & 4)) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            atomicAdd(reinterpret_cast<float4*>(dst + c * 16) + i,
+                      make_float4(z[4 * i], z[4 * i + 1], z[4 * i + 2], z[4 * i + 3]));
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&ctl->acc_empty), 0));
+    }
+  }
+  __syncwarp();
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) tmem_dealloc_pair(tmem_base, 512);
+}
+
 }  // namespace
 
 extern "C" int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long long rows, int V, int H,
@@ -265,21 +452,32 @@ extern "C" int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long 
   p.ks_per_split = (p.ksteps + splits - 1) / splits;
   p.splits = (p.ksteps + p.ks_per_split - 1) / p.ks_per_split;  // every unit has K blocks
   { const char* d = getenv("RNNT_B200_DW2_DEBUG"); p.debug = d ? atoi(d) : 0; }
-  const int units = p.splits * p.nvt * p.nj;
+  bool wide = (H == 512);
+  { const char* w = getenv("RNNT_B200_DW2_WIDE"); if (w && atoi(w) == 0) wide = false; }  // A/B only
+  if (wide) {  // units are (split, tile): recompute the split for nvt units per split
+    int sw = pairs / p.nvt;
+    if (sw < 1) sw = 1;
+    if (const char* e = getenv("RNNT_B200_DW2_SPLITS")) { if (atoi(e) >= 1) sw = atoi(e); }
+    if (sw > p.ksteps) sw = p.ksteps;
+    p.ks_per_split = (p.ksteps + sw - 1) / sw;
+    p.splits = (p.ksteps + p.ks_per_split - 1) / p.ks_per_split;
+  }
+  const int units = wide ? p.splits * p.nvt : p.splits * p.nvt * p.nj;
   const int grid = 2 * (units < pairs ? units : pairs);
-  cudaError_t e = cudaFuncSetAttribute(dw2_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GW_SMEM);
+  cudaError_t e = wide ? cudaFuncSetAttribute(dw2_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GWW_SMEM)
+                       : cudaFuncSetAttribute(dw2_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GW_SMEM);
   if (e != cudaSuccess) return (int)e;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(GW_THREADS);
-  cfg.dynamicSmemBytes = GW_SMEM;
+  cfg.dynamicSmemBytes = wide ? GWW_SMEM : GW_SMEM;
   cfg.stream = (cudaStream_t)stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  e = cudaLaunchKernelEx(&cfg, dw2_gemm_kernel, mds, mh, p);
+  e = wide ? cudaLaunchKernelEx(&cfg, dw2_wide_kernel, mds, mh, p) : cudaLaunchKernelEx(&cfg, dw2_gemm_kernel, mds, mh, p);
   if (e != cudaSuccess) return (int)e;
   return RNNT_B200_OK;
 }
