@@ -15,6 +15,8 @@
 // run on neighbouring pairs at the same time, so the second read of dS hits L2.
 // Warps: 0 dS TMA producer, 6 h TMA producer, 1 MMA issuer (+ TMEM), 2-5 epilogue (TMEM ->
 // red.global.add.v4.f32).
+// H = 512 runs dw2_wide_kernel further down instead (256 x 512 tile per pair, collector reuse of the
+// dS^T slice, db2 by the epilogue warps); dw2_gemm_kernel serves H = 128 and 256 and the A/B switch.
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <stdlib.h>
