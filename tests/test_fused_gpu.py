@@ -110,7 +110,9 @@ def test_full_size_properties_at_the_headline_shape():
 
 
 @pytest.mark.parametrize("rows,V,H", [(64, 200, 256), (128, 256, 512), (1024, 500, 512), (8192, 4232, 512),
-                                      (4096, 49, 128), (192, 300, 128)])
+                                      (4096, 49, 128), (192, 300, 128),
+                                      # more (split, tile) units than CTA pairs: a pair walks several units
+                                      (512, 20000, 512), (192, 33000, 128), (256, 19500, 256)])
 def test_dw2_gemm_matches_torch(rows, V, H):
     # the MN-major tcgen05 GEMM behind dW2/db2 on its own (fp32 accumulation of bf16 products)
     m = G.dw2_gemm_vs_torch(rows, V, H)
