@@ -312,6 +312,14 @@ class _JointLossFn(torch.autograd.Function):
             nchunk = -(-max_tiles // chunk)
             chunk = -(-max_tiles // nchunk)          # balanced chunks,
             chunk += chunk & 1                       # whole CTA-pair tiles
+            # whole waves of the persistent backward kernel (one tile per SM and wave): with balanced chunks
+            # every launch ends in a partial wave (AISHELL shape: 4 x 21.3 -> 4 x 22 waves); chunks of
+            # k * SMs tiles leave one partial wave per step (22 + 22 + 22 + 19.3 -> 86 instead of 88)
+            sms = torch.cuda.get_device_properties(dev).multi_processor_count
+            if chunk >= 4 * sms and os.environ.get("RNNT_B200_WAVE_CHUNK", "1") != "0":
+                up = -(-chunk // sms) * sms
+                if up * 128 * Vds * 2 <= max(_DS_BUDGET_BYTES, chunk * 128 * Vds * 2):
+                    chunk = up
             ds = torch.empty(chunk * 128, Vds, dtype=torch.bfloat16, device=dev)
             w2v = w2q[:Vds]                          # rows Vds..Vpad of the pack are padding only
             for lo in range(0, max_tiles, chunk):
