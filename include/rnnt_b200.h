@@ -110,12 +110,11 @@ int rnnt_b200_vocab_tile(int V);
 int rnnt_b200_pack_vocab(const float* w2, const float* b2, int V, int H,
                          void* w2_bf16, float* b2_log2, void* stream);
 
-/* Row pitch (elements) of the stashed hidden activations h: H + 32. Column H holds 1.0 for valid
+/* Row pitch (elements) of the stashed hidden activations h. H = 128, 256, 512 (the shapes
+ * rnnt_b200_dw2_gemm covers; it sums d b2 itself): H. Other H: H + 32, column H holds 1.0 for valid
  * cells (columns H+1..H+7 zero, H+8.. unwritten) so that the library GEMM h_ext^T . dS yields d b2
- * in row H of its output. (Column sums inside the dS kernel -- shuffles, legacy warp MMA +
- * reductions -- and a separate column-sum pass over dS were tried and cost more than the wider
- * GEMM shape; pitch H+32 is the fastest of the widths the library was tried with:
- * profiles/r01_notes.md.) */
+ * in row H of its output (pitch H+32 is the fastest of the widths the library was tried with:
+ * profiles/r01_notes.md). */
 int rnnt_b200_h_pitch(int H);
 
 /* Row pitch (elements) of the staged bf16 logit gradient dS: V rounded up to 64 (128-byte rows;
@@ -127,7 +126,7 @@ int rnnt_b200_ds_pitch(int V);
 /* Hidden activations of the joint: h = bf16(tanh(P_enc[b,t,:] + P_dec[b,u,:])) for every valid
  * lattice cell, tile-packed (model.py:26-34 without the repeat/cat): row tile*128 + r of h_stash is
  * cell tile_cell0[tile] + r of utterance tile_utt[tile]; rows past an utterance's last cell and
- * tiles past the table are zeros; column H is 1.0 for valid cells.
+ * tiles past the table are zeros; where the pitch exceeds H, column H is 1.0 for valid cells.
  * h_stash: bf16 workspace (tile_cap*128, rnnt_b200_h_pitch(H)), 128-byte aligned. It is the A
  * operand of rnnt_b200_joint_fwd / _bwd_ds (TMA) and an operand of the backward library GEMMs. */
 int rnnt_b200_joint_hidden(const float* p_enc, const float* p_dec,

@@ -301,8 +301,8 @@ class _JointLossFn(torch.autograd.Function):
             dpd = torch.zeros(B, U1, H, dtype=torch.float32, device=dev)
             hp = h_stash.shape[1]
             # dW2/db2: own tcgen05 GEMM (csrc/dw2_gemm.cu) where it covers the shape, else the
-            # library GEMM against the ones column of the stash (RNNT_B200_DW2=lib: A/B timing)
-            own_gemm = H in (128, 256, 512) and os.environ.get("RNNT_B200_DW2", "own") == "own"
+            # library GEMM against the ones column of the stash
+            own_gemm = H in (128, 256, 512)          # the stash has no ones column at these H (pitch == H)
             if own_gemm:
                 dw2x = torch.zeros(Vds, H, dtype=torch.float32, device=dev)
                 db2x = torch.zeros(Vds, dtype=torch.float32, device=dev)

@@ -8,7 +8,8 @@ import subprocess
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "librnnt_b200.so")
+# RNNT_B200_LIB: another build of the same library (A/B timing of compile-time variants in one call)
+SO_PATH = os.environ.get("RNNT_B200_LIB") or os.path.join(_HERE, "librnnt_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
 _lock = threading.Lock()
 _lib = None

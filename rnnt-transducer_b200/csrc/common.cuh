@@ -15,12 +15,15 @@
     if (e__ != cudaSuccess) return (int)e__;               \
   } while (0)
 
-// Row pitch (elements) of the tile-packed bf16 hidden-activation stash: H columns, the ones column
-// at column H (its GEMM against dS gives d b2), padding up to the pitch.
+// Row pitch (elements) of the tile-packed bf16 hidden-activation stash. H = 128, 256, 512 (the shapes the
+// own dW2 GEMM covers, which sums db2 itself): H, rows of whole 128-byte lines. Other H: H + 32 with the
+// ones column at column H (its library GEMM against dS gives d b2) and padding up to the pitch.
 #ifndef RNNT_H_PAD
 #define RNNT_H_PAD 32
 #endif
-__host__ __device__ constexpr int rnnt_hp(int H) { return H + RNNT_H_PAD; }
+__host__ __device__ constexpr int rnnt_hp(int H) {
+  return (H == 128 || H == 256 || H == 512) ? H : H + RNNT_H_PAD;
+}
 
 // Anti-diagonal-major plane index of cell (t,u) of utterance b (see rnnt_b200.h).
 __host__ __device__ __forceinline__ size_t plane_index(int b, int t, int u, int T, int U1) {

@@ -647,7 +647,7 @@ hidden_kernel(const JointParams p, int max_tiles) {
       w = clamp_int(__ldg(p.label_lens + b), 0, p.U1 - 1) + 1;
       ncell = clamp_int(__ldg(p.act_lens + b), 1, p.T) * w;
     }
-    if (threadIdx.x < RNNT_TILE_M)
+    if (hp > p.H && threadIdx.x < RNNT_TILE_M)  // the ones column exists only where the library GEMM needs it
       *reinterpret_cast<uint4*>(dst_tile + (size_t)threadIdx.x * hp + p.H) =
           make_uint4(cell0 + (int)threadIdx.x < ncell ? 0x00003F80u : 0u, 0u, 0u, 0u);
     if (rsub < rows_per_pass) {

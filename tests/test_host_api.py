@@ -37,7 +37,7 @@ def test_shape_helpers_without_gpu():
     assert L.rnnt_b200_max_tiles(32, 500, 101) == 32 * ((500 * 101 + 127) // 128)
     assert L.rnnt_b200_vocab_tile(4232) == 256 and L.rnnt_b200_vocab_pad(4232) == 4352
     assert L.rnnt_b200_vocab_tile(49) == 64 and L.rnnt_b200_vocab_pad(49) == 64
-    assert L.rnnt_b200_h_pitch(512) == 544
+    assert L.rnnt_b200_h_pitch(512) == 512 and L.rnnt_b200_h_pitch(320) == 352
     # dS pitch: V rounded up to the UMMA N granularity (16), never above the W2 pack
     assert L.rnnt_b200_ds_pitch(4232) == 4288 and L.rnnt_b200_ds_pitch(49) == 64
     assert L.rnnt_b200_ds_pitch(256) == 256 and L.rnnt_b200_ds_pitch(270) == 320
