@@ -7,7 +7,7 @@
  * (model.py:6,59), a third-party C++/CUDA extension that is not in the reference
  * tree; the entry points below are what that extension's FFI would bind for this
  * path. Plain pointers and sizes only: no torch types, no allocation inside, no host
- * synchronisation, every launch on the caller's stream. All pointers are DEVICE
+ * synchronisation, no environment variable read, every launch on the caller's stream. All pointers are DEVICE
  * pointers unless stated. Re-entrant: no global mutable state (the reference's
  * nn.DataParallel, train.py:177, calls from one thread per GPU).
  *
@@ -39,7 +39,7 @@ enum {
   RNNT_B200_E_ALIGN = -4,     /* pointer not aligned as documented               */
   RNNT_B200_E_WORKSPACE = -5, /* workspace too small                             */
   RNNT_B200_E_DRIVER = -6,    /* cuTensorMapEncodeTiled unavailable / failed     */
-  RNNT_B200_E_ARCH = -7       /* device is not sm_100                            */
+  RNNT_B200_E_ARCH = -7       /* current device is not sm_100 (compute capability 10.0) */
 };
 
 int rnnt_b200_version(void);
@@ -96,9 +96,13 @@ int rnnt_b200_planes_to_dlogits(const float* logits, const int32_t* labels,
 int rnnt_b200_max_tiles(int B, int T, int U1);
 
 /* Builds the device tile table from the lengths (no host read-back):
- *   tile_utt[i], tile_cell0[i] for i < n_tiles[0]; also clamped lengths. */
+ *   tile_utt[i], tile_cell0[i] for i < n_tiles[0].
+ * tile_cap = rows the two tables hold (rnnt_b200_max_tiles(B,T,U1), or the exact count when the caller
+ * also has the lengths on the host); writes are bounded by it. n_tiles is TWO int32:
+ *   n_tiles[0] = min(tiles the lengths ask for, tile_cap)   (what every later kernel processes)
+ *   n_tiles[1] = tiles the lengths ask for                  (> tile_cap: the capacity was too small) */
 int rnnt_b200_build_tiles(const int32_t* act_lens, const int32_t* label_lens,
-                          int B, int T, int U1,
+                          int B, int T, int U1, int tile_cap,
                           int32_t* tile_utt, int32_t* tile_cell0, int32_t* n_tiles,
                           void* stream);
 
@@ -162,26 +166,45 @@ int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, const float
                            int B, int T, int U1, int V, int H, int blank, int tile_cap,
                            int tile_lo, int tile_hi, void* ds, void* stream);
 
-/* Fused backward, stage 2: dpre = dh_scale * dh * (1 - h^2) and its two reductions
- *   dP_enc[b,t,:] += sum_u dpre,   dP_dec[b,u,:] += sum_t dpre     (float32, red.global.add)
- * for the packed rows of tiles [tile_lo, tile_hi). dh: bf16 rows (tile_hi-tile_lo)*128, pitch H
- * (the library GEMM dS . W2_bf16). dp_enc (B,T,H) and dp_dec (B,U1,H) must be zeroed by the
- * caller before the first chunk. */
-int rnnt_b200_dh_reduce(const void* dh_bf16, const void* h_stash,
-                        const int32_t* act_lens, const int32_t* label_lens,
-                        int B, int T, int U1, int H, int tile_lo, int tile_hi, float dh_scale,
-                        float* dp_enc, float* dp_dec, void* stream);
+/* Fused backward, stage 2 (the backward of project_layer followed by the backward of tanh, rnnt/model.py:32-35
+ * in reverse) for one staged dS chunk, tiles [tile_lo, tile_hi):
+ *   dpre[row, j] = bf16( (sum_v dS[row, v] * W2_bf16[v, j]) * (1 - h[row, j]^2) )
+ * tcgen05 GEMM (CTA pairs, M = 256 rows, N = H with the dS slice shared by the column halves through the
+ * collector, K = ds_pitch(V)) with the tanh derivative in the epilogue. ds: as written by
+ * rnnt_b200_joint_bwd_ds for the same [tile_lo, tile_hi); w2_bf16: the pack of rnnt_b200_pack_vocab; h_stash and
+ * dpre: (tile_cap*128, H) bf16, 128-byte aligned, rows tile*128 + r (dpre rows outside [tile_lo, tile_hi) are not
+ * touched). H in {128, 256, 512} (rnnt_b200_dh_gemm_supported); other H: the caller forms dpre with library GEMMs. */
+int rnnt_b200_dh_gemm_supported(int H);
+int rnnt_b200_dh_gemm(const void* ds_bf16, const void* w2_bf16, const void* h_stash, int V, int H,
+                      int tile_cap, int tile_lo, int tile_hi, void* dpre_bf16, void* stream);
 
-/* Fused backward, weight/bias gradient of project_layer for one staged dS chunk:
- *   dw2[v, j] += sum_r dS[r, v] * h[r, j]      (v < ds_pitch(V), j < H)      (rnnt/model.py:16,35)
- *   db2[v]    += sum_r dS[r, v]
- * ds: bf16, rows x rnnt_b200_ds_pitch(V), 128-byte aligned; h_rows: the chunk's first row of the h
- * stash (bf16, pitch rnnt_b200_h_pitch(H)); rows a multiple of 64; H in {128, 256, 512}.
- * dw2 (ds_pitch(V), H) and db2 (ds_pitch(V)) float32, zeroed by the caller before the first chunk
- * (split-K partial sums are added with red.global.add). tcgen05 GEMM with both operands MN-major;
- * other H use the library GEMM against the ones column of the stash. */
+/* Fused backward, stage 3: the backward of the broadcast add that replaces the reference's repeat + cat
+ * (rnnt/model.py:26-31), once per step over the whole dpre buffer:
+ *   dP_enc[b,t,:] = sum_u dpre[row(b,t,u), :],   dP_dec[b,u,:] = sum_t dpre[row(b,t,u), :]     (float32)
+ * DETERMINISTIC: no atomics, every sum in a fixed order (two calls give bit-identical results).
+ * dp_enc (B,T,H): rows t >= act_lens[b] are NOT written (zero them once); dp_dec (B,U1,H) is fully written.
+ * scratch: rnnt_b200_dpre_reduce_scratch_elems(B,T,U1,H) floats (per-8-row partial sums of dP_dec). */
+size_t rnnt_b200_dpre_reduce_scratch_elems(int B, int T, int U1, int H);
+int rnnt_b200_dpre_reduce(const void* dpre_bf16, const int32_t* act_lens, const int32_t* label_lens,
+                          int B, int T, int U1, int H, float* scratch, float* dp_enc, float* dp_dec,
+                          void* stream);
+
+/* Fused backward, weight/bias gradient of project_layer for one staged dS chunk (rnnt/model.py:16,35):
+ *   dw2_parts[s][v, j] = sum_{r in K split s} dS[r, v] * h[r, j]      (v < ds_pitch(V), j < H)
+ *   db2_parts[s][v]   += sum_{r in K split s} dS[r, v]
+ * for the s < rnnt_b200_dw2_splits(rows, V, H) K splits of the chunk. dw2_parts (splits, ds_pitch(V), H) float32 is
+ * stored (every element exactly once, no zeroing needed); db2_parts (splits, ds_pitch(V)) float32 must be zeroed
+ * by the caller. The caller adds the partials of all chunks in slot order with rnnt_b200_sum_partials: the
+ * result does not depend on the order in which CTAs finish (DETERMINISTIC).
+ * ds: bf16, rows x rnnt_b200_ds_pitch(V), 128-byte aligned; h_rows: the chunk's first row of the h stash
+ * (bf16, pitch rnnt_b200_h_pitch(H)); rows a multiple of 64; H in {128, 256, 512}. tcgen05 GEMM with both
+ * operands MN-major; other H use the library GEMM against the ones column of the stash. */
+int rnnt_b200_dw2_splits(long long rows, int V, int H);
 int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long long rows, int V, int H,
-                       float* dw2, float* db2, void* stream);
+                       float* dw2_parts, float* db2_parts, void* stream);
+
+/* out[i] = parts[0][i] + parts[1][i] + ... + parts[nparts-1][i], i < n, in that order. */
+int rnnt_b200_sum_partials(const float* parts, int nparts, long long n, float* out, void* stream);
 
 /* Greedy decoding, one frame for B <= 64 utterances at once (replaces the per-utterance, per-frame
  * joint + softmax + argmax + .item() of rnnt/model.py:90-93 / rnnt/search.py):

@@ -91,3 +91,69 @@ def time_cpu_path(E, D, H, V, T, U, n_utts=1, steps=1, warmup=0, seed=2019):
     med = float(np.median(secs))
     return {"value": cells / med, "cells": cells, "seconds": secs, "cores": cores,
             "omp_threads": c_oracle.num_threads()}
+
+
+def make_joint_sample(wl, T_s, cores, seed=2019):
+    """Returns a zero-argument callable: ONE CPU fwd+bwd of the joint + loss path over one utterance of the
+    workload's shape cut to its first ``T_s`` frames (full label length). Used by bench.py's cpu_baseline and
+    ``--impl reference`` legs."""
+    torch.set_num_threads(cores)
+    E, D, H, V, U = wl["E"], wl["D"], wl["H"], wl["V"], wl["U"]
+    gen = torch.Generator().manual_seed(seed)
+    joint = RefJointPort(E + D, H, V)
+    enc = torch.randn(1, T_s, E, generator=gen)
+    dec = torch.randn(1, U + 1, D, generator=gen)
+    labels = torch.randint(1, V, (1, U), generator=gen, dtype=torch.int32)
+    tl = torch.full((1,), T_s, dtype=torch.int32)
+    ul = torch.full((1,), U, dtype=torch.int32)
+    return lambda: cpu_step(joint, enc, dec, labels, tl, ul)
+
+
+class RefTransducerPort(torch.nn.Module):
+    """Port of the reference's assembled model for CPU timing (BASELINE.json configs[3]): encoder
+    rnnt/encoder.py:5-40 (LSTM + output_proj), decoder rnnt/decoder.py:5-44 (embedding, LSTM, output_proj),
+    joint rnnt/model.py:9-37 (materialised logits), loss rnnt/model.py:70 -> oracle/rnnt_oracle.c."""
+
+    def __init__(self, cfg):
+        super().__init__()
+        enc, dec = cfg["enc"], cfg["dec"]
+        self.enc_lstm = torch.nn.LSTM(cfg["feature_dim"], enc["hidden_size"], enc["n_layers"], batch_first=True,
+                                      dropout=cfg["dropout"], bidirectional=enc["bidirectional"])
+        self.enc_proj = torch.nn.Linear((2 if enc["bidirectional"] else 1) * enc["hidden_size"], enc["output_size"])
+        self.embedding = torch.nn.Embedding(cfg["vocab_size"], dec["hidden_size"], padding_idx=0)
+        self.dec_lstm = torch.nn.LSTM(dec["hidden_size"], dec["hidden_size"], dec["n_layers"], batch_first=True)
+        self.dec_proj = torch.nn.Linear(dec["hidden_size"], dec["output_size"])
+        self.joint = RefJointPort(cfg["joint"]["input_size"], cfg["joint"]["inner_size"], cfg["vocab_size"])
+
+    def forward(self, x, y, tl, ul):
+        enc = self.enc_proj(self.enc_lstm(x)[0])
+        ypad = torch.nn.functional.pad(y, pad=(1, 0, 0, 0), value=0)          # model.py:64
+        dec = self.dec_proj(self.dec_lstm(self.embedding(ypad.long()))[0])
+        logits = self.joint(enc, dec)
+        return _CLoss.apply(logits, y.int(), tl, ul).sum() / x.shape[0]
+
+
+def make_train_step_sample(wl, T_s, cores, seed=2019):
+    """As make_joint_sample for the full training step (train.py:24-52: forward, backward, grad-norm clip, SGD)."""
+    torch.set_num_threads(cores)
+    cfg = dict(enc=dict(hidden_size=320, output_size=wl["E"], n_layers=4, bidirectional=True),
+               dec=dict(hidden_size=512, output_size=wl["D"], n_layers=1),
+               joint=dict(input_size=wl["E"] + wl["D"], inner_size=wl["H"]), vocab_size=wl["V"], feature_dim=160,
+               dropout=0.3)                                                   # config/aishell.yaml:21-39
+    torch.manual_seed(seed)
+    model = RefTransducerPort(cfg).train()
+    opt = torch.optim.SGD(model.parameters(), lr=1e-4, momentum=0.9)
+    gen = torch.Generator().manual_seed(seed)
+    x = torch.randn(1, T_s, 160, generator=gen)
+    y = torch.randint(1, wl["V"], (1, wl["U"]), generator=gen)
+    tl = torch.full((1,), T_s, dtype=torch.int32)
+    ul = torch.full((1,), wl["U"], dtype=torch.int32)
+
+    def step():
+        opt.zero_grad()
+        loss = model(x, y, tl, ul)
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 200.0)
+        opt.step()
+        return loss.detach()
+    return step

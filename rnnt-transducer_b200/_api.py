@@ -13,6 +13,7 @@ hand-written sm_100a kernels behind include/rnnt_b200.h. There is no CPU fallbac
 from __future__ import annotations
 
 import os
+import threading
 from typing import Optional
 
 import torch
@@ -48,8 +49,8 @@ class KernelTimer:
     active = None
     # kernels launched per C-ABI call
     KERNELS = {"logits_to_planes": 1, "lattice": 2, "planes_to_dlogits": 1, "build_tiles": 1,
-               "pack_vocab": 1, "joint_hidden": 1, "joint_fwd": 1, "joint_bwd_ds": 1, "dh_reduce": 1,
-               "joint_step_argmax": 1, "dw2_gemm": 1}
+               "pack_vocab": 1, "joint_hidden": 1, "joint_fwd": 1, "joint_bwd_ds": 1, "dh_gemm": 1,
+               "dpre_reduce": 2, "sum_partials": 1, "joint_step_argmax": 1, "dw2_gemm": 1}
 
     def __init__(self, events: bool = True):
         self.events = events
@@ -131,12 +132,16 @@ def _check_loss_args(acts_shape, acts_dtype, acts_device, labels, act_lens, labe
         raise RuntimeError("rnnt_b200 has no CPU path: tensors must live on a CUDA device (sm_100)")
 
 
+def _validate() -> bool:
+    return os.environ.get("RNNT_B200_VALIDATE", "0") == "1"
+
+
 def _check_lens(B, T, U1, labels, act_lens, label_lens):
     if labels.dim() != 2 or labels.shape[0] != B or labels.shape[1] != U1 - 1:
         raise ValueError(f"labels must be (B,U)=({B},{U1 - 1}), got {tuple(labels.shape)}")
     if act_lens.shape != (B,) or label_lens.shape != (B,):
         raise ValueError("act_lens and label_lens must have shape (B,)")
-    if os.environ.get("RNNT_B200_VALIDATE", "0") == "1":  # opt-in: costs a device sync
+    if _validate():  # opt-in: costs a device sync
         if int(act_lens.max()) > T or int(act_lens.min()) < 1:
             raise ValueError("act_lens out of range [1,T]")
         if int(label_lens.max()) > U1 - 1 or int(label_lens.min()) < 0:
@@ -262,9 +267,13 @@ class _JointLossFn(torch.autograd.Function):
             Vpad = L.rnnt_b200_vocab_pad(V)
             tile_utt = torch.empty(max_tiles, dtype=torch.int32, device=dev)
             tile_cell0 = torch.empty(max_tiles, dtype=torch.int32, device=dev)
-            n_tiles = torch.empty(1, dtype=torch.int32, device=dev)
-            _call("build_tiles", L.rnnt_b200_build_tiles, _ptr(act_lens), _ptr(label_lens), B, T, U1, _ptr(tile_utt),
-                                               _ptr(tile_cell0), _ptr(n_tiles), st)
+            n_tiles = torch.empty(2, dtype=torch.int32, device=dev)   # [tiles in the table, tiles the lengths ask for]
+            _call("build_tiles", L.rnnt_b200_build_tiles, _ptr(act_lens), _ptr(label_lens), B, T, U1, max_tiles,
+                  _ptr(tile_utt), _ptr(tile_cell0), _ptr(n_tiles), st)
+            if _validate():   # opt-in (costs a device sync): a host_lens hint that undercounts the device lengths
+                have, need = (int(v) for v in n_tiles.tolist())
+                if need > have:
+                    raise ValueError(f"host_lens gives {max_tiles} tiles but the device lengths need {need}")
             w2q = torch.empty(Vpad, H, dtype=torch.bfloat16, device=dev)
             b2l = torch.empty(Vpad, dtype=torch.float32, device=dev)
             _call("pack_vocab", L.rnnt_b200_pack_vocab, _ptr(w2), _ptr(b2), V, H, _ptr(w2q), _ptr(b2l), st)
@@ -297,22 +306,17 @@ class _JointLossFn(torch.autograd.Function):
         with torch.cuda.device(dev):
             st = _stream()
             scale = grad_out.to(torch.float32).contiguous()
-            dpe = torch.zeros(B, T, H, dtype=torch.float32, device=dev)
-            dpd = torch.zeros(B, U1, H, dtype=torch.float32, device=dev)
+            dpe = torch.zeros(B, T, H, dtype=torch.float32, device=dev)   # rows t >= T_b stay zero
+            dpd = torch.empty(B, U1, H, dtype=torch.float32, device=dev)
             hp = h_stash.shape[1]
-            # dW2/db2: own tcgen05 GEMM (csrc/dw2_gemm.cu) where it covers the shape, else the
-            # library GEMM against the ones column of the stash
+            # dh / dW2 / db2: own tcgen05 GEMMs (csrc/dh_gemm.cu, csrc/dw2_gemm.cu) where they cover the shape,
+            # else library GEMMs (dW2/db2 against the ones column of the stash)
             own_gemm = H in (128, 256, 512)          # the stash has no ones column at these H (pitch == H)
-            if own_gemm:
-                dw2x = torch.zeros(Vds, H, dtype=torch.float32, device=dev)
-                db2x = torch.zeros(Vds, dtype=torch.float32, device=dev)
-            else:
-                dw2x = torch.zeros(hp, Vds, dtype=torch.float32, device=dev)  # [dW2 | db2 | unused rows]^T
             chunk = max(2, min(max_tiles, _DS_BUDGET_BYTES // (128 * Vds * 2)))
             nchunk = -(-max_tiles // chunk)
             chunk = -(-max_tiles // nchunk)          # balanced chunks,
             chunk += chunk & 1                       # whole CTA-pair tiles
-            # whole waves of the persistent backward kernel (one tile per SM and wave): with balanced chunks
+            # whole waves of the persistent backward kernels (one tile per SM and wave): with balanced chunks
             # every launch ends in a partial wave (AISHELL shape: 4 x 21.3 -> 4 x 22 waves); chunks of
             # k * SMs tiles leave one partial wave per step (22 + 22 + 22 + 19.3 -> 86 instead of 88)
             sms = torch.cuda.get_device_properties(dev).multi_processor_count
@@ -320,10 +324,20 @@ class _JointLossFn(torch.autograd.Function):
                 up = -(-chunk // sms) * sms
                 if up * 128 * Vds * 2 <= max(_DS_BUDGET_BYTES, chunk * 128 * Vds * 2):
                     chunk = up
+            bounds = [(lo, min(max_tiles, lo + chunk)) for lo in range(0, max_tiles, chunk)]
             ds = torch.empty(chunk * 128, Vds, dtype=torch.bfloat16, device=dev)
+            # dpre = dh * (1 - h^2), bf16, all M rows (M x H, never M x V): written chunk by chunk, reduced once
+            dpre = torch.empty(max_tiles * 128, H, dtype=torch.bfloat16, device=dev)
+            if own_gemm:
+                # split-K / per-chunk partial results, added in slot order at the end (deterministic)
+                nsplit = [L.rnnt_b200_dw2_splits((hi - lo) * 128, V, H) for lo, hi in bounds]
+                dw2_parts = torch.empty(sum(nsplit), Vds, H, dtype=torch.float32, device=dev)
+                db2_parts = torch.zeros(sum(nsplit), Vds, dtype=torch.float32, device=dev)
+            else:
+                dw2x = torch.zeros(hp, Vds, dtype=torch.float32, device=dev)  # [dW2 | db2 | unused rows]^T
             w2v = w2q[:Vds]                          # rows Vds..Vpad of the pack are padding only
-            for lo in range(0, max_tiles, chunk):
-                hi = min(max_tiles, lo + chunk)
+            slot = 0
+            for ci, (lo, hi) in enumerate(bounds):
                 rows = (hi - lo) * 128
                 dsc = ds[:rows]
                 _call("joint_bwd_ds", L.rnnt_b200_joint_bwd_ds, _ptr(h_stash), _ptr(w2q), _ptr(b2l), _ptr(labels),
@@ -331,38 +345,51 @@ class _JointLossFn(torch.autograd.Function):
                                                     _ptr(tile_cell0), _ptr(n_tiles), _ptr(lse), _ptr(lpb),
                                                     _ptr(lpl), _ptr(cb), _ptr(cl), _ptr(scale), B, T, U1, V, H, blank, max_tiles, lo, hi,
                                                     _ptr(dsc), st)
-                # two plain library GEMMs on the staged bf16 gradient tile (fp32 accumulate/out)
-                with _region("lib_gemm_dh"):
-                    dh = torch.mm(dsc, w2v)                                            # (rows, H) bf16
                 if own_gemm:
+                    _call("dh_gemm", L.rnnt_b200_dh_gemm, _ptr(dsc), _ptr(w2q), _ptr(h_stash), V, H, max_tiles, lo, hi,
+                          _ptr(dpre), st)
                     _call("dw2_gemm", L.rnnt_b200_dw2_gemm, _ptr(dsc), h_stash.data_ptr() + lo * 128 * hp * 2,
-                          rows, V, H, _ptr(dw2x), _ptr(db2x), st)
+                          rows, V, H, dw2_parts.data_ptr() + slot * Vds * H * 4, db2_parts.data_ptr() + slot * Vds * 4, st)
+                    slot += nsplit[ci]
                 else:
-                  with _region("lib_gemm_dw2"):
-                    # K = rows is huge and the output (pitch x Vds) small: split K (batched GEMM;
-                    # measured best, profiles/r01_notes.md). Column H of the stash is 1 for valid
-                    # cells, so row H of the product is db2; the stash pitch (H+32) and this
-                    # orientation (h^T . dS) are the fastest of the shapes the library was tried
-                    # with (tools/dw2_gemm_bench.py). Rows H+8.. of the product are never read.
                     hc = h_stash[lo * 128: hi * 128]
-                    dw2x += torch.bmm(hc.view(_SPLIT_K, rows // _SPLIT_K, hp).transpose(1, 2),
-                                      dsc.view(_SPLIT_K, rows // _SPLIT_K, Vds),
-                                      out_dtype=torch.float32).sum(0)
-                _call("dh_reduce", L.rnnt_b200_dh_reduce, _ptr(dh), _ptr(h_stash), _ptr(act_lens), _ptr(label_lens),
-                      B, T, U1, H, lo, hi, 1.0, _ptr(dpe), _ptr(dpd), st)
+                    with _region("lib_gemm_dh"):
+                        dh = torch.mm(dsc, w2v)                                        # (rows, H) bf16
+                        hf = hc[:, :H].float()
+                        dpre[lo * 128: hi * 128] = (dh.float() * (1.0 - hf * hf)).to(torch.bfloat16)
+                    with _region("lib_gemm_dw2"):
+                        # K = rows is huge and the output (pitch x Vds) small: split K (batched GEMM;
+                        # measured best, profiles/r01_notes.md). Column H of the stash is 1 for valid
+                        # cells, so row H of the product is db2; the stash pitch (H+32) and this
+                        # orientation (h^T . dS) are the fastest of the shapes the library was tried
+                        # with (tools/dw2_gemm_bench.py). Rows H+8.. of the product are never read.
+                        dw2x += torch.bmm(hc.view(_SPLIT_K, rows // _SPLIT_K, hp).transpose(1, 2),
+                                          dsc.view(_SPLIT_K, rows // _SPLIT_K, Vds),
+                                          out_dtype=torch.float32).sum(0)
+            scratch = torch.empty(L.rnnt_b200_dpre_reduce_scratch_elems(B, T, U1, H), dtype=torch.float32, device=dev)
+            _call("dpre_reduce", L.rnnt_b200_dpre_reduce, _ptr(dpre), _ptr(act_lens), _ptr(label_lens), B, T, U1, H,
+                  _ptr(scratch), _ptr(dpe), _ptr(dpd), st)
             if own_gemm:
-                dw2, db2 = dw2x[:V].contiguous(), db2x[:V].contiguous()
+                dw2f = torch.empty(Vds, H, dtype=torch.float32, device=dev)
+                db2f = torch.empty(Vds, dtype=torch.float32, device=dev)
+                _call("sum_partials", L.rnnt_b200_sum_partials, _ptr(dw2_parts), sum(nsplit), Vds * H, _ptr(dw2f), st)
+                _call("sum_partials", L.rnnt_b200_sum_partials, _ptr(db2_parts), sum(nsplit), Vds, _ptr(db2f), st)
+                dw2, db2 = dw2f[:V], db2f[:V]
             else:
                 dw2 = dw2x[:H, :V].t().contiguous()
                 db2 = dw2x[H, :V].contiguous()
         return dpe, dpd, dw2, db2, None, None, None, None, None
 
 
-def _tile_count(host_lens) -> Optional[int]:
+def _tile_count(host_lens, T: int, U1: int) -> Optional[int]:
+    """Exact tile count from host-side lengths, with the clamps the device applies (t in [1,T], u in [0,U1-1])."""
     if host_lens is None:
         return None
     tl, ul = host_lens
-    return int(sum((int(t) * (int(u) + 1) + 127) // 128 for t, u in zip(tl, ul)))
+    return int(sum((min(max(int(t), 1), T) * (min(max(int(u), 0), U1 - 1) + 1) + 127) // 128 for t, u in zip(tl, ul)))
+
+
+_tf32_lock = threading.Lock()
 
 
 class _FirstLayer(torch.autograd.Function):
@@ -383,15 +410,18 @@ class _FirstLayer(torch.autograd.Function):
         x, w = ctx.saved_tensors
         g2 = g.reshape(-1, g.shape[-1])
         gx = gw = gb = None
-        prev = torch.backends.cuda.matmul.allow_tf32
-        torch.backends.cuda.matmul.allow_tf32 = os.environ.get("RNNT_B200_TF32_BWD", "1") != "0"
-        try:
-            if ctx.needs_input_grad[0]:
-                gx = torch.matmul(g2, w).reshape(x.shape)
-            if ctx.needs_input_grad[1]:
-                gw = torch.matmul(g2.t(), x.reshape(-1, x.shape[-1]))
-        finally:
-            torch.backends.cuda.matmul.allow_tf32 = prev
+        # the precision switch is process-global in torch: held under a lock so that two backward passes (autograd
+        # runs one worker thread per device) cannot interleave their save/restore ("Numerics")
+        with _tf32_lock:
+            prev = torch.backends.cuda.matmul.allow_tf32
+            torch.backends.cuda.matmul.allow_tf32 = os.environ.get("RNNT_B200_TF32_BWD", "1") != "0"
+            try:
+                if ctx.needs_input_grad[0]:
+                    gx = torch.matmul(g2, w).reshape(x.shape)
+                if ctx.needs_input_grad[1]:
+                    gw = torch.matmul(g2.t(), x.reshape(-1, x.shape[-1]))
+            finally:
+                torch.backends.cuda.matmul.allow_tf32 = prev
         if ctx.has_bias and ctx.needs_input_grad[2]:
             gb = g2.sum(0)
         return gx, gw, gb
@@ -431,7 +461,7 @@ def joint_rnnt_loss(enc_state, dec_state, w1, b1, w2, b2, labels, act_lens, labe
     pe = _FirstLayer.apply(enc_state, w1[:, :E], b1).contiguous()
     pd = _FirstLayer.apply(dec_state, w1[:, E:], None).contiguous()
     loss_b = _JointLossFn.apply(pe, pd, w2.contiguous(), b2.contiguous(), labels, act_lens, label_lens,
-                                int(blank), _tile_count(host_lens))
+                                int(blank), _tile_count(host_lens, T, U1))
     return _reduce(loss_b, reduction)
 
 

@@ -26,7 +26,7 @@ SIGNATURES = {
     "rnnt_b200_lattice": (_i, [_p, _p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p]),
     "rnnt_b200_planes_to_dlogits": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p]),
     "rnnt_b200_max_tiles": (_i, [_i, _i, _i]),
-    "rnnt_b200_build_tiles": (_i, [_p, _p, _i, _i, _i, _p, _p, _p, _p]),
+    "rnnt_b200_build_tiles": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p, _p]),
     "rnnt_b200_vocab_pad": (_i, [_i]),
     "rnnt_b200_vocab_tile": (_i, [_i]),
     "rnnt_b200_pack_vocab": (_i, [_p, _p, _i, _i, _p, _p, _p]),
@@ -36,9 +36,14 @@ SIGNATURES = {
     "rnnt_b200_joint_fwd": (_i, [_p] * 9 + [_i] * 7 + [_p] * 4),
     "rnnt_b200_joint_bwd_ds": (_i, [_p] * 15 + [_i] * 9 + [_p, _p]),
     "rnnt_b200_joint_step_argmax": (_i, [_p, ctypes.c_longlong, _p, _p, _p, _i, _i, _i, _p, _p, _p]),
+    "rnnt_b200_dw2_splits": (_i, [ctypes.c_longlong, _i, _i]),
     "rnnt_b200_dw2_gemm": (_i, [_p, _p, ctypes.c_longlong, _i, _i, _p, _p, _p]),
+    "rnnt_b200_sum_partials": (_i, [_p, _i, ctypes.c_longlong, _p, _p]),
+    "rnnt_b200_dh_gemm_supported": (_i, [_i]),
+    "rnnt_b200_dh_gemm": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _p, _p]),
+    "rnnt_b200_dpre_reduce_scratch_elems": (ctypes.c_size_t, [_i, _i, _i, _i]),
+    "rnnt_b200_dpre_reduce": (_i, [_p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p]),
     "rnnt_b200_features_batch": (_i, [_p] * 5 + [_i] * 4 + [_p, _p, _i, _i, _p, _p]),
-    "rnnt_b200_dh_reduce": (_i, [_p] * 4 + [_i] * 6 + [ctypes.c_float] + [_p, _p, _p]),
     "rnnt_b200_selftest_gemm": (_i, [_p, _p, _p, _i, _i, _i, _p]),
     "rnnt_b200_selftest_gemm_ts": (_i, [_p, _p, _p, _i, _i, _i, _i, _p]),
 }

@@ -9,11 +9,39 @@
 #define RNNT_LN2 0.6931471805599453f
 #define RNNT_NEG_BIG (-1.0e30f)    // bias of padded vocabulary columns (log2 domain)
 
+// Timing-experiment knobs (environment variables, clock64 traces) exist only in the -DRNNT_B200_TUNE build
+// (`make tune` -> librnnt_b200_tune.so, loaded through RNNT_B200_LIB by tools/). The release library reads no
+// environment variable, allocates nothing and never synchronises inside an entry point.
+#ifdef RNNT_B200_TUNE
+#include <stdlib.h>
+static inline int rnnt_tune_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e ? atoi(e) : dflt;
+}
+#else
+#define rnnt_tune_int(name, dflt) (dflt)
+#endif
+
 #define RNNT_CUDA_RETURN_IF_ERROR()                        \
   do {                                                     \
     cudaError_t e__ = cudaGetLastError();                  \
     if (e__ != cudaSuccess) return (int)e__;               \
   } while (0)
+
+// RNNT_B200_E_ARCH unless the current device is sm_100 (the kernels are compiled for sm_100a only).
+static inline int rnnt_check_arch() {
+  static int cached[64];  // 0 = not looked at yet, 1 = sm_100, -1 = something else (benign race: same value)
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return RNNT_B200_E_ARCH;
+  if (dev >= 0 && dev < 64 && cached[dev]) return cached[dev] > 0 ? RNNT_B200_OK : RNNT_B200_E_ARCH;
+  int major = 0, minor = 0;
+  if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess ||
+      cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev) != cudaSuccess)
+    return RNNT_B200_E_ARCH;
+  const int ok = (major == 10 && minor == 0) ? 1 : -1;
+  if (dev >= 0 && dev < 64) cached[dev] = ok;
+  return ok > 0 ? RNNT_B200_OK : RNNT_B200_E_ARCH;
+}
 
 // Row pitch (elements) of the tile-packed bf16 hidden-activation stash. H = 128, 256, 512 (the shapes the
 // own dW2 GEMM covers, which sums db2 itself): H, rows of whole 128-byte lines. Other H: H + 32 with the

@@ -321,6 +321,7 @@ extern "C" int rnnt_b200_logits_to_planes(const float* logits, const int32_t* la
   if (B <= 0 || T <= 0 || U1 <= 0 || V <= 0) return RNNT_B200_E_SHAPE;
   if (blank < 0 || blank >= V) return RNNT_B200_E_BLANK;
   if ((V & 3) == 0 && ((uintptr_t)logits & 15)) return RNNT_B200_E_ALIGN;
+  if (const int arch = rnnt_check_arch()) return arch;
   const long long ncell = (long long)B * T * U1;
   if (V <= 256 && ncell < 0x7fffffffLL) {  // several cells per warp
     const FastDiv dTU = make_fastdiv((uint32_t)T * (uint32_t)U1), dU1 = make_fastdiv((uint32_t)U1);
@@ -349,6 +350,7 @@ extern "C" int rnnt_b200_planes_to_dlogits(const float* logits, const int32_t* l
   if (B <= 0 || T <= 0 || U1 <= 0 || V <= 0) return RNNT_B200_E_SHAPE;
   if (blank < 0 || blank >= V) return RNNT_B200_E_BLANK;
   if ((V & 3) == 0 && (((uintptr_t)logits & 15) || ((uintptr_t)dlogits & 15))) return RNNT_B200_E_ALIGN;
+  if (const int arch = rnnt_check_arch()) return arch;
   const long long ncell = (long long)B * T * U1;
   if (V <= 256 && ncell < 0x7fffffffLL) {  // several cells per warp
     const FastDiv dTU = make_fastdiv((uint32_t)T * (uint32_t)U1), dU1 = make_fastdiv((uint32_t)U1);

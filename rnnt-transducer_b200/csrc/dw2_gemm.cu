@@ -19,7 +19,6 @@
 // dS^T slice, db2 by the epilogue warps); dw2_gemm_kernel serves H = 128 and 256 and the A/B switch.
 #include <cuda.h>
 #include <cuda_bf16.h>
-#include <stdlib.h>
 #include "common.cuh"
 #include "sm100_ptx.cuh"
 #include "tma_host.cuh"
@@ -41,8 +40,8 @@ struct GwCtl {
 };
 
 struct GwParams {
-  float* dw2;      // (Vds, H) fp32, accumulated
-  float* db2;      // (Vds) fp32, accumulated
+  float* dw2;      // partial s at dw2 + s * Vds * H: (Vds, H) fp32, every element stored exactly once
+  float* db2;      // partial s at db2 + s * Vds: (Vds) fp32 (dw2_gemm_kernel adds into it: zeroed by the caller)
   int Vds, H;
   int nvt, nj;     // vocabulary tiles of 256, column units of N
   int N;           // UMMA N of a unit: 256 (H a multiple of 256) or 128 (H = 128)
@@ -50,20 +49,6 @@ struct GwParams {
   int splits, ks_per_split;
   int debug;  // RNNT_B200_DW2_DEBUG (timing experiments): 1 no ones-MMA, 2 no main MMA, 4 no epilogue adds, 8 no TMA loads, 16 no A reuse through the collector
 };
-
-// MN-major operand, SWIZZLE_128B (see the header comment); version 1 = sm_100.
-__device__ __forceinline__ uint64_t umma_desc_mn128(uint32_t saddr, uint32_t lbo_bytes) {
-  uint64_t d = 0;
-  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
-  d |= (uint64_t)(lbo_bytes >> 4) << 16;
-  d |= (uint64_t)(1024 >> 4) << 32;
-  d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
-  return d;
-}
-__host__ __device__ constexpr uint32_t umma_idesc_bf16_mn(int M, int N) {
-  return umma_idesc_bf16(M, N) | (1u << 15) | (1u << 16);  // a_major = b_major = MN
-}
 
 __global__ void __launch_bounds__(GW_THREADS, 1)
 dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constant__ CUtensorMap map_h,
@@ -198,7 +183,7 @@ dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
         mbar_wait(&ctl->acc_full, it & 1);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-        float* dst = p.dw2 + (size_t)v * p.H + jh * p.N;
+        float* dst = p.dw2 + ((size_t)s * p.Vds + v) * p.H + jh * p.N;
 #pragma unroll 1
         for (int c = 0; c < p.N / 16; ++c) {
           float z[16];
@@ -207,15 +192,16 @@ dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
           if (v < p.Vds && !(p.debug & 4)) {
 #pragma unroll
             for (int i = 0; i < 4; ++i)
-              atomicAdd(reinterpret_cast<float4*>(dst + c * 16) + i,
-                        make_float4(z[4 * i], z[4 * i + 1], z[4 * i + 2], z[4 * i + 3]));
+              reinterpret_cast<float4*>(dst + c * 16)[i] = make_float4(z[4 * i], z[4 * i + 1], z[4 * i + 2], z[4 * i + 3]);
           }
         }
         if (has_ones) {
+          // at most two adds per element of a partial (the two column halves of H, by K-block parity) onto the
+          // caller's zeros: commutative, hence deterministic
           float z[16];
           tmem_ld_32x16(taddr + 256, z);
           tmem_ld_wait();
-          if (v < p.Vds) atomicAdd(p.db2 + v, z[0]);
+          if (v < p.Vds) atomicAdd(p.db2 + (size_t)s * p.Vds + v, z[0]);
         }
       }
       tc_fence_before();
@@ -242,7 +228,8 @@ dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
 // ---------------------------------------------------------------------------------------
 constexpr int GWW_STAGES = 4;
 constexpr int GWW_STAGE = 6 * GW_BLOCK;  // A: 2 boxes (128 v), B: 4 boxes (2 x 128 j)
-constexpr int GWW_SMEM = GWW_STAGES * GWW_STAGE + 256;
+constexpr int GWW_CS = 128 * 8 * 4;      // column-sum exchange of the four epilogue warps
+constexpr int GWW_SMEM = GWW_STAGES * GWW_STAGE + GWW_CS + 256;
 
 struct GwwCtl {
   uint64_t full[GWW_STAGES], mma_done[GWW_STAGES], empty[GWW_STAGES], acc_full, acc_empty;
@@ -254,7 +241,8 @@ dw2_wide_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
                 const GwParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
-  GwwCtl* ctl = reinterpret_cast<GwwCtl*>(smem + GWW_STAGES * GWW_STAGE);
+  float* cs_x = reinterpret_cast<float*>(smem + GWW_STAGES * GWW_STAGE);
+  GwwCtl* ctl = reinterpret_cast<GwwCtl*>(smem + GWW_STAGES * GWW_STAGE + GWW_CS);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const int cid = blockIdx.x >> 1, ncl = gridDim.x >> 1;
@@ -382,17 +370,24 @@ dw2_wide_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
         if (++stage == GWW_STAGES) { stage = 0; phase ^= 1; }
       }
       {
-        const int v = vt * 256 + (int)rank * 128 + chunk * 8;
+        // the eight row groups' sums of a column meet in shared memory and are added in row-group order
+        // (deterministic); thread tid then owns column tid of this CTA's 128
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (v + j < p.Vds) atomicAdd(p.db2 + v + j, cs[j]);
+        for (int j = 0; j < 8; ++j) cs_x[rg * 128 + chunk * 8 + j] = cs[j];
+        named_bar_sync(1, 128);
+        float a = cs_x[tid];
+#pragma unroll
+        for (int r = 1; r < 8; ++r) a += cs_x[r * 128 + tid];
+        const int v = vt * 256 + (int)rank * 128 + tid;
+        if (v < p.Vds) p.db2[(size_t)s * p.Vds + v] = a;
+        named_bar_sync(1, 128);  // cs_x is free again
       }
-      // ---- accumulators -> dW2 ----
+      // ---- accumulators -> this split's partial of dW2 ----
       const int v = vt * 256 + (int)rank * 128 + q * 32 + lane;
       mbar_wait(&ctl->acc_full, it & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-      float* dst = p.dw2 + (size_t)v * p.H;
+      float* dst = p.dw2 + ((size_t)s * p.Vds + v) * p.H;
 #pragma unroll 1
       for (int c = 0; c < 512 / 16; ++c) {
         float z[16];
@@ -401,8 +396,7 @@ dw2_wide_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
         if (v < p.Vds && !(p.debug & 4)) {
 #pragma unroll
           for (int i = 0; i < 4; ++i)
-            atomicAdd(reinterpret_cast<float4*>(dst + c * 16) + i,
-                      make_float4(z[4 * i], z[4 * i + 1], z[4 * i + 2], z[4 * i + 3]));
+            reinterpret_cast<float4*>(dst + c * 16)[i] = make_float4(z[4 * i], z[4 * i + 1], z[4 * i + 2], z[4 * i + 3]);
         }
       }
       tc_fence_before();
@@ -418,52 +412,66 @@ dw2_wide_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
 
 }  // namespace
 
+// K splits of one chunk: one wave of (split, vocabulary tile[, column half]) units over the CTA pairs.
+// splits = pairs / units-per-split leaves 6 of the 74 pairs idle at the AISHELL shape (68 units). Filling them
+// (13 splits = 442 units = 5.97 waves) made this kernel 3 % faster inside the step and the step no faster
+// (24.7 / 25.1 against 24.3 / 24.8 ms in the same call): the chip sits at its power cap, the extra SMs only
+// lower the clock of everything else; alone, 1.455 against 1.431 ms.
+struct GwSplit { int splits, ks_per_split; bool wide; };
+static GwSplit gw_split(long long rows, int V, int H) {
+  GwSplit g;
+  g.wide = (H == 512) && rnnt_tune_int("RNNT_B200_DW2_WIDE", 1) != 0;  // the 256 x 256 kernel at H = 512: A/B only
+  const int Vds = rnnt_b200_ds_pitch(V);
+  const int nvt = (Vds + 255) / 256;
+  const int nj = g.wide ? 1 : H / (H >= 256 ? 256 : 128);
+  const int ksteps = (int)(rows / 64);
+  int sw = (sm_count() / 2) / (nvt * nj);
+  if (sw < 1) sw = 1;
+  { const int e = rnnt_tune_int("RNNT_B200_DW2_SPLITS", 0); if (e >= 1) sw = e; }
+  if (sw > ksteps) sw = ksteps;
+  if (sw < 1) sw = 1;
+  g.ks_per_split = (ksteps + sw - 1) / sw;
+  if (g.ks_per_split < 1) g.ks_per_split = 1;
+  g.splits = (ksteps + g.ks_per_split - 1) / g.ks_per_split;  // every unit has K blocks
+  if (g.splits < 1) g.splits = 1;
+  return g;
+}
+
+extern "C" int rnnt_b200_dw2_splits(long long rows, int V, int H) {
+  if (rows <= 0 || (rows & 63) || V <= 0 || !(H == 128 || H == 256 || H == 512)) return 0;
+  return gw_split(rows, V, H).splits;
+}
+
 extern "C" int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long long rows, int V, int H,
-                                  float* dw2, float* db2, void* stream) {
-  if (!ds_bf16 || !h_rows || !dw2 || !db2) return RNNT_B200_E_NULL;
+                                  float* dw2_parts, float* db2_parts, void* stream) {
+  if (!ds_bf16 || !h_rows || !dw2_parts || !db2_parts) return RNNT_B200_E_NULL;
   if (rows < 0 || (rows & 63) || V <= 0 || !(H == 128 || H == 256 || H == 512)) return RNNT_B200_E_SHAPE;
   if ((reinterpret_cast<uintptr_t>(ds_bf16) & 127u) || (reinterpret_cast<uintptr_t>(h_rows) & 15u) ||
-      (reinterpret_cast<uintptr_t>(dw2) & 15u))
+      (reinterpret_cast<uintptr_t>(dw2_parts) & 15u))
     return RNNT_B200_E_ALIGN;
   if (rows == 0) return RNNT_B200_OK;
+  int rc = rnnt_check_arch();
+  if (rc != RNNT_B200_OK) return rc;
   const int Vds = rnnt_b200_ds_pitch(V);
   CUtensorMap mds, mh;
-  int rc = make_map_bf16(&mds, ds_bf16, (uint64_t)rows, (uint64_t)Vds, (uint64_t)Vds, 64, 64,
-                         CU_TENSOR_MAP_SWIZZLE_128B);
+  rc = make_map_bf16(&mds, ds_bf16, (uint64_t)rows, (uint64_t)Vds, (uint64_t)Vds, 64, 64,
+                     CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc != RNNT_B200_OK) return rc;
   rc = make_map_bf16(&mh, h_rows, (uint64_t)rows, (uint64_t)H, (uint64_t)rnnt_hp(H), 64, 64,
                      CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc != RNNT_B200_OK) return rc;
+  const GwSplit g = gw_split(rows, V, H);
   GwParams p;
-  p.dw2 = dw2; p.db2 = db2; p.Vds = Vds; p.H = H;
+  p.dw2 = dw2_parts; p.db2 = db2_parts; p.Vds = Vds; p.H = H;
   p.nvt = (Vds + 255) / 256;
   p.N = H >= 256 ? 256 : 128;
   p.nj = H / p.N;
   p.ksteps = (int)(rows / 64);
+  p.splits = g.splits;
+  p.ks_per_split = g.ks_per_split;
+  p.debug = rnnt_tune_int("RNNT_B200_DW2_DEBUG", 0);
+  const bool wide = g.wide;
   const int pairs = sm_count() / 2;
-  // One wave of units: splits = pairs / (nvt * nj) leaves 6 of the 74 pairs idle at the AISHELL shape
-  // (68 units). Filling them (13 splits = 442 units = 5.97 waves) made this kernel 3 % faster inside the
-  // step and the step no faster (24.7 / 25.1 against 24.3 / 24.8 ms in the same call): the chip sits at its
-  // power cap, the extra SMs only lower the clock of everything else; alone, 1.455 against 1.431 ms.
-  int splits = pairs / (p.nvt * p.nj);
-  if (splits < 1) splits = 1;
-  if (const char* e = getenv("RNNT_B200_DW2_SPLITS")) {  // timing experiments only
-    if (atoi(e) >= 1) splits = atoi(e);
-  }
-  if (splits > p.ksteps) splits = p.ksteps;
-  p.ks_per_split = (p.ksteps + splits - 1) / splits;
-  p.splits = (p.ksteps + p.ks_per_split - 1) / p.ks_per_split;  // every unit has K blocks
-  { const char* d = getenv("RNNT_B200_DW2_DEBUG"); p.debug = d ? atoi(d) : 0; }
-  bool wide = (H == 512);
-  { const char* w = getenv("RNNT_B200_DW2_WIDE"); if (w && atoi(w) == 0) wide = false; }  // A/B only
-  if (wide) {  // units are (split, tile): recompute the split for nvt units per split
-    int sw = pairs / p.nvt;
-    if (sw < 1) sw = 1;
-    if (const char* e = getenv("RNNT_B200_DW2_SPLITS")) { if (atoi(e) >= 1) sw = atoi(e); }
-    if (sw > p.ksteps) sw = p.ksteps;
-    p.ks_per_split = (p.ksteps + sw - 1) / sw;
-    p.splits = (p.ksteps + p.ks_per_split - 1) / p.ks_per_split;
-  }
   const int units = wide ? p.splits * p.nvt : p.splits * p.nvt * p.nj;
   const int grid = 2 * (units < pairs ? units : pairs);
   cudaError_t e = wide ? cudaFuncSetAttribute(dw2_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GWW_SMEM)

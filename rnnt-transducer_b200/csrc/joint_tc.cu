@@ -32,7 +32,6 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <stdio.h>
-#include <stdlib.h>
 #include <type_traits>
 #include "common.cuh"
 #include "sm100_ptx.cuh"
@@ -40,6 +39,15 @@
 
 
 using namespace sm100;
+
+// clock64 traces and the debug knock-outs exist only in the tuning build (common.cuh)
+#ifdef RNNT_B200_TUNE
+#define RNNT_TRACING(p) ((p).trace != nullptr)
+#define RNNT_DBG(p) ((p).debug)
+#else
+#define RNNT_TRACING(p) false
+#define RNNT_DBG(p) 0
+#endif
 
 namespace {
 
@@ -291,10 +299,10 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       for (int vi = 0; vi < NV; ++vi, ++acc_it) {
         const int vt = (vi + cid) % NV;
         const uint32_t buf = V2 ? acc_buf : (acc_it & 1);
-        const long long tr0 = p.trace ? clock64() : 0;
+        const long long tr0 = RNNT_TRACING(p) ? clock64() : 0;
         mbar_wait(&ctl->acc_full[buf], V2 ? acc_par : ((acc_it >> 1) & 1));
         if (V2 && ++acc_buf == (uint32_t)p.nacc) { acc_buf = 0; acc_par ^= 1; }
-        const long long tr1 = p.trace ? clock64() : 0;
+        const long long tr1 = RNNT_TRACING(p) ? clock64() : 0;
         tc_fence_after();
         if (bias_loader) {  // next tile's slice -> the buffer nobody reads during this tile
           reinterpret_cast<float4*>(bias_h + ((acc_it + 1) & 1) * HALF)[lane] = bias_next;
@@ -306,7 +314,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         // columns of this tile that belong to this warp's half (the last tile is narrower; the
         // UMMA N granularity makes every chunk a full 16 columns)
         const int ncol = min(HALF, max(0, ((vt == NV - 1) ? n_last : BN) - half * HALF));
-        const int nch = (p.debug & 1) ? 0 : ncol >> 4;
+        const int nch = (RNNT_DBG(p) & 1) ? 0 : ncol >> 4;
         const int colbase = vt * BN + half * HALF;
         auto release_acc = [&]() {
           tc_fence_before();
@@ -400,7 +408,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
               }
               fence_proxy_async_smem();
               __syncwarp();
-              if (lane == 0 && !dead && !(p.debug & 16)) {
+              if (lane == 0 && !dead && !(RNNT_DBG(p) & 16)) {
                 tma_store_2d(&map_ds, stage_w, cbase, (tile - p.tile_lo) * RNNT_TILE_M + q * 32);
                 bulk_commit_group();
               }
@@ -445,7 +453,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
           }
         }
         named_bar_sync(2 + half, 128);  // bias ring hand-over (see above)
-        if (p.trace && blockIdx.x == p.trace_cta && threadIdx.x == 0 && acc_it < 4096) {
+        if (RNNT_TRACING(p) && blockIdx.x == p.trace_cta && threadIdx.x == 0 && acc_it < 4096) {
           long long* t = p.trace + 6 * 4096;
           t[3 * acc_it + 0] = tr0; t[3 * acc_it + 1] = tr1; t[3 * acc_it + 2] = clock64();
         }
@@ -494,16 +502,16 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       int tr_n = 0;
       while (pt < n_pairs) {
         const int row0 = vt * BN + (int)rank * (((vt == NV - 1) ? n_last : BN) / 2);
-        const long long tr0 = p.trace ? clock64() : 0;
+        const long long tr0 = RNNT_TRACING(p) ? clock64() : 0;
         mbar_wait(&ctl->b_empty[slot], phase ^ 1);
-        const long long tr1 = p.trace ? clock64() : 0;
+        const long long tr1 = RNNT_TRACING(p) ? clock64() : 0;
         const uint32_t full = mapa_u32(smem_u32(&ctl->b_full[slot]), 0);
         if (rank == 0) mbar_arrive_expect_tx(&ctl->b_full[slot], 2 * kSlotBytes);
         else mbar_arrive_cluster(full);
 #pragma unroll
         for (int j = 0; j < KSLOT; ++j)
           tma_load_2d_pair(smem_b + slot * kSlotBytes + j * kSubBytes, &map_w2, full, (kb + j) * kKBlock, row0);
-        if (p.trace && blockIdx.x == p.trace_cta && parity == 0 && tr_n < 4096) {
+        if (RNNT_TRACING(p) && blockIdx.x == p.trace_cta && parity == 0 && tr_n < 4096) {
           long long* t = p.trace + 3 * 4096;
           t[3 * tr_n + 0] = tr0; t[3 * tr_n + 1] = tr1; t[3 * tr_n + 2] = clock64();
           ++tr_n;
@@ -547,7 +555,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       (void)tmem_a;
       int it = 0, tr_n = 0;
       const uint32_t a0 = smem_u32(smem_a), b0 = smem_u32(smem_b);
-      const bool tracing = p.trace != nullptr && blockIdx.x == p.trace_cta;
+      const bool tracing = RNNT_TRACING(p) && blockIdx.x == p.trace_cta;
       for (int pt = cid; pt < n_pairs; pt += ncl, ++it) {
         for (int vi = 0; vi < NV; ++vi, ++acc_it) {
           const int vt = (vi + cid) % NV;  // same rotated order as the producer and the epilogue
@@ -575,7 +583,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
             if (elect_one_sync()) {
               for (int sub = 0; sub < KSUB; ++sub) {
                 const uint32_t sl = sub ? s1 : s0;
-                if (!(p.debug & 4)) {
+                if (!(RNNT_DBG(p) & 4)) {
 #pragma unroll
                   for (int j = 0; j < KSLOT; ++j) {
                     const int kb = (ks * KSUB + sub) * KSLOT + j;
@@ -804,13 +812,11 @@ int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap
   // read through L1 (very large vocabularies)
   constexpr int kslot = V2 ? 2 : 1;
   p.slots = pick_slots(p.H, BN, MODE, kslot);
+  p.debug = rnnt_tune_int("RNNT_B200_DEBUG", 0);
+  if (rnnt_tune_int("RNNT_B200_DEBUG_MODE", MODE) != MODE) p.debug = 0;
   {
-    const char* dbg = getenv("RNNT_B200_DEBUG");
-    p.debug = dbg ? atoi(dbg) : 0;
-    const char* dm = getenv("RNNT_B200_DEBUG_MODE");
-    if (dm && atoi(dm) != MODE) p.debug = 0;
-    const char* stg = getenv("RNNT_B200_SLOTS");
-    if (stg && atoi(stg) >= 2 && atoi(stg) < p.slots) p.slots = atoi(stg);
+    const int stg = rnnt_tune_int("RNNT_B200_SLOTS", 0);
+    if (stg >= 2 && stg < p.slots) p.slots = stg;
   }
   const int smem = smem_bytes_for(p.H, BN, p.slots, MODE, kslot);
   if (smem > kSmemLimit) return RNNT_B200_E_SHAPE;
@@ -821,8 +827,8 @@ int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap
   if (ntile < 1) return RNNT_B200_OK;
   if (grid > ((ntile + 1) & ~1)) grid = (ntile + 1) & ~1;
   {
-    const char* g = getenv("RNNT_B200_GRID");  // timing experiments only
-    if (g && atoi(g) >= 2 && atoi(g) < grid) grid = atoi(g) & ~1;
+    const int g = rnnt_tune_int("RNNT_B200_GRID", 0);  // timing experiments only
+    if (g >= 2 && g < grid) grid = g & ~1;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
@@ -836,21 +842,22 @@ int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  const char* trace_path = getenv("RNNT_B200_TRACE");  // debug only: synchronises and writes a file
-  const char* trace_mode = getenv("RNNT_B200_DEBUG_MODE");
-  if (trace_path && trace_mode && atoi(trace_mode) != MODE) trace_path = nullptr;
   p.trace = nullptr;
-  {
-    const char* tc = getenv("RNNT_B200_TRACE_CTA");
-    p.trace_cta = tc ? atoi(tc) : 0;
-  }
+  p.trace_cta = 0;
+#ifdef RNNT_B200_TUNE
+  // tuning build only: clock64 stamps of one CTA, written to a file -- allocates and synchronises
+  const char* trace_path = getenv("RNNT_B200_TRACE");
+  if (trace_path && rnnt_tune_int("RNNT_B200_DEBUG_MODE", MODE) != MODE) trace_path = nullptr;
+  p.trace_cta = rnnt_tune_int("RNNT_B200_TRACE_CTA", 0);
   const size_t trace_bytes = 9 * 4096 * sizeof(long long);
   if (trace_path) {
     if (cudaMalloc(&p.trace, trace_bytes) != cudaSuccess) p.trace = nullptr;
     else cudaMemsetAsync(p.trace, 0, trace_bytes, st);
   }
+#endif
   e = cudaLaunchKernelEx(&cfg, joint_kernel<BN, MODE, V2>, mw, mh, md, p);
   if (e != cudaSuccess) return (int)e;
+#ifdef RNNT_B200_TUNE
   if (p.trace) {
     long long* host = (long long*)malloc(trace_bytes);
     cudaStreamSynchronize(st);
@@ -860,24 +867,31 @@ int launch_joint(const CUtensorMap& mw, const CUtensorMap& mh, const CUtensorMap
     free(host);
     cudaFree(p.trace);
   }
+#endif
   RNNT_CUDA_RETURN_IF_ERROR();
   return RNNT_B200_OK;
 }
 
 template <int MODE>
 int dispatch_joint(JointParams& p, const void* w2q, const void* h_stash, int max_tiles, cudaStream_t st) {
+  {
+    const int arch = rnnt_check_arch();
+    if (arch != RNNT_B200_OK) return arch;
+  }
   int BN = rnnt_b200_vocab_tile(p.V);
   p.kts = 0; p.nacc = 2;
   bool v2 = false;
+#ifdef RNNT_B200_TUNE
   if (MODE == 1 && BN == 256 && p.H % 128 == 0) {  // experiment: A operand (partly) from TMEM, 128-column tiles
-    const char* e = getenv("RNNT_B200_V2");
-    if (e && atoi(e) >= 0) {
+    const int e = rnnt_tune_int("RNNT_B200_V2", -1);
+    if (e >= 0) {
       v2 = true;
       BN = 128;
-      p.kts = atoi(e) < p.H / kKBlock ? atoi(e) : p.H / kKBlock;
+      p.kts = e < p.H / kKBlock ? e : p.H / kKBlock;
       p.nacc = (512 - 32 * p.kts) / 128 < 4 ? (512 - 32 * p.kts) / 128 : 4;
     }
   }
+#endif
   CUtensorMap mw, mh;
   int rc = make_map_bf16(&mw, w2q, p.Vpad, p.H, p.H, kKBlock, BN / 2, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
@@ -890,9 +904,12 @@ int dispatch_joint(JointParams& p, const void* w2q, const void* h_stash, int max
                        CU_TENSOR_MAP_SWIZZLE_64B);
     if (rc) return rc;
   }
+#ifdef RNNT_B200_TUNE
   if (v2) {
     if constexpr (MODE == 1) return launch_joint<128, 1, 1>(mw, mh, md, p, st);
   }
+#endif
+  (void)v2;
   switch (BN) {
     case 64: return launch_joint<64, MODE>(mw, mh, md, p, st);
     case 128: return launch_joint<128, MODE>(mw, mh, md, p, st);
@@ -921,6 +938,7 @@ extern "C" int rnnt_b200_joint_hidden(const float* p_enc, const float* p_dec, co
   if (rc) return rc;
   if (((uintptr_t)p_enc & 15) || ((uintptr_t)p_dec & 15) || ((uintptr_t)h_stash & 127)) return RNNT_B200_E_ALIGN;
   if (tile_cap < 1 || tile_cap > rnnt_b200_max_tiles(B, T, U1)) return RNNT_B200_E_SHAPE;
+  if (const int arch = rnnt_check_arch()) return arch;
   JointParams p = {};
   p.pe = p_enc; p.pd = p_dec; p.act_lens = act_lens; p.label_lens = label_lens;
   p.tile_utt = tile_utt; p.tile_cell0 = tile_cell0; p.n_tiles = n_tiles; p.h_stash = (__nv_bfloat16*)h_stash;

@@ -179,6 +179,10 @@ extern "C" int rnnt_b200_lattice(const float* lp_blank, const float* lp_label,
       !c_label || !loss)
     return RNNT_B200_E_NULL;
   if (B <= 0 || T <= 0 || U1 <= 0 || U1 > 1024) return RNNT_B200_E_SHAPE;
+  {
+    const int arch = rnnt_check_arch();
+    if (arch != RNNT_B200_OK) return arch;
+  }
   cudaStream_t st = (cudaStream_t)stream;
   // ll scratch lives in the (never read) tail of the planes?  No: keep it explicit --
   // the last diagonal row D-1 of utterance b is only used when T_b=T and U_b=U1-1, and
@@ -189,7 +193,9 @@ extern "C" int rnnt_b200_lattice(const float* lp_blank, const float* lp_label,
   double* ll_b = beta + rnnt_b200_plane_elems(B, T, U1);
   const int threads = ((U1 + 31) / 32) * 32;
   const size_t ring_bytes = (size_t)RING * 2 * threads * sizeof(float);  // <= 128 KB at 1024 threads
-  if (ring_bytes > 32 * 1024) {
+  // static (the diagonal exchange) + dynamic (the ring) shared memory above the 48 KB default needs the opt-in;
+  // set it whenever the sum can get there (U+1 >= 225 with the 16 KB exchange array)
+  if (ring_bytes > 16 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(lattice_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)ring_bytes);
     if (e != cudaSuccess) return (int)e;

@@ -140,6 +140,26 @@ __device__ __forceinline__ uint64_t umma_desc_kmajor(uint32_t saddr) {
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
+// MN-major operand (the contraction index runs over the ROWS of the shared-memory tile), SWIZZLE_128B:
+// a 64 (mn) x 64 (k) bf16 TMA box lands as 64 k-rows of 128 bytes = eight 8-row swizzle atoms, the canonical
+// layout ((8,n),(8,k)) : ((1,LBO),(8,SBO)) in 16-byte units with SBO = 1024 B between 8-row groups and LBO =
+// the distance between two 64-wide blocks of the operand. version 1 = sm_100.
+__device__ __forceinline__ uint64_t umma_desc_mn128(uint32_t saddr, uint32_t lbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)(lbo_bytes >> 4) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// instruction-descriptor bits 15 / 16: A / B operand MN-major
+__host__ __device__ constexpr uint32_t umma_idesc_bf16_mn(int M, int N) {
+  return umma_idesc_bf16(M, N) | (1u << 15) | (1u << 16);  // a_major = b_major = MN
+}
+__host__ __device__ constexpr uint32_t umma_idesc_bf16_bmn(int M, int N) {
+  return umma_idesc_bf16(M, N) | (1u << 16);               // A K-major, B MN-major
+}
 // D[tmem] (+)= A[smem] . B[smem]^T ; issued by ONE thread.
 __device__ __forceinline__ void umma_bf16_ss(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
                                              uint32_t idesc, uint32_t accumulate) {

@@ -223,11 +223,13 @@ def full_size_properties(B=32, T=500, U=100, E=320, D=320, H=512, V=4232, seed=2
         return loss.detach(), [t.grad for t in leaves]
 
     l1, g1 = run(1.0)
+    l1b, g1b = run(1.0)
     l2, g2 = run(2.0)
     ls, _ = run(1.0, slice(0, 3))
     out = {"loss_mean": float(l1.mean()), "finite": bool(all(torch.isfinite(g).all() for g in g1)),
            "db2_sum_over_abs": float(g1[5].sum().abs() / g1[5].abs().sum()),
-           "loss_subbatch_rel": float(((ls - l1[:3]).abs() / l1[:3].abs()).max())}
+           "loss_subbatch_rel": float(((ls - l1[:3]).abs() / l1[:3].abs()).max()),
+           "deterministic": bool(torch.equal(l1, l1b) and all(torch.equal(a, b) for a, b in zip(g1, g1b)))}
     for n, a, b in zip(names, g1, g2):
         out[f"lin_{n}"] = float((b - 2 * a).norm() / (2 * a).norm())
     # (4) drop-in boundary on two utterances at full T, U, fed the bf16-consistent logits
@@ -243,26 +245,178 @@ def full_size_properties(B=32, T=500, U=100, E=320, D=320, H=512, V=4232, seed=2
     return out
 
 
+def _dw2_run(L, ds, h, rows, V, H, Vds):
+    """One chunk through rnnt_b200_dw2_gemm + the ordered sum of its K-split partials."""
+    ns = L.rnnt_b200_dw2_splits(rows, V, H)
+    parts = torch.empty(ns, Vds, H, device=DEV)
+    bparts = torch.zeros(ns, Vds, device=DEV)
+    dw2 = torch.empty(Vds, H, device=DEV)
+    db2 = torch.empty(Vds, device=DEV)
+    st = torch.cuda.current_stream().cuda_stream
+    rc = L.rnnt_b200_dw2_gemm(ds.data_ptr(), h.data_ptr(), rows, V, H, parts.data_ptr(), bparts.data_ptr(), st)
+    assert rc == 0, rc
+    assert L.rnnt_b200_sum_partials(parts.data_ptr(), ns, Vds * H, dw2.data_ptr(), st) == 0
+    assert L.rnnt_b200_sum_partials(bparts.data_ptr(), ns, Vds, db2.data_ptr(), st) == 0
+    torch.cuda.synchronize()
+    return dw2, db2, ns
+
+
 def dw2_gemm_vs_torch(rows, V, H, seed=0):
-    """rnnt_b200_dw2_gemm (tcgen05, MN-major operands, split-K red.global.add) against fp32 torch
-    products of the same bf16 operands; called twice to check that it ACCUMULATES."""
+    """rnnt_b200_dw2_gemm (tcgen05, MN-major operands, K-split partials added in slot order) against float64 torch
+    products of the same bf16 operands; run twice: the two results must be bit-identical (deterministic)."""
     from rnnt_transducer_b200 import _lib
     L = _lib.lib()
     Vds, hp = L.rnnt_b200_ds_pitch(V), L.rnnt_b200_h_pitch(H)
     g = torch.Generator().manual_seed(seed)
     ds = (torch.randn(rows, Vds, generator=g) * 0.05).to(torch.bfloat16).to(DEV)
     h = torch.tanh(torch.randn(rows, hp, generator=g)).to(torch.bfloat16).to(DEV)
-    dw2 = torch.zeros(Vds, H, device=DEV)
-    db2 = torch.zeros(Vds, device=DEV)
+    dw2, db2, ns = _dw2_run(L, ds, h, rows, V, H, Vds)
+    dw2b, db2b, _ = _dw2_run(L, ds, h, rows, V, H, Vds)
+    ref = ds.double().t() @ h[:, :H].double()
+    refb = ds.double().sum(0)
+    return {"dw2_rel_l2": rel_l2(dw2.cpu(), ref.cpu()), "db2_rel_l2": rel_l2(db2.cpu(), refb.cpu()), "splits": ns,
+            "bit_identical": bool(torch.equal(dw2, dw2b) and torch.equal(db2, db2b))}
+
+
+def dh_gemm_vs_torch(tiles, V, H, lo=0, hi=None, seed=0):
+    """rnnt_b200_dh_gemm on its own: dpre = (dS . W2q) * (1 - h^2) for tiles [lo, hi) of a stash of ``tiles`` tiles,
+    against the float64 product of the same bf16 operands; rows outside [lo, hi) must stay untouched."""
+    from rnnt_transducer_b200 import _lib
+    L = _lib.lib()
+    hi = tiles if hi is None else hi
+    Vds, Vpad = L.rnnt_b200_ds_pitch(V), L.rnnt_b200_vocab_pad(V)
+    g = torch.Generator().manual_seed(seed)
+    rows = (hi - lo) * 128
+    ds = (torch.randn(rows, Vds, generator=g) * 0.05).to(torch.bfloat16)
+    ds[:, V:] = 0
+    w2q = torch.zeros(Vpad, H, dtype=torch.bfloat16)
+    w2q[:V] = (torch.randn(V, H, generator=g) * 0.05).to(torch.bfloat16)
+    h = torch.tanh(torch.randn(tiles * 128, H, generator=g)).to(torch.bfloat16)
+    dsd, w2d, hd = ds.to(DEV), w2q.to(DEV), h.to(DEV)
+    dpre = torch.full((tiles * 128, H), 7.0, dtype=torch.bfloat16, device=DEV)
+    st = torch.cuda.current_stream().cuda_stream
+    rc = L.rnnt_b200_dh_gemm(dsd.data_ptr(), w2d.data_ptr(), hd.data_ptr(), V, H, tiles, lo, hi, dpre.data_ptr(), st)
+    torch.cuda.synchronize()
+    assert rc == 0, rc
+    hs = h[lo * 128: hi * 128].double()
+    ref = (ds.double() @ w2q[:Vds].double()) * (1.0 - hs * hs)
+    got = dpre.cpu()
+    outside = torch.cat((got[:lo * 128], got[hi * 128:]))
+    return {"rel_l2": rel_l2(got[lo * 128: hi * 128], ref), "max_abs": max_abs(got[lo * 128: hi * 128], ref),
+            "ref_absmax": float(ref.abs().max()), "outside_untouched": bool((outside == 7.0).all())}
+
+
+def dpre_reduce_vs_torch(B, T, U, H, mode="ragged", seed=0):
+    """rnnt_b200_dpre_reduce against float64 sums of the same bf16 dpre rows (tile-packed), twice (bit-identical)."""
+    from rnnt_transducer_b200 import _lib
+    L = _lib.lib()
+    g = torch.Generator().manual_seed(seed)
+    tl, ul = synth_lengths(B, T, U, mode, g)
+    U1 = U + 1
+    ntile = [(int(t) * (int(u) + 1) + 127) // 128 for t, u in zip(tl, ul)]
+    tiles = sum(ntile)
+    dpre = (torch.randn(tiles * 128, H, generator=g) * 0.01).to(torch.bfloat16)
+    want_e = torch.zeros(B, T, H, dtype=torch.float64)
+    want_d = torch.zeros(B, U1, H, dtype=torch.float64)
+    first = 0
+    for b in range(B):
+        tb, w = int(tl[b]), int(ul[b]) + 1
+        blk = dpre[first * 128: first * 128 + tb * w].double().view(tb, w, H)
+        want_e[b, :tb] = blk.sum(1)
+        want_d[b, :w] = blk.sum(0)
+        first += ntile[b]
+    dd, tld, uld = dpre.to(DEV), tl.to(DEV), ul.to(DEV)
+    outs = []
     st = torch.cuda.current_stream().cuda_stream
     for _ in range(2):
-        rc = L.rnnt_b200_dw2_gemm(ds.data_ptr(), h.data_ptr(), rows, V, H, dw2.data_ptr(), db2.data_ptr(), st)
+        scratch = torch.empty(L.rnnt_b200_dpre_reduce_scratch_elems(B, T, U1, H), device=DEV)
+        dpe = torch.zeros(B, T, H, device=DEV)
+        dpd = torch.full((B, U1, H), 7.0, device=DEV)
+        rc = L.rnnt_b200_dpre_reduce(dd.data_ptr(), tld.data_ptr(), uld.data_ptr(), B, T, U1, H, scratch.data_ptr(),
+                                     dpe.data_ptr(), dpd.data_ptr(), st)
         assert rc == 0, rc
-    torch.cuda.synchronize()
-    ref = 2 * (ds.double().t() @ h[:, :H].double())
-    refb = 2 * ds.double().sum(0)
-    return {"dw2_rel_l2": rel_l2(dw2.cpu(), ref.cpu()), "db2_rel_l2": rel_l2(db2.cpu(), refb.cpu())}
+        torch.cuda.synchronize()
+        outs.append((dpe, dpd))
+    return {"dpe_rel_l2": rel_l2(outs[0][0].cpu(), want_e), "dpd_rel_l2": rel_l2(outs[0][1].cpu(), want_d),
+            "bit_identical": bool(torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1]))}
 
+
+def fused_vs_large_oracle(B, T, U, E, D, H, V, mode="ragged", seed=2019, full_grads=True, lens=None):
+    """Boundary 2 at a BASELINE shape against the per-utterance, t-chunked float64 oracle (oracle/large_oracle.py):
+    per-utterance loss and all six gradients of sum_b loss_b, (i) with the same bf16-rounded h / W2 and (ii) in
+    full precision (``full_grads=False``: loss only for (ii))."""
+    from oracle import large_oracle as LO
+    ins = _joint_inputs(B, T, U, E, D, H, V, mode, seed)
+    enc, dec, w1, b1, w2, b2, y, tl, ul = ins
+    if lens is not None:
+        tl, ul = (torch.tensor(v, dtype=torch.int32) for v in lens)
+        y = synth_labels(B, U, V, ul, torch.Generator().manual_seed(seed + 1))
+    names = ["enc", "dec", "w1", "b1", "w2", "b2"]
+    leaves = [t.to(DEV).requires_grad_(True) for t in (enc, dec, w1, b1, w2, b2)]
+    loss = R.joint_rnnt_loss(*leaves, y.to(DEV), tl.to(DEV), ul.to(DEV), reduction="none", host_lens=(tl, ul))
+    loss.sum().backward()
+    torch.cuda.synchronize()
+    out = {"loss_mean": float(loss.detach().mean()), "cells": int((tl.long() * (ul.long() + 1)).sum())}
+    lg = loss.detach().cpu().double()
+    for tag, q, want_g in (("q", True, True), ("full", False, full_grads)):
+        lo, g = LO.joint_rnnt_loss_and_grads(enc, dec, w1, b1, w2, b2, y, tl, ul, quantize_bf16=q, grads=want_g)
+        out[f"loss_rel_{tag}"] = float(((lg - lo).abs() / lo.abs()).max())
+        if want_g:
+            for n, a in zip(names, leaves):
+                out[f"d{n}_rel_l2_{tag}"] = rel_l2(a.grad, g[n])
+                out[f"d{n}_max_abs_{tag}"] = max_abs(a.grad, g[n])
+    return out
+
+
+def fused_is_deterministic(B, T, U, E, D, H, V, mode="ragged", seed=3, repeats=3):
+    """Identical calls must give BIT-identical losses and gradients (no order-dependent atomics in the backward)."""
+    ins = _joint_inputs(B, T, U, E, D, H, V, mode, seed)
+    y, tl, ul = (t.to(DEV) for t in ins[6:])
+    runs = []
+    for _ in range(repeats):
+        leaves = [t.to(DEV).clone().requires_grad_(True) for t in ins[:6]]
+        loss = R.joint_rnnt_loss(*leaves, y, tl, ul, reduction="none")
+        loss.sum().backward()
+        torch.cuda.synchronize()
+        runs.append([loss.detach()] + [t.grad for t in leaves])
+    names = ["loss", "enc", "dec", "w1", "b1", "w2", "b2"]
+    return {n: all(torch.equal(runs[0][i], r[i]) for r in runs[1:]) for i, n in enumerate(names)}
+
+
+def shared_embedding_grads(seed=4):
+    """rnnt/model.py:55-57 (share_embedding): decoder.embedding.weight IS joint.project_layer.weight. The fused
+    loss's dW2 and the embedding's own gradient must both land in the one shared tensor: compared with the float64
+    oracle's d loss / d W2 plus the embedding gradient of an identical model without the tying."""
+    import copy
+    cfg = dict(enc=dict(type="lstm", hidden_size=16, output_size=12, n_layers=1, bidirectional=True),
+               dec=dict(type="lstm", hidden_size=128, output_size=12, n_layers=1),
+               joint=dict(input_size=24, inner_size=128), vocab_size=30, share_weight=False,
+               share_embedding=True, feature_dim=20, dropout=0.0)
+    torch.manual_seed(seed)
+    tied = R.Transducer(cfg).to(DEV)
+    assert tied.decoder.embedding.weight is tied.joint.project_layer.weight
+    cfg2 = dict(cfg, share_embedding=False)
+    free = R.Transducer(cfg2).to(DEV)
+    sd = {k: v for k, v in tied.state_dict().items()}
+    free.load_state_dict(sd, strict=True)   # same values, two separate tensors
+    g = torch.Generator().manual_seed(seed)
+    B, T, U = 3, 14, 5
+    x = torch.randn(B, T, 20, generator=g).to(DEV)
+    xl = torch.tensor([14, 11, 9], dtype=torch.int32, device=DEV)
+    yl = torch.tensor([5, 3, 4], dtype=torch.int32, device=DEV)
+    yy = torch.randint(1, 30, (B, U), generator=g).to(DEV)
+    for b in range(B):
+        yy[b, int(yl[b]):] = 0
+    lt = tied(x, xl, yy, yl)
+    lt.backward()
+    lf = free(x, xl, yy, yl)
+    lf.backward()
+    torch.cuda.synchronize()
+    want = free.joint.project_layer.weight.grad + free.decoder.embedding.weight.grad
+    got = tied.joint.project_layer.weight.grad
+    return {"loss_equal": abs(float(lt) - float(lf)) / abs(float(lf)), "shared_grad_rel_l2": rel_l2(got, want),
+            "emb_part_norm": float(free.decoder.embedding.weight.grad.norm()),
+            "w2_part_norm": float(free.joint.project_layer.weight.grad.norm())}
 
 
 def transducer_vs_reference_fixture():
@@ -301,24 +455,24 @@ def transducer_vs_reference_fixture():
 
 def dw2_gemm_guard_bands(rows=192, V=300, H=128):
     """compute-sanitizer is not available on the GPU pool: run the GEMM with its outputs embedded
-    in larger poisoned buffers and check that nothing outside (Vds x H) / (Vds) was touched."""
+    in larger poisoned buffers and check that nothing outside the partial slots was touched."""
     from rnnt_transducer_b200 import _lib
     L = _lib.lib()
     Vds, hp = L.rnnt_b200_ds_pitch(V), L.rnnt_b200_h_pitch(H)
     g = torch.Generator().manual_seed(1)
     ds = (torch.randn(rows, Vds, generator=g) * 0.05).to(torch.bfloat16).to(DEV)
     h = torch.tanh(torch.randn(rows, hp, generator=g)).to(torch.bfloat16).to(DEV)
+    ns = L.rnnt_b200_dw2_splits(rows, V, H)
     pad = 4096
-    big = torch.full((pad + Vds * H + pad,), 7.0, device=DEV)
-    bigb = torch.full((pad + Vds + pad,), 7.0, device=DEV)
-    big[pad:pad + Vds * H] = 0
-    bigb[pad:pad + Vds] = 0
+    big = torch.full((pad + ns * Vds * H + pad,), 7.0, device=DEV)
+    bigb = torch.full((pad + ns * Vds + pad,), 7.0, device=DEV)
+    bigb[pad:pad + ns * Vds] = 0
     st = torch.cuda.current_stream().cuda_stream
     rc = L.rnnt_b200_dw2_gemm(ds.data_ptr(), h.data_ptr(), rows, V, H, big.data_ptr() + pad * 4,
                               bigb.data_ptr() + pad * 4, st)
     torch.cuda.synchronize()
-    ok = bool((big[:pad] == 7).all() and (big[pad + Vds * H:] == 7).all() and
-              (bigb[:pad] == 7).all() and (bigb[pad + Vds:] == 7).all())
+    ok = bool((big[:pad] == 7).all() and (big[pad + ns * Vds * H:] == 7).all() and
+              (bigb[:pad] == 7).all() and (bigb[pad + ns * Vds:] == 7).all())
     ref = ds.double().t() @ h[:, :H].double()
-    return {"rc": rc, "guards_intact": ok,
-            "dw2_rel_l2": rel_l2(big[pad:pad + Vds * H].view(Vds, H).cpu(), ref.cpu())}
+    got = big[pad:pad + ns * Vds * H].view(ns, Vds, H).double().sum(0)
+    return {"rc": rc, "guards_intact": ok, "dw2_rel_l2": rel_l2(got.cpu(), ref.cpu())}

@@ -132,6 +132,31 @@ def test_dw2_gemm_rejects_bad_arguments():
     assert L.rnnt_b200_dw2_gemm(a, a, 128, 100, 192, a, a, None) == -2      # H not in {128, 256, 512}
     assert L.rnnt_b200_dw2_gemm(a + 2, a, 128, 100, 512, a, a, None) == -4  # alignment
     assert L.rnnt_b200_dw2_gemm(a, a, 0, 100, 512, a, a, None) == 0         # nothing to do
+    assert L.rnnt_b200_dw2_splits(100, 100, 512) == 0 and L.rnnt_b200_dw2_splits(128, 100, 192) == 0
+    assert L.rnnt_b200_dw2_splits(64, 100, 512) == 1                        # one K block: one split
+
+
+def test_dh_gemm_and_reduce_reject_bad_arguments():
+    L = _lib.lib()
+    a = 256
+    assert L.rnnt_b200_dh_gemm_supported(512) == 1 and L.rnnt_b200_dh_gemm_supported(192) == 0
+    assert L.rnnt_b200_dh_gemm(None, a, a, 100, 512, 4, 0, 4, a, None) == -1
+    assert L.rnnt_b200_dh_gemm(a, a, a, 100, 192, 4, 0, 4, a, None) == -2      # H not in {128, 256, 512}
+    assert L.rnnt_b200_dh_gemm(a, a, a, 100, 512, 4, 2, 5, a, None) == -2      # tile_hi > tile_cap
+    assert L.rnnt_b200_dh_gemm(a + 16, a, a, 100, 512, 4, 0, 4, a, None) == -4  # alignment
+    assert L.rnnt_b200_dh_gemm(a, a, a, 100, 512, 4, 2, 2, a, None) == 0       # nothing to do
+    assert L.rnnt_b200_dpre_reduce_scratch_elems(32, 500, 101, 512) == 32 * 63 * 101 * 512
+    assert L.rnnt_b200_dpre_reduce(a, a, a, 1, 4, 2, 100, a, a, a, None) == -2   # H % 64
+    assert L.rnnt_b200_dpre_reduce(a, None, a, 1, 4, 2, 128, a, a, a, None) == -1
+    assert L.rnnt_b200_sum_partials(a, 0, 10, a, None) == -2
+    assert L.rnnt_b200_build_tiles(a, a, 1, 4, 2, 99, a, a, a, None) == -2       # tile_cap above the padded bound
+
+
+def test_host_tile_count_applies_the_device_clamps():
+    from rnnt_transducer_b200._api import _tile_count
+    # t = 0 counts as one frame, lengths above the padded dims are cut: same clamps as build_tiles_kernel
+    assert _tile_count(([0, 700, 5], [3, 50, 900]), 500, 101) == 1 + (500 * 51 + 127) // 128 + (5 * 101 + 127) // 128
+    assert _tile_count(None, 500, 101) is None
 
 
 def test_transducer_loads_reference_checkpoint_and_matches_its_encoder_decoder_joint():

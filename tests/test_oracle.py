@@ -130,3 +130,25 @@ def test_hypothesis_ragged_shapes_c_oracle_vs_torch_oracle():
             assert float(np.abs(gc[b, :, ub + 1:]).max(initial=0.0)) == 0.0
             assert float(np.abs(gc[b, :tb, :ub + 1].sum(-1)).max()) < 1e-5   # softmax-Jacobian rows sum to 0
     check()
+
+
+@pytest.mark.parametrize("dims,mode", [((3, 13, 6, 16, 12, 64, 50), "edge"), ((2, 9, 4, 8, 8, 32, 20), "ragged"),
+                                       ((1, 1, 0, 8, 8, 32, 5), "full")])
+@pytest.mark.parametrize("quantize", [False, True])
+def test_large_shape_oracle_agrees_with_the_materialising_oracle(dims, mode, quantize):
+    # oracle/large_oracle.py (per utterance, t-chunked, bounded memory) is the checker at the BASELINE shapes;
+    # here it is pinned on the oracle that materialises the logits, at shapes both can run
+    from oracle import large_oracle as LO
+    from tests.gpu_checks import _joint_inputs
+    enc, dec, w1, b1, w2, b2, y, tl, ul = _joint_inputs(*dims, mode, 3)
+    ol = [t.double().requires_grad_(True) for t in (enc, dec, w1, b1, w2, b2)]
+    lo = O.joint_rnnt_loss(*ol, y, tl, ul, reduction="none", quantize_bf16=quantize)
+    lo.sum().backward()
+    l2, g = LO.joint_rnnt_loss_and_grads(enc, dec, w1, b1, w2, b2, y, tl, ul, quantize_bf16=quantize,
+                                         cells_per_chunk=20)
+    assert float((l2 - lo.detach()).abs().max()) < 1e-11
+    # (quantised mode: the fp32 addition of the two projections rounds the gradient that passes through it)
+    for n, t in zip(["enc", "dec", "w1", "b1", "w2", "b2"], ol):
+        assert max_abs(g[n], t.grad) < (1e-6 if quantize else 1e-11), n
+    l3, none = LO.joint_rnnt_loss_and_grads(enc, dec, w1, b1, w2, b2, y, tl, ul, quantize_bf16=quantize, grads=False)
+    assert none is None and float((l3 - l2).abs().max()) < 1e-11
