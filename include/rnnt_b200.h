@@ -108,11 +108,12 @@ int rnnt_b200_build_tiles(const int32_t* act_lens, const int32_t* label_lens,
 
 /* W2 (V,H) float32 -> bf16 (Vpad,H) zero-padded rows; b2 (V) -> (Vpad) float32 scaled by
  * log2(e) with -1e30 in the padding (masks padded vocabulary columns).
- * Vpad = rnnt_b200_vocab_pad(V). */
+ * Vpad = rnnt_b200_vocab_pad(V). w2t_bf16 (nullable): the transposed pack (H,Vpad) bf16, zero columns in the
+ * padding -- the K-major B operand of rnnt_b200_dh_gemm (backward only). */
 int rnnt_b200_vocab_pad(int V);
 int rnnt_b200_vocab_tile(int V);
 int rnnt_b200_pack_vocab(const float* w2, const float* b2, int V, int H,
-                         void* w2_bf16, float* b2_log2, void* stream);
+                         void* w2_bf16, float* b2_log2, void* w2t_bf16, void* stream);
 
 /* Row pitch (elements) of the stashed hidden activations h. H = 128, 256, 512 (the shapes
  * rnnt_b200_dw2_gemm covers; it sums d b2 itself): H. Other H: H + 32, column H holds 1.0 for valid
@@ -169,13 +170,14 @@ int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, const float
 /* Fused backward, stage 2 (the backward of project_layer followed by the backward of tanh, rnnt/model.py:32-35
  * in reverse) for one staged dS chunk, tiles [tile_lo, tile_hi):
  *   dpre[row, j] = bf16( (sum_v dS[row, v] * W2_bf16[v, j]) * (1 - h[row, j]^2) )
- * tcgen05 GEMM (CTA pairs, M = 256 rows, N = H with the dS slice shared by the column halves through the
- * collector, K = ds_pitch(V)) with the tanh derivative in the epilogue. ds: as written by
- * rnnt_b200_joint_bwd_ds for the same [tile_lo, tile_hi); w2_bf16: the pack of rnnt_b200_pack_vocab; h_stash and
+ * w2t_bf16: the TRANSPOSED pack (H, Vpad) of rnnt_b200_pack_vocab.
+ * tcgen05 GEMM (CTA pairs, M = 256 rows, N = H: both column halves against one dS box per K block,
+ * K = ds_pitch(V)) with the tanh derivative in the epilogue. ds: as written by
+ * rnnt_b200_joint_bwd_ds for the same [tile_lo, tile_hi); h_stash and
  * dpre: (tile_cap*128, H) bf16, 128-byte aligned, rows tile*128 + r (dpre rows outside [tile_lo, tile_hi) are not
  * touched). H in {128, 256, 512} (rnnt_b200_dh_gemm_supported); other H: the caller forms dpre with library GEMMs. */
 int rnnt_b200_dh_gemm_supported(int H);
-int rnnt_b200_dh_gemm(const void* ds_bf16, const void* w2_bf16, const void* h_stash, int V, int H,
+int rnnt_b200_dh_gemm(const void* ds_bf16, const void* w2t_bf16, const void* h_stash, int V, int H,
                       int tile_cap, int tile_lo, int tile_hi, void* dpre_bf16, void* stream);
 
 /* Fused backward, stage 3: the backward of the broadcast add that replaces the reference's repeat + cat

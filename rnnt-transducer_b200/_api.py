@@ -49,7 +49,7 @@ class KernelTimer:
     active = None
     # kernels launched per C-ABI call
     KERNELS = {"logits_to_planes": 1, "lattice": 2, "planes_to_dlogits": 1, "build_tiles": 1,
-               "pack_vocab": 1, "joint_hidden": 1, "joint_fwd": 1, "joint_bwd_ds": 1, "dh_gemm": 1,
+               "pack_vocab": 2, "joint_hidden": 1, "joint_fwd": 1, "joint_bwd_ds": 1, "dh_gemm": 1,
                "dpre_reduce": 2, "sum_partials": 1, "joint_step_argmax": 1, "dw2_gemm": 1}
 
     def __init__(self, events: bool = True):
@@ -276,7 +276,9 @@ class _JointLossFn(torch.autograd.Function):
                     raise ValueError(f"host_lens gives {max_tiles} tiles but the device lengths need {need}")
             w2q = torch.empty(Vpad, H, dtype=torch.bfloat16, device=dev)
             b2l = torch.empty(Vpad, dtype=torch.float32, device=dev)
-            _call("pack_vocab", L.rnnt_b200_pack_vocab, _ptr(w2), _ptr(b2), V, H, _ptr(w2q), _ptr(b2l), st)
+            # the backward's dh GEMM contracts over v: it takes W2 transposed (H, Vpad), packed in the same call
+            w2t = torch.empty(H, Vpad, dtype=torch.bfloat16, device=dev) if (need_grad and H in (128, 256, 512)) else None
+            _call("pack_vocab", L.rnnt_b200_pack_vocab, _ptr(w2), _ptr(b2), V, H, _ptr(w2q), _ptr(b2l), _ptr(w2t), st)
             n = L.rnnt_b200_plane_elems(B, T, U1)
             lse = torch.empty(n, dtype=torch.float32, device=dev)
             lpb = torch.empty(n, dtype=torch.float32, device=dev)
@@ -292,14 +294,14 @@ class _JointLossFn(torch.autograd.Function):
             loss, cb, cl = _lattice(lpb, lpl, act_lens, label_lens, B, T, U1)
         if need_grad:
             ctx.save_for_backward(labels, act_lens, label_lens, tile_utt, tile_cell0, n_tiles, w2q, b2l,
-                                  lse, lpb, lpl, cb, cl, h_stash)
+                                  lse, lpb, lpl, cb, cl, h_stash, w2t)
         ctx.dims = (B, T, U1, V, H, L.rnnt_b200_ds_pitch(V), max_tiles, blank)
         return loss
 
     @staticmethod
     def backward(ctx, grad_out):
         (labels, act_lens, label_lens, tile_utt, tile_cell0, n_tiles, w2q, b2l, lse, lpb, lpl, cb, cl,
-         h_stash) = ctx.saved_tensors
+         h_stash, w2t) = ctx.saved_tensors
         B, T, U1, V, H, Vds, max_tiles, blank = ctx.dims
         L = _lib.lib()
         dev = lse.device
@@ -312,6 +314,7 @@ class _JointLossFn(torch.autograd.Function):
             # dh / dW2 / db2: own tcgen05 GEMMs (csrc/dh_gemm.cu, csrc/dw2_gemm.cu) where they cover the shape,
             # else library GEMMs (dW2/db2 against the ones column of the stash)
             own_gemm = H in (128, 256, 512)          # the stash has no ones column at these H (pitch == H)
+            lib_dh = (not own_gemm) or os.environ.get("RNNT_B200_DH_LIB", "0") == "1"   # "1": A/B timing only
             chunk = max(2, min(max_tiles, _DS_BUDGET_BYTES // (128 * Vds * 2)))
             nchunk = -(-max_tiles // chunk)
             chunk = -(-max_tiles // nchunk)          # balanced chunks,
@@ -345,18 +348,20 @@ class _JointLossFn(torch.autograd.Function):
                                                     _ptr(tile_cell0), _ptr(n_tiles), _ptr(lse), _ptr(lpb),
                                                     _ptr(lpl), _ptr(cb), _ptr(cl), _ptr(scale), B, T, U1, V, H, blank, max_tiles, lo, hi,
                                                     _ptr(dsc), st)
-                if own_gemm:
-                    _call("dh_gemm", L.rnnt_b200_dh_gemm, _ptr(dsc), _ptr(w2q), _ptr(h_stash), V, H, max_tiles, lo, hi,
+                if lib_dh:
+                    with _region("lib_gemm_dh"):
+                        dh = torch.mm(dsc, w2v)                                        # (rows, H) bf16
+                    hf = h_stash[lo * 128: hi * 128, :H].float()
+                    dpre[lo * 128: hi * 128] = (dh.float() * (1.0 - hf * hf)).to(torch.bfloat16)
+                else:
+                    _call("dh_gemm", L.rnnt_b200_dh_gemm, _ptr(dsc), _ptr(w2t), _ptr(h_stash), V, H, max_tiles, lo, hi,
                           _ptr(dpre), st)
+                if own_gemm:
                     _call("dw2_gemm", L.rnnt_b200_dw2_gemm, _ptr(dsc), h_stash.data_ptr() + lo * 128 * hp * 2,
                           rows, V, H, dw2_parts.data_ptr() + slot * Vds * H * 4, db2_parts.data_ptr() + slot * Vds * 4, st)
                     slot += nsplit[ci]
                 else:
                     hc = h_stash[lo * 128: hi * 128]
-                    with _region("lib_gemm_dh"):
-                        dh = torch.mm(dsc, w2v)                                        # (rows, H) bf16
-                        hf = hc[:, :H].float()
-                        dpre[lo * 128: hi * 128] = (dh.float() * (1.0 - hf * hf)).to(torch.bfloat16)
                     with _region("lib_gemm_dw2"):
                         # K = rows is huge and the output (pitch x Vds) small: split K (batched GEMM;
                         # measured best, profiles/r01_notes.md). Column H of the stash is 1 for valid

@@ -29,7 +29,7 @@ SIGNATURES = {
     "rnnt_b200_build_tiles": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p, _p]),
     "rnnt_b200_vocab_pad": (_i, [_i]),
     "rnnt_b200_vocab_tile": (_i, [_i]),
-    "rnnt_b200_pack_vocab": (_i, [_p, _p, _i, _i, _p, _p, _p]),
+    "rnnt_b200_pack_vocab": (_i, [_p, _p, _i, _i, _p, _p, _p, _p]),
     "rnnt_b200_h_pitch": (_i, [_i]),
     "rnnt_b200_ds_pitch": (_i, [_i]),
     "rnnt_b200_joint_hidden": (_i, [_p] * 7 + [_i] * 5 + [_p, _p]),

@@ -6,22 +6,34 @@
 //   dpre[row, j] = bf16( dh[row, j] * (1 - h[row, j]^2) )
 //
 // One GEMM per staged dS chunk on the 5th-gen tensor cores: M = rows (256 per CTA pair, cta_group::2),
-// N = H (all of it: two UMMAs of N = 256 per K = 16 slice share the dS slice through the tensor core's
-// collector, accumulators in TMEM columns 0..255 / 256..511), K = v. dS is K-major as it lies
-// (128 rows x 64 v TMA boxes, SWIZZLE_128B); W2q (V,H) row-major supplies B[n = j][k = v] MN-major as it
-// lies (64 v x 64 j boxes, the same canonical layout dw2_gemm.cu uses for its operands). Shared memory per
-// K block of 64: fill 48 KB + operand reads 48 KB per 1024 clk of MMA = 96 of 128 B/clk/SM.
+// N = H (all of it: per K block of 64 four UMMAs of N = 256 into TMEM columns 0..255, then four into columns
+// 256..511, so that a dS box is fetched from L2 once for both column halves), K = v. dS is K-major as it lies
+// (128 rows x 64 v TMA boxes, SWIZZLE_128B); B[n = j][k = v] comes K-major from a TRANSPOSED bf16 pack of W2
+// (H, Vpad) that rnnt_b200_pack_vocab writes next to the (Vpad, H) one (64 j x 64 v boxes), so both operands use
+// one descriptor form. Shared memory per K block of 64: fill 48 KB + operand reads 64 KB per 1024 clk of MMA =
+// 112 of 128 B/clk/SM (measured with clock64 stamps: 1024-1060 clk per K block; profiles/r02_notes.md).
+//
+// Order of the UMMAs: a first version alternated the two accumulator halves UMMA by UMMA so that the dS slice
+// could be shared through the tensor core's collector (as dw2_wide_kernel does): 145 clk per UMMA without and
+// 154 clk with the collector hint, against 128 clk when the four K slices of one half are issued back to back
+// (with or without TMA traffic: the cost is in the tensor pipe, not in shared memory).
 //
 // TMEM is full (512 columns), so the epilogue of a unit cannot overlap the next unit's MMAs; it is
 // kept short instead: the unit's h rows (the tanh derivative) are TMA-loaded into ring stages that the
-// last K blocks have just released ("H items" of the same ring), eight warps drain TMEM (64 B/clk/SM is the
-// hardware's TMEM read rate: ~4 k clk per unit against ~69 k clk of MMA at V = 4232), multiply, pack to
-// bf16 and hand 32 x 32 boxes to TMA stores out of per-warp double-buffered staging tiles.
+// last K blocks have just released ("H items" of the same ring), eight warps drain TMEM, multiply, pack to
+// bf16 and write dpre IN PLACE over the h blocks (same swizzled 16-byte chunks, same thread), and a store warp
+// sends every finished 128 x 64 block out with one TMA store (full 128-byte lines).
 //
-// Ring items of one unit, in order: NK K items (dS box + W2 boxes; consumed by the MMA thread, released by
-// a multicast tcgen05.commit) then NHI H items (up to three 128 x 64 h blocks each; consumed and released
-// by the CTA's own eight epilogue warps). Every role walks the same item sequence (RingWalk).
-// Warps: 0-7 epilogue, 8 dS TMA, 9 TMEM alloc + MMA issue (leader CTA), 10 W2 TMA, 11 h TMA.
+// Ring items of one unit, in order: NK K items (dS box + W2^T boxes; consumed by the MMA thread, released by
+// a multicast tcgen05.commit) then NHI H items (up to three 128 x 64 h blocks each; consumed by the CTA's own
+// eight epilogue warps, released by the store warp once its stores have read them). Every role walks the same
+// item sequence (RingWalk). An mbarrier parity wait is only meaningful within one phase of the barrier, so every
+// waiter must follow the barrier it waits on use by use: every producer thread performs the acquire wait of
+// EVERY item of the ring, also of the items it loads nothing for (a first version whose h producer skipped the
+// K items ran phases ahead of the barriers and its waits passed spuriously). Three producer threads: one wait +
+// expect_tx + five TMA issues per 1024 clk of MMA is more than one thread manages.
+// Warps: 0-7 epilogue, 8 TMA producer (dS boxes, H items), 9 TMEM alloc + MMA issue (leader CTA), 10 / 11 TMA
+// producers of the W2^T boxes of column half 0 / 1, 12 store warp.
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include "common.cuh"
@@ -30,32 +42,45 @@
 
 using namespace sm100;
 
+#ifdef RNNT_B200_TUNE
+#include <stdio.h>
+// RNNT_B200_DH_DEBUG: 1 no epilogue work (barriers only), 4 no dpre stores, 8 no TMA loads of the K items (MMA on
+// stale buffers), 16 accumulator halves alternating per K slice through the collector (the first version)
+#define RNNT_DH_DBG(p) ((p).debug)
+#define RNNT_DH_TRACE(p) ((p).trace != nullptr && blockIdx.x == 0)  // RNNT_B200_DH_TRACE=<file>: clock64 stamps of CTA 0
+#else
+#define RNNT_DH_DBG(p) 0
+#define RNNT_DH_TRACE(p) false
+#endif
+
 namespace {
 
-constexpr int DH_THREADS = 384;
+constexpr int DH_THREADS = 416;                   // 13 warps (roles in the header comment)
 constexpr int DH_STAGES = 4;
 constexpr int DH_ABYTES = 128 * 128;              // dS box: 128 rows x 64 v
-constexpr int DH_BBOX = 64 * 128;                 // W2 box: 64 v x 64 j
+constexpr int DH_BBOX = 64 * 128;                 // W2^T box: 64 j rows x 64 v
 constexpr int DH_HBLK = 128 * 128;                // h block: 128 rows x 64 j
 constexpr int DH_STAGE = DH_ABYTES + 4 * DH_BBOX;  // 48 KB = three h blocks
-constexpr int DH_OUT = 8 * 2 * 2048;              // per epilogue warp: two 32 x 32 bf16 staging tiles
-constexpr int DH_SMEM = DH_STAGES * DH_STAGE + DH_OUT + 256;
+constexpr int DH_SMEM = DH_STAGES * DH_STAGE + 512;
 
 struct DhCtl {
-  uint64_t full[DH_STAGES];    // leader CTA: K item landed ({dS, W2} producer x {leader, peer} + bytes)
+  uint64_t full[DH_STAGES];    // leader CTA: K item landed (the producer threads of both CTAs + the bytes of both)
   uint64_t kempty[DH_STAGES];  // both CTAs: multicast commit behind the K item's UMMAs
   uint64_t hfull[DH_STAGES];   // this CTA: h blocks landed
-  uint64_t hempty[DH_STAGES];  // this CTA: its eight epilogue warps are done with the h blocks
+  uint64_t hempty[DH_STAGES];  // this CTA: the store warp's TMA stores have read the stage's blocks
+  uint64_t blk_done[8];        // this CTA: the eight epilogue warps have written dpre over h block i
   uint64_t acc_full, acc_empty;
   uint32_t tmem_base;
 };
-static_assert(sizeof(DhCtl) <= 256, "ctl region");
+static_assert(sizeof(DhCtl) <= 512, "ctl region");
 
 struct DhParams {
   int H, HN, NH;          // UMMA N (min(H, 256)) and the number of such column halves (1 or 2)
   int NK;                 // K blocks of 64 (ds_pitch / 64)
   int NHI;                // H items per unit: ceil((H / 64) / 3)
   int tile_lo, tile_hi;   // tiles of this chunk; dS row 0 is row 0 of tile_lo
+  int debug;              // tuning build only
+  long long* trace;       // tuning build only: 3 roles x 4096 x 3 clock64 stamps
 };
 
 // Position in the ring's item sequence. bit s of kpar / hpar: parity of the number of K / H items that
@@ -93,8 +118,7 @@ dh_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constant
                const DhParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
-  uint8_t* smem_out = smem + DH_STAGES * DH_STAGE;
-  DhCtl* ctl = reinterpret_cast<DhCtl*>(smem_out + DH_OUT);
+  DhCtl* ctl = reinterpret_cast<DhCtl*>(smem + DH_STAGES * DH_STAGE);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const int cid = blockIdx.x >> 1, ncl = gridDim.x >> 1;
@@ -109,11 +133,12 @@ dh_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constant
   }
   if (warp == 9 && lane == 0) {
     for (int i = 0; i < DH_STAGES; ++i) {
-      mbar_init(&ctl->full[i], 4);
+      mbar_init(&ctl->full[i], 2 * (1 + p.NH));  // producers of both CTAs
       mbar_init(&ctl->kempty[i], 1);
       mbar_init(&ctl->hfull[i], 1);
-      mbar_init(&ctl->hempty[i], 8);
+      mbar_init(&ctl->hempty[i], 1);
     }
+    for (int i = 0; i < 8; ++i) mbar_init(&ctl->blk_done[i], 8);
     mbar_init(&ctl->acc_full, 1);
     mbar_init(&ctl->acc_empty, 2 * 8);
     fence_barrier_init();
@@ -129,59 +154,68 @@ dh_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constant
   tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
 
-  if (warp == 8 || warp == 10) {
-    // =========================== TMA PRODUCERS of the K items (dS / W2) ===========================
-    const bool is_a = warp == 8;
-    if (lane == 0) {
+  if (warp == 8 || warp == 10 || warp == 11) {
+    // =========================== TMA PRODUCERS ===========================
+    // role 0 (warp 8): dS boxes and H items; role 1 / 2 (warps 10 / 11): W2^T boxes of column half 0 / 1.
+    const int role = warp == 8 ? 0 : warp - 9;
+    if (lane == 0 && role <= p.NH) {
       RingWalk rw;
-      const int nbox = p.NH * (p.HN / 128);  // 64-wide W2 boxes per CTA and K item
+      const int nbx = p.HN / 128;  // 64-row W2^T boxes per CTA, K item and column half
       for (int u = cid; u < n_units; u += ncl) {
         const int row0 = (2 * u + (int)rank) * RNNT_TILE_M;  // chunk-local dS row of this CTA's tile
-        for (int kb = 0; kb < p.NK; ++kb) {
+        int kb = (u * 5) % p.NK;  // rotated start: the pairs do not pull the same W2^T boxes out of L2 at once
+        for (int i = 0; i < p.NK; ++i) {
+          const long long tr0 = RNNT_DH_TRACE(p) ? clock64() : 0;
           rw.acquire(ctl);
+          const long long tr1 = RNNT_DH_TRACE(p) ? clock64() : 0;
           const uint32_t s = rw.stage();
           const uint32_t full = mapa_u32(smem_u32(&ctl->full[s]), 0);
-          const uint32_t bytes = is_a ? DH_ABYTES : nbox * DH_BBOX;
+          const uint32_t bytes = role == 0 ? DH_ABYTES : nbx * DH_BBOX;
+          if (RNNT_DH_DBG(p) & 8) {
+            mbar_arrive_cluster(full);
+            rw.next_k();
+            continue;
+          }
           if (rank == 0) mbar_arrive_expect_tx(&ctl->full[s], 2 * bytes);  // both CTAs' boxes
           else mbar_arrive_cluster(full);
           uint8_t* st = smem + s * DH_STAGE;
-          if (is_a) {
+          if (role == 0) {
             tma_load_2d_pair(st, &map_ds, full, kb * 64, row0);
           } else {
-            for (int hf = 0; hf < p.NH; ++hf)
-              for (int bx = 0; bx < p.HN / 128; ++bx) {
-                const int j0 = hf * p.HN + (int)rank * (p.HN / 2) + bx * 64;
-                tma_load_2d_pair(st + DH_ABYTES + (hf * 2 + bx) * DH_BBOX, &map_w2, full, j0, kb * 64);
-              }
+            const int hf = role - 1;
+            for (int bx = 0; bx < nbx; ++bx) {  // this CTA's HN/2 rows j of W2^T, 64 v wide: K-major like the dS box
+              const int j0 = hf * p.HN + (int)rank * (p.HN / 2) + bx * 64;
+              tma_load_2d_pair(st + DH_ABYTES + (hf * 2 + bx) * DH_BBOX, &map_w2, full, kb * 64, j0);
+            }
+          }
+          if (RNNT_DH_TRACE(p) && role == 0 && rw.n < 4096) {
+            long long* t = p.trace + 3 * 4096 + 3 * rw.n;
+            t[0] = tr0; t[1] = tr1; t[2] = clock64();
           }
           rw.next_k();
+          if (++kb == p.NK) kb = 0;
         }
-        for (int i = 0; i < p.NHI; ++i) rw.next_h();
-      }
-    }
-  } else if (warp == 11) {
-    // =========================== TMA PRODUCER of the H items (this CTA's h rows) ===========================
-    if (lane == 0) {
-      RingWalk rw;
-      for (int u = cid; u < n_units; u += ncl) {
         const int tile = p.tile_lo + 2 * u + (int)rank;  // past the stash: TMA fills zeros
-        for (int kb = 0; kb < p.NK; ++kb) rw.next_k();
-        for (int i = 0; i < p.NHI; ++i) {
-          rw.acquire(ctl);
-          const uint32_t s = rw.stage();
-          const int nb = min(3, HB - 3 * i);
-          mbar_arrive_expect_tx(&ctl->hfull[s], nb * DH_HBLK);
-          for (int j = 0; j < nb; ++j)
-            tma_load_2d(smem + s * DH_STAGE + j * DH_HBLK, &map_h, &ctl->hfull[s], (3 * i + j) * 64,
-                        tile * RNNT_TILE_M);
+        for (int i = 0; i < p.NHI; ++i) {  // H items: this CTA's h rows, into stages the last K blocks have released
+          rw.acquire(ctl);                 // (every producer follows every release: see the header comment)
+          if (role == 0) {
+            const uint32_t s = rw.stage();
+            const int nb = min(3, HB - 3 * i);
+            mbar_arrive_expect_tx(&ctl->hfull[s], nb * DH_HBLK);
+            for (int j = 0; j < nb; ++j)
+              tma_load_2d(smem + s * DH_STAGE + j * DH_HBLK, &map_h, &ctl->hfull[s], (3 * i + j) * 64,
+                          tile * RNNT_TILE_M);
+          }
           rw.next_h();
         }
       }
     }
   } else if (warp == 9) {
     // =========================== MMA ISSUER (leader CTA) ===========================
+    // Per K item: the four K = 16 slices into column half 0 (TMEM columns 0..255), then the four into half 1
+    // (see the header comment for why not alternating).
     if (rank == 0) {
-      const uint32_t idesc = umma_idesc_bf16_bmn(256, p.HN);
+      const uint32_t idesc = umma_idesc_bf16(256, p.HN);  // both operands K-major
       const uint32_t s0 = smem_u32(smem);
       RingWalk rw;
       int it = 0;
@@ -190,118 +224,152 @@ dh_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constant
         tc_fence_after();
         for (int kb = 0; kb < p.NK; ++kb) {
           const uint32_t s = rw.stage();
+          const long long tr0 = RNNT_DH_TRACE(p) ? clock64() : 0;
           mbar_wait(&ctl->full[s], rw.k_parity());
+          const long long tr1 = RNNT_DH_TRACE(p) ? clock64() : 0;
           tc_fence_after();
           if (elect_one_sync()) {
             const uint32_t a0 = s0 + s * DH_STAGE, b0 = a0 + DH_ABYTES;
+            const uint32_t acc0 = kb > 0 ? 1u : 0u;
+            if (p.NH == 2 && (RNNT_DH_DBG(p) & 16)) {  // experiment: halves alternating per K slice through the collector
 #pragma unroll
-            for (int kk = 0; kk < 4; ++kk) {  // K = 16: 32 bytes along a dS row, two 8-row atoms of W2
-              const uint64_t adesc = umma_desc_kmajor<128>(a0) + 2 * kk;
-              const uint64_t bdesc0 = umma_desc_mn128(b0 + kk * 2048, DH_BBOX);
-              const uint32_t acc = (kb > 0 || kk > 0) ? 1u : 0u;
-              if (p.NH == 2) {
-                const uint64_t bdesc1 = umma_desc_mn128(b0 + 2 * DH_BBOX + kk * 2048, DH_BBOX);
-                umma_bf16_ss_pair_areuse<1>(tmem_base, adesc, bdesc0, idesc, acc);
-                umma_bf16_ss_pair_areuse<0>(tmem_base + 256, adesc, bdesc1, idesc, acc);
-              } else {
-                umma_bf16_ss_pair(tmem_base, adesc, bdesc0, idesc, acc);
+              for (int kk = 0; kk < 4; ++kk) {
+                umma_bf16_ss_pair_areuse<1>(tmem_base, umma_desc_kmajor<128>(a0) + 2 * kk,
+                                            umma_desc_kmajor<128>(b0) + 2 * kk, idesc, (kk > 0) ? 1u : acc0);
+                umma_bf16_ss_pair_areuse<0>(tmem_base + 256, umma_desc_kmajor<128>(a0) + 2 * kk,
+                                            umma_desc_kmajor<128>(b0 + 2 * DH_BBOX) + 2 * kk, idesc, (kk > 0) ? 1u : acc0);
+              }
+            } else {
+              for (int hf = 0; hf < p.NH; ++hf) {
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk)  // K = 16: 32 bytes along a row of the dS box and of the W2^T boxes
+                  umma_bf16_ss_pair(tmem_base + hf * 256, umma_desc_kmajor<128>(a0) + 2 * kk,
+                                    umma_desc_kmajor<128>(b0 + hf * 2 * DH_BBOX) + 2 * kk, idesc, (kk > 0) ? 1u : acc0);
               }
             }
             umma_commit_pair_mc(&ctl->kempty[s], 3);
             if (kb == p.NK - 1) umma_commit_pair_mc(&ctl->acc_full, 3);
           }
           __syncwarp();
+          if (RNNT_DH_TRACE(p) && lane == 0 && rw.n < 4096) {
+            long long* t = p.trace + 3 * rw.n;
+            t[0] = tr0; t[1] = tr1; t[2] = clock64();
+          }
           rw.next_k();
         }
         for (int i = 0; i < p.NHI; ++i) rw.next_h();
       }
     }
-  } else {
+  } else if (warp == 12) {
+    // =========================== STORE WARP ===========================
+    // dpre lies where h lay (the epilogue warps overwrite the h blocks in place): one 128 x 64 TMA store per
+    // block as soon as all eight epilogue warps are done with it; a stage goes back to the producers when the
+    // stores of its blocks have read it.
+    if (lane == 0) {
+      RingWalk rw;
+      int it = 0;
+      for (int u = cid; u < n_units; u += ncl, ++it) {
+        const int tile = p.tile_lo + 2 * u + (int)rank;
+        const bool dead = tile >= p.tile_hi;  // odd tail: this CTA only keeps the pair's protocol going
+        for (int kb = 0; kb < p.NK; ++kb) rw.next_k();
+        for (int i = 0; i < p.NHI; ++i) {
+          const uint32_t s = rw.stage();
+          const int nb = min(3, HB - 3 * i);
+          for (int j = 0; j < nb; ++j) {
+            mbar_wait(&ctl->blk_done[3 * i + j], it & 1);
+            if (!dead && !(RNNT_DH_DBG(p) & 4)) {
+              tma_store_2d(&map_out, smem + s * DH_STAGE + j * DH_HBLK, (3 * i + j) * 64, tile * RNNT_TILE_M);
+              bulk_commit_group();
+            }
+          }
+          bulk_wait_group_read0();
+          mbar_arrive(&ctl->hempty[s]);
+          rw.next_h();
+        }
+      }
+      bulk_wait_group0();  // all stores have landed
+    }
+  } else if (warp < 8) {
     // =========================== EPILOGUE (warps 0-7) ===========================
     // Warp w reads TMEM lanes 32*(w&3).. (thread = row of the tile) and the 32-column groups g = (w>>2),
-    // (w>>2)+2, ... in increasing order: all eight warps work through the low columns first.
+    // (w>>2)+2, ...: in its i-th round every warp works on h block i (64 columns = two groups).
     const int q = warp & 3, sub = warp >> 2;
     const int row = q * 32 + lane;
-    uint8_t* stage_w = smem_out + warp * 4096;
     const int ngroups = p.H / 32;
     RingWalk rw;
-    uint32_t nstore = 0;
     int it = 0;
     for (int u = cid; u < n_units; u += ncl, ++it) {
-      const int tile = p.tile_lo + 2 * u + (int)rank;
-      const bool dead = tile >= p.tile_hi;  // odd tail: this CTA only keeps the pair's protocol going
       for (int kb = 0; kb < p.NK; ++kb) rw.next_k();
+      const long long tr0 = RNNT_DH_TRACE(p) ? clock64() : 0;
       mbar_wait(&ctl->acc_full, it & 1);
+      const long long tr1 = RNNT_DH_TRACE(p) ? clock64() : 0;
       tc_fence_after();
       int cur_item = -1;
       uint32_t cur_stage = 0;
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-      for (int g = sub; g < ngroups; g += 2) {
+      // One 32-column group: the group's accumulators have landed in zc; the next group's TMEM load (into zn) is
+      // issued first and flies while this group is multiplied by the tanh derivative and written over h.
+      auto group = [&](float (&zc)[32], float (&zn)[32], int g) {
         const int blk = g >> 1, item = blk / 3;
-        while (cur_item < item) {  // items arrive in order; every warp takes and releases every item
-          if (cur_item >= 0) {
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&ctl->hempty[cur_stage]);
-          }
+        while (cur_item < item) {  // H items arrive in order; every warp follows every one of them
           cur_stage = rw.stage();
           mbar_wait(&ctl->hfull[cur_stage], rw.h_parity());
           rw.next_h();
           ++cur_item;
         }
-        float z[32];
-        tmem_ld_32x32(taddr + g * 32, z);
-        const uint8_t* hrow = smem + cur_stage * DH_STAGE + (blk - 3 * item) * DH_HBLK + row * 128;
+        uint8_t* hrow = smem + cur_stage * DH_STAGE + (blk - 3 * item) * DH_HBLK + row * 128;
         uint4 hv[4];
 #pragma unroll
         for (int c = 0; c < 4; ++c)
           hv[c] = *reinterpret_cast<const uint4*>(hrow + ((((g & 1) * 4 + c) ^ (row & 7)) << 4));
-        tmem_ld_wait();
-        if (g + 2 >= ngroups) {  // last TMEM read of the unit: hand the accumulators back
+        tmem_ld_wait();  // this group's accumulators
+        if (g + 2 < ngroups) {
+          tmem_ld_32x32(taddr + (g + 2) * 32, zn);
+        } else {  // last TMEM read of the unit: hand the accumulators back
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&ctl->acc_empty), 0));
         }
-        uint32_t o[16];
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           const uint32_t hw[4] = {hv[c].x, hv[c].y, hv[c].z, hv[c].w};
+          uint32_t o[4];
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const float h0 = __uint_as_float(hw[j] << 16), h1 = __uint_as_float(hw[j] & 0xffff0000u);
-            o[c * 4 + j] = pack2_bf16(z[c * 8 + 2 * j] * fmaf(-h0, h0, 1.f), z[c * 8 + 2 * j + 1] * fmaf(-h1, h1, 1.f));
+            o[j] = pack2_bf16(zc[c * 8 + 2 * j] * fmaf(-h0, h0, 1.f), zc[c * 8 + 2 * j + 1] * fmaf(-h1, h1, 1.f));
           }
+          *reinterpret_cast<uint4*>(hrow + ((((g & 1) * 4 + c) ^ (row & 7)) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
         }
-        // 32 rows x 32 columns of bf16 -> this warp's staging tile (64-byte rows, SWIZZLE_64B) -> TMA store
-        uint8_t* sb = stage_w + (nstore & 1) * 2048;
-        if (lane == 0) bulk_wait_group_read1();  // the store issued two tiles ago has read its buffer
+        fence_proxy_async_smem();  // the TMA store (async proxy) reads what this thread wrote
         __syncwarp();
-        uint8_t* srow = sb + lane * 64;
-        const int swz = (lane >> 1) & 3;
-#pragma unroll
-        for (int c = 0; c < 4; ++c)
-          *reinterpret_cast<uint4*>(srow + ((c ^ swz) << 4)) = make_uint4(o[4 * c], o[4 * c + 1], o[4 * c + 2], o[4 * c + 3]);
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0 && !dead) {
-          tma_store_2d(&map_out, sb, g * 32, tile * RNNT_TILE_M + q * 32);
-          bulk_commit_group();
+        if (lane == 0) mbar_arrive(&ctl->blk_done[blk]);
+      };
+      if (!(RNNT_DH_DBG(p) & 1)) {
+        float z0[32], z1[32];
+        tmem_ld_32x32(taddr + sub * 32, z0);
+        for (int g = sub; g < ngroups; g += 4) {  // ngroups / 2 groups per warp: 2, 4 or 8 (even)
+          group(z0, z1, g);
+          group(z1, z0, g + 2);
         }
-        ++nstore;
+      } else {  // tuning build: barriers only (what the unit costs without its epilogue work)
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&ctl->acc_empty), 0));
+        for (int b = 0; b < HB; ++b)
+          if (lane == 0) mbar_arrive(&ctl->blk_done[b]);
       }
-      while (cur_item < p.NHI - 1) {  // (never taken for the supported H: every warp reads every item)
-        if (cur_item >= 0) {
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&ctl->hempty[cur_stage]);
-        }
+      while (cur_item < p.NHI - 1) {  // (only in the barriers-only mode: every warp reads every item otherwise)
         cur_stage = rw.stage();
         mbar_wait(&ctl->hfull[cur_stage], rw.h_parity());
         rw.next_h();
         ++cur_item;
       }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&ctl->hempty[cur_stage]);
+      if (RNNT_DH_TRACE(p) && threadIdx.x == 0 && it < 4096) {
+        long long* t = p.trace + 2 * 3 * 4096 + 3 * it;
+        t[0] = tr0; t[1] = tr1; t[2] = clock64();
+      }
     }
-    if (lane == 0) bulk_wait_group0();  // all of this warp's stores have landed
   }
   __syncwarp();
   tc_fence_before();
@@ -433,12 +501,12 @@ dpd_final_kernel(const float* __restrict__ part_dec, const int32_t* __restrict__
 
 extern "C" int rnnt_b200_dh_gemm_supported(int H) { return (H == 128 || H == 256 || H == 512) ? 1 : 0; }
 
-extern "C" int rnnt_b200_dh_gemm(const void* ds_bf16, const void* w2_bf16, const void* h_stash, int V, int H,
+extern "C" int rnnt_b200_dh_gemm(const void* ds_bf16, const void* w2t_bf16, const void* h_stash, int V, int H,
                                  int tile_cap, int tile_lo, int tile_hi, void* dpre_bf16, void* stream) {
-  if (!ds_bf16 || !w2_bf16 || !h_stash || !dpre_bf16) return RNNT_B200_E_NULL;
+  if (!ds_bf16 || !w2t_bf16 || !h_stash || !dpre_bf16) return RNNT_B200_E_NULL;
   if (V <= 0 || !rnnt_b200_dh_gemm_supported(H)) return RNNT_B200_E_SHAPE;
   if (tile_cap < 1 || tile_lo < 0 || tile_hi < tile_lo || tile_hi > tile_cap) return RNNT_B200_E_SHAPE;
-  if ((reinterpret_cast<uintptr_t>(ds_bf16) & 127u) || (reinterpret_cast<uintptr_t>(w2_bf16) & 127u) ||
+  if ((reinterpret_cast<uintptr_t>(ds_bf16) & 127u) || (reinterpret_cast<uintptr_t>(w2t_bf16) & 127u) ||
       (reinterpret_cast<uintptr_t>(h_stash) & 127u) || (reinterpret_cast<uintptr_t>(dpre_bf16) & 127u))
     return RNNT_B200_E_ALIGN;
   if (tile_hi == tile_lo) return RNNT_B200_OK;
@@ -449,11 +517,11 @@ extern "C" int rnnt_b200_dh_gemm(const void* ds_bf16, const void* w2_bf16, const
   CUtensorMap mds, mw2, mh, mout;
   rc = make_map_bf16(&mds, ds_bf16, rows, (uint64_t)Vds, (uint64_t)Vds, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc != RNNT_B200_OK) return rc;
-  rc = make_map_bf16(&mw2, w2_bf16, (uint64_t)Vpad, (uint64_t)H, (uint64_t)H, 64, 64, CU_TENSOR_MAP_SWIZZLE_128B);
+  rc = make_map_bf16(&mw2, w2t_bf16, (uint64_t)H, (uint64_t)Vpad, (uint64_t)Vpad, 64, 64, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc != RNNT_B200_OK) return rc;
   rc = make_map_bf16(&mh, h_stash, all_rows, (uint64_t)H, (uint64_t)rnnt_hp(H), 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc != RNNT_B200_OK) return rc;
-  rc = make_map_bf16(&mout, dpre_bf16, all_rows, (uint64_t)H, (uint64_t)H, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B);
+  rc = make_map_bf16(&mout, dpre_bf16, all_rows, (uint64_t)H, (uint64_t)H, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc != RNNT_B200_OK) return rc;
   DhParams p;
   p.H = H;
@@ -463,6 +531,7 @@ extern "C" int rnnt_b200_dh_gemm(const void* ds_bf16, const void* w2_bf16, const
   p.NHI = (H / 64 + 2) / 3;
   p.tile_lo = tile_lo;
   p.tile_hi = tile_hi;
+  p.debug = rnnt_tune_int("RNNT_B200_DH_DEBUG", 0);
   const int n_units = (tile_hi - tile_lo + 1) / 2;
   const int pairs = sm_count() / 2;
   const int grid = 2 * (n_units < pairs ? n_units : pairs);
@@ -478,8 +547,25 @@ extern "C" int rnnt_b200_dh_gemm(const void* ds_bf16, const void* w2_bf16, const
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  p.trace = nullptr;
+#ifdef RNNT_B200_TUNE
+  const char* trace_path = getenv("RNNT_B200_DH_TRACE");  // tuning build only: allocates, synchronises, writes a file
+  const size_t trace_bytes = 3 * 4096 * 3 * sizeof(long long);
+  if (trace_path && cudaMalloc(&p.trace, trace_bytes) == cudaSuccess) cudaMemsetAsync(p.trace, 0, trace_bytes, cfg.stream);
+#endif
   e = cudaLaunchKernelEx(&cfg, dh_gemm_kernel, mds, mw2, mh, mout, p);
   if (e != cudaSuccess) return (int)e;
+#ifdef RNNT_B200_TUNE
+  if (p.trace) {
+    long long* host = (long long*)malloc(trace_bytes);
+    cudaStreamSynchronize(cfg.stream);
+    cudaMemcpy(host, p.trace, trace_bytes, cudaMemcpyDeviceToHost);
+    FILE* f = fopen(trace_path, "wb");
+    if (f) { fwrite(host, 1, trace_bytes, f); fclose(f); }
+    free(host);
+    cudaFree(p.trace);
+  }
+#endif
   return RNNT_B200_OK;
 }
 

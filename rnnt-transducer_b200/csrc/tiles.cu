@@ -43,6 +43,24 @@ pack_vocab_kernel(const float* __restrict__ w2, const float* __restrict__ b2, in
   }
 }
 
+// w2t[j][v] = bf16(w2[v][j]) for v < V, 0 for V <= v < Vpad: the K-major B operand of the dh GEMM (contraction over v).
+// 32 x 32 tiles through shared memory: coalesced reads along j, coalesced writes along v.
+__global__ void __launch_bounds__(256)
+pack_vocab_t_kernel(const float* __restrict__ w2, int V, int Vpad, int H, __nv_bfloat16* __restrict__ w2t) {
+  __shared__ float tile[32][33];
+  const int v0 = blockIdx.x * 32, j0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  for (int r = ty; r < 32; r += 8) {
+    const int v = v0 + r, j = j0 + tx;
+    tile[r][tx] = (v < V && j < H) ? w2[(size_t)v * H + j] : 0.f;
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    const int j = j0 + r, v = v0 + tx;
+    if (j < H && v < Vpad) w2t[(size_t)j * Vpad + v] = __float2bfloat16_rn(tile[tx][r]);
+  }
+}
+
 // out[i] = parts[0][i] + parts[1][i] + ... in slot order: the deterministic end of a split-K GEMM
 __global__ void __launch_bounds__(256)
 sum_partials_kernel(const float* __restrict__ parts, int nparts, long long n, float* __restrict__ out) {
@@ -97,7 +115,7 @@ extern "C" int rnnt_b200_ds_pitch(int V) {
 }
 
 extern "C" int rnnt_b200_pack_vocab(const float* w2, const float* b2, int V, int H, void* w2_bf16,
-                                    float* b2_log2, void* stream) {
+                                    float* b2_log2, void* w2t_bf16, void* stream) {
   if (!w2 || !b2 || !w2_bf16 || !b2_log2) return RNNT_B200_E_NULL;
   if (V <= 0 || H <= 0) return RNNT_B200_E_SHAPE;
   const int Vpad = rnnt_b200_vocab_pad(V);
@@ -107,6 +125,11 @@ extern "C" int rnnt_b200_pack_vocab(const float* w2, const float* b2, int V, int
   pack_vocab_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w2, b2, V, Vpad, H,
                                                            (__nv_bfloat16*)w2_bf16, b2_log2);
   RNNT_CUDA_RETURN_IF_ERROR();
+  if (w2t_bf16) {
+    pack_vocab_t_kernel<<<dim3((Vpad + 31) / 32, (H + 31) / 32), 256, 0, (cudaStream_t)stream>>>(
+        w2, V, Vpad, H, (__nv_bfloat16*)w2t_bf16);
+    RNNT_CUDA_RETURN_IF_ERROR();
+  }
   return RNNT_B200_OK;
 }
 

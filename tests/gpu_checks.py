@@ -292,7 +292,7 @@ def dh_gemm_vs_torch(tiles, V, H, lo=0, hi=None, seed=0):
     w2q = torch.zeros(Vpad, H, dtype=torch.bfloat16)
     w2q[:V] = (torch.randn(V, H, generator=g) * 0.05).to(torch.bfloat16)
     h = torch.tanh(torch.randn(tiles * 128, H, generator=g)).to(torch.bfloat16)
-    dsd, w2d, hd = ds.to(DEV), w2q.to(DEV), h.to(DEV)
+    dsd, w2d, hd = ds.to(DEV), w2q.t().contiguous().to(DEV), h.to(DEV)   # the kernel takes W2 transposed (H, Vpad)
     dpre = torch.full((tiles * 128, H), 7.0, dtype=torch.bfloat16, device=DEV)
     st = torch.cuda.current_stream().cuda_stream
     rc = L.rnnt_b200_dh_gemm(dsd.data_ptr(), w2d.data_ptr(), hd.data_ptr(), V, H, tiles, lo, hi, dpre.data_ptr(), st)

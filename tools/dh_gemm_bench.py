@@ -15,11 +15,12 @@ for tiles in [int(a) for a in sys.argv[1:]] or [3256, 3108, 2960]:
     ds = (torch.randn(rows, Vds, device=dev, generator=g) * 0.05).to(torch.bfloat16)
     w2 = torch.zeros(Vpad, H, dtype=torch.bfloat16, device=dev)
     w2[:V] = (torch.randn(V, H, device=dev, generator=g) * 0.05).to(torch.bfloat16)
+    w2t = w2.t().contiguous()
     h = torch.tanh(torch.randn(rows, H, device=dev, generator=g)).to(torch.bfloat16)
     dpre = torch.empty(rows, H, dtype=torch.bfloat16, device=dev)
 
     def own():
-        rc = L.rnnt_b200_dh_gemm(ds.data_ptr(), w2.data_ptr(), h.data_ptr(), V, H, tiles, 0, tiles, dpre.data_ptr(), st)
+        rc = L.rnnt_b200_dh_gemm(ds.data_ptr(), w2t.data_ptr(), h.data_ptr(), V, H, tiles, 0, tiles, dpre.data_ptr(), st)
         assert rc == 0, rc
 
     def lib():
