@@ -73,6 +73,25 @@ int rnnt_b200_lattice(const float* lp_blank, const float* lp_label,
                       float* c_blank, float* c_label,
                       float* loss, double* loss64, void* stream);
 
+/* rnnt_b200_lattice without a caller-supplied workspace, for callers that cannot allocate (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE.
+ * Same inputs, outputs and results as rnnt_b200_lattice; the float64 alpha / beta
+ * planes live in a file-scope device array inside the library (2 x (RNNT_B200_STATIC_PLANE_ELEMS +
+ * RNNT_B200_STATIC_MAX_B) doubles = 32 MiB + 16 KiB, held by every GPU that loads the library until exit).
+ * Limits: B <= RNNT_B200_STATIC_MAX_B and rnnt_b200_plane_elems(B,T,U1) <= RNNT_B200_STATIC_PLANE_ELEMS (covers
+ * B=32,T=500,U=100); beyond them RNNT_B200_E_WORKSPACE is returned and nothing is launched. Calls no cudaMalloc /
+ * cudaFree or any allocating routine. The first call on a device resolves the array's address
+ * (cudaGetSymbolAddress; make one call before starting a capture). All calls on a device share the array, which
+ * keeps the previous call's contents (every cell is written before it is read: nothing needs clearing); calls
+ * that overlap on the GPU (other streams / threads) RACE on it -- serialise them. */
+#define RNNT_B200_STATIC_PLANE_ELEMS (1 << 21)
+#define RNNT_B200_STATIC_MAX_B 1024
+int rnnt_b200_lattice_static(const float* lp_blank, const float* lp_label,
+                             const int32_t* act_lens, const int32_t* label_lens,
+                             int B, int T, int U1,
+                             float* c_blank, float* c_label,
+                             float* loss, double* loss64, void* stream);
+
 /* d loss / d logits for boundary 1 (the autograd backward of model.py:70):
  *   g[b,t,u,v] = scale[b] * ( exp(logit - lse)*(c_blank+c_label) - [v=blank] c_blank
  *                             - [v=labels[b,u]] c_label ),   0 outside the valid window.

@@ -24,6 +24,7 @@ SIGNATURES = {
     "rnnt_b200_plane_elems": (ctypes.c_size_t, [_i, _i, _i]),
     "rnnt_b200_logits_to_planes": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _i, _p, _p, _p, _p]),
     "rnnt_b200_lattice": (_i, [_p, _p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p]),
+    "rnnt_b200_lattice_static": (_i, [_p, _p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _p]),
     "rnnt_b200_planes_to_dlogits": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p]),
     "rnnt_b200_max_tiles": (_i, [_i, _i, _i]),
     "rnnt_b200_build_tiles": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p, _p]),

@@ -211,3 +211,51 @@ extern "C" int rnnt_b200_lattice(const float* lp_blank, const float* lp_label,
   RNNT_CUDA_RETURN_IF_ERROR();
   return RNNT_B200_OK;
 }
+
+// ---------------------------------------------------------------------------------------
+// rnnt_b200_lattice_static: rnnt_b200_lattice for callers that cannot allocate (CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc). The float64 alpha / beta workspace lives in a file-scope device array
+// of RNNT_B200_STATIC_PLANE_ELEMS + RNNT_B200_STATIC_MAX_B doubles per plane (2 x 16 MiB + 16 KiB: every GPU that
+// loads the library holds it until exit). No counterpart in the reference.
+// Every call on a device shares the array, which keeps the last call's contents: the kernels write every
+// alpha / beta cell (and both log-likelihood slots) before reading it, so nothing has to start at zero -- but two
+// calls that overlap on one GPU (two streams, two threads) race on it.
+// ---------------------------------------------------------------------------------------
+namespace {
+constexpr size_t kStaticPlane = (size_t)RNNT_B200_STATIC_PLANE_ELEMS + (size_t)RNNT_B200_STATIC_MAX_B;
+}
+static __device__ __align__(256) double g_lattice_scratch[2 * kStaticPlane];
+
+// Device address of the scratch array on the CURRENT device. In host code `g_lattice_scratch` is only a stand-in
+// for the symbol, not a device address: the address comes from cudaGetSymbolAddress, once per device.
+static int lattice_static_scratch(double** out) {
+  static double* cached[64];  // per device ordinal; benign race (every writer stores the same value)
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev >= 0 && dev < 64 && cached[dev]) { *out = cached[dev]; return RNNT_B200_OK; }
+  double* ptr = nullptr;
+  e = cudaGetSymbolAddress((void**)&ptr, g_lattice_scratch);
+  if (e != cudaSuccess) return (int)e;
+  if (!ptr) return RNNT_B200_E_DRIVER;
+  if (dev >= 0 && dev < 64) cached[dev] = ptr;
+  *out = ptr;
+  return RNNT_B200_OK;
+}
+
+extern "C" int rnnt_b200_lattice_static(const float* lp_blank, const float* lp_label,
+                                        const int32_t* act_lens, const int32_t* label_lens,
+                                        int B, int T, int U1, float* c_blank, float* c_label,
+                                        float* loss, double* loss64, void* stream) {
+  if (!lp_blank || !lp_label || !act_lens || !label_lens || !c_blank || !c_label || !loss) return RNNT_B200_E_NULL;
+  if (B <= 0 || T <= 0 || U1 <= 0 || U1 > 1024) return RNNT_B200_E_SHAPE;
+  // the fixed scratch holds B <= RNNT_B200_STATIC_MAX_B utterances and B*(T+U1-1)*U1 <= RNNT_B200_STATIC_PLANE_ELEMS cells
+  if (B > RNNT_B200_STATIC_MAX_B || rnnt_b200_plane_elems(B, T, U1) > (size_t)RNNT_B200_STATIC_PLANE_ELEMS)
+    return RNNT_B200_E_WORKSPACE;
+  double* scratch = nullptr;
+  const int rc = lattice_static_scratch(&scratch);
+  if (rc != RNNT_B200_OK) return rc;
+  // rnnt_b200_lattice keeps its two log-likelihood slots right behind the plane_elems(B,T,U1) cells of each plane
+  return rnnt_b200_lattice(lp_blank, lp_label, act_lens, label_lens, B, T, U1, scratch, scratch + kStaticPlane,
+                           c_blank, c_label, loss, loss64, stream);
+}
