@@ -57,11 +57,25 @@ class Optimizer:
     def zero_grad(self):
         self.optimizer.zero_grad(set_to_none=True)
 
+    # implementation-only switches of torch's optimisers: kept out of checkpoints so that the reference's plain
+    # optim.SGD / Adam (rnnt/optim.py) loads them unchanged, and kept as configured here when loading
+    _IMPL_KEYS = ("fused", "foreach", "capturable", "differentiable")
+
     def state_dict(self):
-        return self.optimizer.state_dict()
+        sd = self.optimizer.state_dict()
+        sd["param_groups"] = [{k: v for k, v in g.items() if k not in self._IMPL_KEYS} for g in sd["param_groups"]]
+        return sd
 
     def load_state_dict(self, state_dict):
-        self.optimizer.load_state_dict(state_dict)
+        mine = self.optimizer.param_groups
+        groups = []
+        for i, g in enumerate(state_dict["param_groups"]):
+            g = {k: v for k, v in g.items() if k not in self._IMPL_KEYS}
+            if i < len(mine):
+                g.update({k: mine[i][k] for k in self._IMPL_KEYS if k in mine[i]})
+            groups.append(g)
+        self.optimizer.load_state_dict({"state": state_dict["state"], "param_groups": groups})
+        self.lr = self.optimizer.param_groups[0]["lr"]   # the decayed rate the checkpoint carries
 
     def decay_lr(self):
         self.lr *= self.decay_ratio

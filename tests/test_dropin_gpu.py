@@ -27,6 +27,8 @@ def test_golden(name):
     ((1, 1, 0, 4232), "full"),         # T=1, U=0
     ((2, 3, 40, 64), "full"),          # U+1 > 32: several warps per lattice CTA
     ((1, 300, 200, 8), "ragged"),      # long lattice, tiny vocabulary
+    ((1, 12, 230, 8), "full"),         # U+1 in 225..256: 32 KB ring + the 16 KB static exchange array need the
+    ((2, 9, 255, 8), "ragged"),        # shared-memory opt-in (the launch failed without it)
 ])
 def test_synthetic(shape, mode):
     m = G.dropin_synth(*shape, mode=mode)

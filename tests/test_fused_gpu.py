@@ -1,10 +1,15 @@
 """Boundary 2 (fused joint + loss, bf16 tensor-core GEMM, logits never materialised).
 
-Stated bf16-path tolerances (measured first, then fixed here -- DESIGN.md "Tolerances"):
+Stated bf16-path tolerances. Measured first on B200 over every case of this file (tools/parity_report.py ->
+profiles/r02_parity.json), then fixed at about twice the worst case found, per tensor (DESIGN.md section 4 says
+which rounding owns which share):
   vs the float64 oracle fed the SAME bf16-rounded h and W2 (isolates kernel error):
-      per-utterance loss 2e-5 relative; gradients rel-L2 1e-2 (dS is staged in bf16)
-  vs the full-precision float64 oracle (kernel + operand quantisation):
-      per-utterance loss 2e-3 relative; gradients rel-L2 3e-2
+      per-utterance loss 5e-6 relative (worst 2.4e-6); gradients rel-L2: enc 7.5e-3, dec 6e-3, w1 / b1 7e-3
+      (worst 3.0e-3 .. 3.7e-3, all at the single-cell case where nothing averages the bf16 rounding of dS and
+      dpre; 2e-3 / 4e-4 at the BASELINE shapes), w2 2.5e-3 (worst 1.1e-3), b2 2e-3 (worst 8.3e-4)
+  vs the full-precision float64 oracle (kernel + operand quantisation of h and W2):
+      per-utterance loss 4e-4 relative (worst 1.8e-4: a one-frame utterance); gradients rel-L2 8.5e-3 (worst 4.2e-3),
+      w2 6.5e-3 (worst 3.1e-3), b2 2e-3 (worst 8.3e-4)
 """
 import pytest
 
@@ -13,14 +18,18 @@ from tests import gpu_checks as G
 pytestmark = pytest.mark.gpu
 
 GRADS = ["enc", "dec", "w1", "b1", "w2", "b2"]
+LOSS_Q, LOSS_FULL = 5e-6, 4e-4
+GRAD_Q = {"enc": 7.5e-3, "dec": 6e-3, "w1": 7e-3, "b1": 7e-3, "w2": 2.5e-3, "b2": 2e-3}
+GRAD_FULL = {"enc": 8.5e-3, "dec": 8.5e-3, "w1": 8.5e-3, "b1": 8.5e-3, "w2": 6.5e-3, "b2": 2e-3}
 
 
-def _assert_fused(m, loss_q=2e-5, loss_full=2e-3, grad_q=1e-2, grad_full=3e-2):
-    assert m["loss_rel_q"] < loss_q, m
-    assert m["loss_rel_full"] < loss_full, m
+def _assert_fused(m, full_grads=True):
+    assert m["loss_rel_q"] < LOSS_Q, m
+    assert m["loss_rel_full"] < LOSS_FULL, m
     for n in GRADS:
-        assert m[f"d{n}_rel_l2_q"] < grad_q, (n, m)
-        assert m[f"d{n}_rel_l2_full"] < grad_full, (n, m)
+        assert m[f"d{n}_rel_l2_q"] < GRAD_Q[n], (n, m)
+        if full_grads:
+            assert m[f"d{n}_rel_l2_full"] < GRAD_FULL[n], (n, m)
 
 
 @pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 512, 512), (128, 64, 128), (384, 192, 512)])
@@ -154,7 +163,7 @@ def test_dw2_gemm_writes_only_its_outputs(rows, V, H):
 
 
 # ---- BASELINE.json shapes against the per-utterance, t-chunked float64 oracle (SURVEY.md 8(c) "Large shapes") ----
-# Tolerances as above: quantised oracle 2e-5 loss / grad_q; full-precision oracle 2e-3 loss / grad_full.
+# Same tolerances as every other case of this file.
 def test_config0_aishell_cpu_shape_against_the_oracle():
     # BASELINE.json configs[0]: B=8, T=200, U=30 at the AISHELL joint, full lengths
     _assert_fused(G.fused_vs_large_oracle(8, 200, 30, 320, 320, 512, 4232, mode="full"))
@@ -174,10 +183,8 @@ def test_config2_aishell_sweep_shape_ragged_utterances_against_the_oracle():
 def test_config4_long_utterance_against_the_oracle():
     # BASELINE.json configs[4] (T=1500, U=200, V=4232): one full-length utterance; gradients against the
     # quantised oracle, loss against both
-    m = G.fused_vs_large_oracle(1, 1500, 200, 320, 320, 512, 4232, mode="full", full_grads=False)
-    assert m["loss_rel_q"] < 2e-5 and m["loss_rel_full"] < 2e-3, m
-    for n in GRADS:
-        assert m[f"d{n}_rel_l2_q"] < 1e-2, (n, m)
+    _assert_fused(G.fused_vs_large_oracle(1, 1500, 200, 320, 320, 512, 4232, mode="full", full_grads=False),
+                  full_grads=False)
 
 
 def test_full_size_properties_at_the_headline_shape():

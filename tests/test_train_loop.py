@@ -116,3 +116,24 @@ def test_training_and_validation_over_kaldi_directory():
     model.eval()
     x, xl, y, yl = next(iter(ds.loader(batch_size=3)))
     assert torch.isfinite(model(x, xl, y, yl)).all()
+
+
+def test_checkpoint_optimizer_entry_has_no_implementation_only_keys():
+    # 'fused' / 'foreach' in the saved param groups would switch the reference's plain optimiser
+    # (rnnt/optim.py) onto another code path when it loads the checkpoint (train.py:190, -mode continue)
+    import torch
+    import rnnt_transducer_b200 as R
+    lin = torch.nn.Linear(3, 2)
+    opt = R.Optimizer(lin.parameters(), dict(type="sgd", lr=0.5, momentum=0.9))
+    lin(torch.ones(1, 3)).sum().backward()
+    opt.step()
+    opt.decay_lr()
+    sd = opt.state_dict()
+    for g in sd["param_groups"]:
+        assert not {"fused", "foreach", "capturable", "differentiable"} & set(g)
+    plain = torch.optim.SGD(lin.parameters(), lr=0.1, momentum=0.9)     # what the reference constructs
+    plain.load_state_dict(sd)
+    assert plain.param_groups[0]["lr"] == opt.lr
+    other = R.Optimizer(lin.parameters(), dict(type="sgd", lr=0.5, momentum=0.9))
+    other.load_state_dict(plain.state_dict())                           # and back, from a reference checkpoint
+    assert other.lr == opt.lr and other.optimizer.param_groups[0]["lr"] == opt.lr
