@@ -282,33 +282,38 @@ def roofline_objects(R, wl, cells, ks, kern_ms, ms_step, steps, workload):
             continue
     from rnnt_transducer_b200 import _lib
     bn = _lib.lib().rnnt_b200_vocab_tile(V)                              # UMMA N of the vocabulary tiles
-    own = {"joint_fwd": (f"joint_kernel<{bn},0,0> (tcgen05 vocab GEMM + online LSE)", "joint_kernel_fwd_dram_bytes"),
+    own = {"joint_fwd": (f"joint_kernel<{bn},0,0> (tcgen05 vocab GEMM + online LSE)", "joint_kernel_fwd_dram_bytes", 1),
            "joint_bwd_ds": (f"joint_kernel<{bn},1,0> (tcgen05 vocab GEMM recompute + dS epilogue)",
-                            "joint_kernel_bwd_dram_bytes_per_chunk"),
-           "dh_gemm": ("dh_gemm_kernel (tcgen05 dS.W2, tanh-derivative epilogue)", "dh_gemm_dram_bytes_per_chunk"),
+                            "joint_kernel_bwd_dram_bytes_per_chunk", 1),
+           "dh_gemm": ("dh_gemm_kernel (tcgen05 dS.W2, tanh-derivative epilogue)", "dh_gemm_dram_bytes_per_chunk", 1),
            "dw2_gemm": ("dw2_wide_kernel / dw2_gemm_kernel (tcgen05 dS^T.[h|1], MN-major operands)",
-                        "dw2_gemm_dram_bytes_per_chunk")}
+                        "dw2_gemm_dram_bytes_per_chunk", 1),
+           # the two consumers of a dS chunk launched side by side on half of the SMs each, timed as one region:
+           # 2 x 2*H*V flop per cell
+           "dh_dw2_pair": ("dh_gemm_kernel || dw2_wide_kernel (side by side on two streams, half of the CTA pairs each)",
+                           "dh_dw2_pair_dram_bytes_per_chunk", 2)}
 
     def roof(k):
         ms = kern_ms.get(k, 0.0)
         n = max(len(ks.get(k, [])) // steps, 1)                          # launches per step (dS chunks)
-        ach = flops / (ms * 1e-3) / 1e12 if ms > 0 else 0.0              # = flop per launch / ms per launch
+        ach = own[k][2] * flops / (ms * 1e-3) / 1e12 if ms > 0 else 0.0  # = flop per launch / ms per launch
         return {"bound": "tensor", "kernel": own[k][0], "achieved": ach, "peak": peak, "unit": "TFLOP/s",
                 "frac": ach / peak, "frac_of_burst_peak": ach / burst,
                 "peak_source": peaks["source"] + " bf16_tflops_sustained (burst: bf16_tflops)",
                 "traffic": traffic_tab.get(own[k][1]), "traffic_source": f"{traffic_src} (committed ncu capture)",
                 "kernel_ms": ms / n, "launches_per_step": n, "share_of_step": ms / ms_step}
 
-    dominant = max(own, key=lambda k: kern_ms.get(k, 0.0))
+    # the kernel (or side-by-side pair) with the largest time per 2*H*V flop/cell of work it does
+    dominant = max(own, key=lambda k: kern_ms.get(k, 0.0) / own[k][2])
     total_alg = 6.0 * H * V * cells
     path = {"algorithmic_tflops": total_alg / (ms_step * 1e-3) / 1e12,
             "frac_of_sustained_peak": total_alg / (ms_step * 1e-3) / 1e12 / peak,
             "kernel_ms_one_step": {k: round(v, 4) for k, v in kern_ms.items()},
             # every vocabulary-sized GEMM of the step against the same peak (2*H*V flop per cell each;
             # joint_bwd_ds is the recompute: hardware work, not counted in the algorithmic 6*H*V)
-            "gemm_frac_of_sustained_peak": {k: round(flops / (kern_ms[k] * 1e-3) / 1e12 / peak, 4)
-                                            for k in ("joint_fwd", "joint_bwd_ds", "dh_gemm", "lib_gemm_dh", "dw2_gemm")
-                                            if kern_ms.get(k, 0.0) > 0}}
+            "gemm_frac_of_sustained_peak": {k: round(own.get(k, (0, 0, 1))[2] * flops / (kern_ms[k] * 1e-3) / 1e12 / peak, 4)
+                                            for k in ("joint_fwd", "joint_bwd_ds", "dh_gemm", "lib_gemm_dh", "dw2_gemm",
+                                                      "dh_dw2_pair") if kern_ms.get(k, 0.0) > 0}}
     return roof(dominant), roof("joint_fwd"), path
 
 

@@ -195,9 +195,14 @@ int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, const float
  * rnnt_b200_joint_bwd_ds for the same [tile_lo, tile_hi); h_stash and
  * dpre: (tile_cap*128, H) bf16, 128-byte aligned, rows tile*128 + r (dpre rows outside [tile_lo, tile_hi) are not
  * touched). H in {128, 256, 512} (rnnt_b200_dh_gemm_supported); other H: the caller forms dpre with library GEMMs. */
+/* sm_pairs (rnnt_b200_dh_gemm, rnnt_b200_dw2_gemm, rnnt_b200_dw2_splits): how many CTA pairs (= 2 SMs each) the
+ * launch may occupy; <= 0 or more than the device has: all of them. Both consumers of a dS chunk walk its rows front
+ * to back at the same rate per SM, so launched SIDE BY SIDE on two streams with half of the pairs each (37 + 37 on a
+ * B200) one HBM read of the chunk serves both through L2 (measured: the pair of kernels 9.7 instead of 10.1 ms per
+ * step at B=32,T=500,U=100). */
 int rnnt_b200_dh_gemm_supported(int H);
 int rnnt_b200_dh_gemm(const void* ds_bf16, const void* w2t_bf16, const void* h_stash, int V, int H,
-                      int tile_cap, int tile_lo, int tile_hi, void* dpre_bf16, void* stream);
+                      int tile_cap, int tile_lo, int tile_hi, int sm_pairs, void* dpre_bf16, void* stream);
 
 /* Fused backward, stage 3: the backward of the broadcast add that replaces the reference's repeat + cat
  * (rnnt/model.py:26-31), once per step over the whole dpre buffer:
@@ -213,15 +218,16 @@ int rnnt_b200_dpre_reduce(const void* dpre_bf16, const int32_t* act_lens, const 
 /* Fused backward, weight/bias gradient of project_layer for one staged dS chunk (rnnt/model.py:16,35):
  *   dw2_parts[s][v, j] = sum_{r in K split s} dS[r, v] * h[r, j]      (v < ds_pitch(V), j < H)
  *   db2_parts[s][v]   += sum_{r in K split s} dS[r, v]
- * for the s < rnnt_b200_dw2_splits(rows, V, H) K splits of the chunk. dw2_parts (splits, ds_pitch(V), H) float32 is
+ * for the s < rnnt_b200_dw2_splits(rows, V, H, sm_pairs) K splits of the chunk (split s takes the 64-row blocks
+ * s, s + splits, ...). dw2_parts (splits, ds_pitch(V), H) float32 is
  * stored (every element exactly once, no zeroing needed); db2_parts (splits, ds_pitch(V)) float32 must be zeroed
  * by the caller. The caller adds the partials of all chunks in slot order with rnnt_b200_sum_partials: the
  * result does not depend on the order in which CTAs finish (DETERMINISTIC).
  * ds: bf16, rows x rnnt_b200_ds_pitch(V), 128-byte aligned; h_rows: the chunk's first row of the h stash
  * (bf16, pitch rnnt_b200_h_pitch(H)); rows a multiple of 64; H in {128, 256, 512}. tcgen05 GEMM with both
  * operands MN-major; other H use the library GEMM against the ones column of the stash. */
-int rnnt_b200_dw2_splits(long long rows, int V, int H);
-int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long long rows, int V, int H,
+int rnnt_b200_dw2_splits(long long rows, int V, int H, int sm_pairs);
+int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long long rows, int V, int H, int sm_pairs,
                        float* dw2_parts, float* db2_parts, void* stream);
 
 /* out[i] = parts[0][i] + parts[1][i] + ... + parts[nparts-1][i], i < n, in that order. */

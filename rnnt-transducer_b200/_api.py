@@ -56,6 +56,7 @@ class KernelTimer:
         self.events = events
         self.records = []
         self.launches = 0
+        self.quiet = 0
 
     def __enter__(self):
         KernelTimer.active = self
@@ -78,7 +79,7 @@ def _call(name, fn, *args):
         _lib.check(fn(*args), "rnnt_b200_" + name)
         return
     kt.launches += KernelTimer.KERNELS[name]
-    if kt.events:
+    if kt.events and not kt.quiet:
         e0 = torch.cuda.Event(enable_timing=True)
         e1 = torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -90,10 +91,12 @@ def _call(name, fn, *args):
 
 
 class _region:
-    """Times a non-kernel region (library GEMMs) under an active KernelTimer; not a launch of ours."""
+    """Times a region of the current stream under an active KernelTimer (library GEMMs; kernels that run side by
+    side on two streams). ``quiet``: the own kernels launched inside are counted but not timed one by one."""
 
-    def __init__(self, name):
+    def __init__(self, name, quiet=False):
         self.name = name
+        self.quiet = quiet
 
     def __enter__(self):
         kt = KernelTimer.active
@@ -101,12 +104,30 @@ class _region:
         if kt is not None and kt.events:
             self.e0 = torch.cuda.Event(enable_timing=True)
             self.e0.record()
+            if self.quiet:
+                kt.quiet += 1
 
     def __exit__(self, *exc):
-        if self.e0 is not None and KernelTimer.active is not None:
+        kt = KernelTimer.active
+        if self.e0 is not None and kt is not None:
             e1 = torch.cuda.Event(enable_timing=True)
             e1.record()
-            KernelTimer.active.records.append((self.name, self.e0, e1))
+            kt.records.append((self.name, self.e0, e1))
+            if self.quiet:
+                kt.quiet -= 1
+
+
+_side_streams = {}
+
+
+def _side_stream(dev):
+    """One side stream per device for the kernels that run beside the current stream (created once: a new stream per
+    backward call would cost a cudaStreamCreate each)."""
+    key = (dev.type, dev.index if dev.index is not None else torch.cuda.current_device())
+    s = _side_streams.get(key)
+    if s is None:
+        s = _side_streams[key] = torch.cuda.Stream(device=dev)
+    return s
 
 
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
@@ -315,6 +336,11 @@ class _JointLossFn(torch.autograd.Function):
             # else library GEMMs (dW2/db2 against the ones column of the stash)
             own_gemm = H in (128, 256, 512)          # the stash has no ones column at these H (pitch == H)
             lib_dh = (not own_gemm) or os.environ.get("RNNT_B200_DH_LIB", "0") == "1"   # "1": A/B timing only
+            # dh and dW2 of a chunk run side by side (RNNT_B200_BWD_OVERLAP=0: one after the other, A/B timing only)
+            sms = torch.cuda.get_device_properties(dev).multi_processor_count
+            overlap = own_gemm and not lib_dh and os.environ.get("RNNT_B200_BWD_OVERLAP", "1") != "0"
+            side = _side_stream(dev) if overlap else None
+            half = max(1, sms // 4) if overlap else 0      # CTA pairs per consumer kernel (37 of 74 on a B200)
             chunk = max(2, min(max_tiles, _DS_BUDGET_BYTES // (128 * Vds * 2)))
             nchunk = -(-max_tiles // chunk)
             chunk = -(-max_tiles // nchunk)          # balanced chunks,
@@ -322,7 +348,6 @@ class _JointLossFn(torch.autograd.Function):
             # whole waves of the persistent backward kernels (one tile per SM and wave): with balanced chunks
             # every launch ends in a partial wave (AISHELL shape: 4 x 21.3 -> 4 x 22 waves); chunks of
             # k * SMs tiles leave one partial wave per step (22 + 22 + 22 + 19.3 -> 86 instead of 88)
-            sms = torch.cuda.get_device_properties(dev).multi_processor_count
             if chunk >= 4 * sms and os.environ.get("RNNT_B200_WAVE_CHUNK", "1") != "0":
                 up = -(-chunk // sms) * sms
                 if up * 128 * Vds * 2 <= max(_DS_BUDGET_BYTES, chunk * 128 * Vds * 2):
@@ -333,7 +358,7 @@ class _JointLossFn(torch.autograd.Function):
             dpre = torch.empty(max_tiles * 128, H, dtype=torch.bfloat16, device=dev)
             if own_gemm:
                 # split-K / per-chunk partial results, added in slot order at the end (deterministic)
-                nsplit = [L.rnnt_b200_dw2_splits((hi - lo) * 128, V, H) for lo, hi in bounds]
+                nsplit = [L.rnnt_b200_dw2_splits((hi - lo) * 128, V, H, half) for lo, hi in bounds]
                 dw2_parts = torch.empty(sum(nsplit), Vds, H, dtype=torch.float32, device=dev)
                 db2_parts = torch.zeros(sum(nsplit), Vds, dtype=torch.float32, device=dev)
             else:
@@ -354,12 +379,27 @@ class _JointLossFn(torch.autograd.Function):
                     hf = h_stash[lo * 128: hi * 128, :H].float()
                     dpre[lo * 128: hi * 128] = (dh.float() * (1.0 - hf * hf)).to(torch.bfloat16)
                 else:
+                    if overlap:
+                        # The two consumers of the dS chunk side by side, each on half of the CTA pairs: both walk
+                        # the chunk's rows front to back at the same rate, so one HBM read of dS serves both through
+                        # L2 (the pair 9.7 instead of 10.1 ms per step at the AISHELL shape: profiles/r02_notes.md).
+                        pair_region = _region("dh_dw2_pair", quiet=True)
+                        pair_region.__enter__()
+                        fork = torch.cuda.Event()
+                        fork.record()
+                        side.wait_event(fork)
                     _call("dh_gemm", L.rnnt_b200_dh_gemm, _ptr(dsc), _ptr(w2t), _ptr(h_stash), V, H, max_tiles, lo, hi,
-                          _ptr(dpre), st)
+                          half, _ptr(dpre), st)
                 if own_gemm:
                     _call("dw2_gemm", L.rnnt_b200_dw2_gemm, _ptr(dsc), h_stash.data_ptr() + lo * 128 * hp * 2,
-                          rows, V, H, dw2_parts.data_ptr() + slot * Vds * H * 4, db2_parts.data_ptr() + slot * Vds * 4, st)
+                          rows, V, H, half, dw2_parts.data_ptr() + slot * Vds * H * 4,
+                          db2_parts.data_ptr() + slot * Vds * 4, side.cuda_stream if overlap else st)
                     slot += nsplit[ci]
+                    if overlap:   # the next chunk's dS overwrites the staging buffer: join first
+                        join = torch.cuda.Event()
+                        join.record(side)
+                        torch.cuda.current_stream().wait_event(join)
+                        pair_region.__exit__(None, None, None)
                 else:
                     hc = h_stash[lo * 128: hi * 128]
                     with _region("lib_gemm_dw2"):

@@ -502,7 +502,7 @@ dpd_final_kernel(const float* __restrict__ part_dec, const int32_t* __restrict__
 extern "C" int rnnt_b200_dh_gemm_supported(int H) { return (H == 128 || H == 256 || H == 512) ? 1 : 0; }
 
 extern "C" int rnnt_b200_dh_gemm(const void* ds_bf16, const void* w2t_bf16, const void* h_stash, int V, int H,
-                                 int tile_cap, int tile_lo, int tile_hi, void* dpre_bf16, void* stream) {
+                                 int tile_cap, int tile_lo, int tile_hi, int sm_pairs, void* dpre_bf16, void* stream) {
   if (!ds_bf16 || !w2t_bf16 || !h_stash || !dpre_bf16) return RNNT_B200_E_NULL;
   if (V <= 0 || !rnnt_b200_dh_gemm_supported(H)) return RNNT_B200_E_SHAPE;
   if (tile_cap < 1 || tile_lo < 0 || tile_hi < tile_lo || tile_hi > tile_cap) return RNNT_B200_E_SHAPE;
@@ -533,7 +533,8 @@ extern "C" int rnnt_b200_dh_gemm(const void* ds_bf16, const void* w2t_bf16, cons
   p.tile_hi = tile_hi;
   p.debug = rnnt_tune_int("RNNT_B200_DH_DEBUG", 0);
   const int n_units = (tile_hi - tile_lo + 1) / 2;
-  const int pairs = sm_count() / 2;
+  const int all_pairs = sm_count() / 2;
+  const int pairs = (sm_pairs > 0 && sm_pairs < all_pairs) ? sm_pairs : all_pairs;
   const int grid = 2 * (n_units < pairs ? n_units : pairs);
   cudaError_t e = cudaFuncSetAttribute(dh_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DH_SMEM);
   if (e != cudaSuccess) return (int)e;

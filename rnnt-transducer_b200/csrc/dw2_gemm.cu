@@ -47,6 +47,7 @@ struct GwParams {
   int N;           // UMMA N of a unit: 256 (H a multiple of 256) or 128 (H = 128)
   int ksteps;      // 64-row K blocks in the chunk
   int splits, ks_per_split;
+  int interleave;  // dw2_wide_kernel: K split s takes the 64-row blocks s, s + splits, ... instead of a contiguous range
   int debug;  // RNNT_B200_DW2_DEBUG (timing experiments): 1 no ones-MMA, 2 no main MMA, 4 no epilogue adds, 8 no TMA loads, 16 no A reuse through the collector
 };
 
@@ -226,6 +227,14 @@ dw2_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
 // retired, release the stage, and add their partial sums with red.global.add at the end of the unit.
 // Warps as above: 0 dS TMA, 6 h TMA, 1 MMA issuer, 2-5 column sums during the K loop + epilogue.
 // ---------------------------------------------------------------------------------------
+// K blocks of split s: iteration k in [k0, k1) works on 64-row block base + (k - k0) * stride.
+struct GwRange { int k0, k1, base, stride; };
+__device__ __forceinline__ GwRange gw_range(const GwParams& p, int s) {
+  if (p.interleave) return {0, (p.ksteps - s + p.splits - 1) / p.splits, s, p.splits};
+  const int k0 = s * p.ks_per_split;
+  return {k0, min(p.ksteps, k0 + p.ks_per_split), k0, 1};
+}
+
 constexpr int GWW_STAGES = 4;
 constexpr int GWW_STAGE = 6 * GW_BLOCK;  // A: 2 boxes (128 v), B: 4 boxes (2 x 128 j)
 constexpr int GWW_CS = 128 * 8 * 4;      // column-sum exchange of the four epilogue warps
@@ -279,9 +288,11 @@ dw2_wide_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
       uint32_t stage = 0, phase = 0;
       for (int u = cid; u < n_units; u += ncl) {
         const int vt = u % p.nvt, s = u / p.nvt;
-        const int k0 = s * p.ks_per_split, k1 = min(p.ksteps, k0 + p.ks_per_split);
+        const GwRange kr = gw_range(p, s);
+        const int k0 = kr.k0, k1 = kr.k1;
         const int v0 = vt * 256 + (int)rank * 128;
         for (int k = k0; k < k1; ++k) {
+          const int kc = kr.base + (k - kr.k0) * kr.stride;  // the 64-row block of this iteration
           mbar_wait(&ctl->empty[stage], phase ^ 1);
           const uint32_t full = mapa_u32(smem_u32(&ctl->full[stage]), 0);
           const int nbox = is_a ? 2 : 4;
@@ -289,14 +300,14 @@ dw2_wide_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
           else mbar_arrive_cluster(full);
           uint8_t* st = smem + stage * GWW_STAGE + (is_a ? 0 : 2 * GW_BLOCK);
           if (is_a) {
-            tma_load_2d_pair(st, &map_ds, full, v0, k * 64);
-            tma_load_2d_pair(st + GW_BLOCK, &map_ds, full, v0 + 64, k * 64);
+            tma_load_2d_pair(st, &map_ds, full, v0, kc * 64);
+            tma_load_2d_pair(st + GW_BLOCK, &map_ds, full, v0 + 64, kc * 64);
           } else {
 #pragma unroll
             for (int hf = 0; hf < 2; ++hf) {  // this CTA's 128 of the 256 columns of each half of H
               const int j0 = hf * 256 + (int)rank * 128;
-              tma_load_2d_pair(st + (2 * hf) * GW_BLOCK, &map_h, full, j0, k * 64);
-              tma_load_2d_pair(st + (2 * hf + 1) * GW_BLOCK, &map_h, full, j0 + 64, k * 64);
+              tma_load_2d_pair(st + (2 * hf) * GW_BLOCK, &map_h, full, j0, kc * 64);
+              tma_load_2d_pair(st + (2 * hf + 1) * GW_BLOCK, &map_h, full, j0 + 64, kc * 64);
             }
           }
           if (++stage == GWW_STAGES) { stage = 0; phase ^= 1; }
@@ -311,7 +322,8 @@ dw2_wide_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
       int it = 0;
       for (int u = cid; u < n_units; u += ncl, ++it) {
         const int s = u / p.nvt;
-        const int k0 = s * p.ks_per_split, k1 = min(p.ksteps, k0 + p.ks_per_split);
+        const GwRange kr = gw_range(p, s);
+        const int k0 = kr.k0, k1 = kr.k1;
         mbar_wait(&ctl->acc_empty, (it & 1) ^ 1);
         tc_fence_after();
         for (int k = k0; k < k1; ++k) {
@@ -346,7 +358,8 @@ dw2_wide_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
     int it = 0;
     for (int u = cid; u < n_units; u += ncl, ++it) {
       const int vt = u % p.nvt, s = u / p.nvt;
-      const int k0 = s * p.ks_per_split, k1 = min(p.ksteps, k0 + p.ks_per_split);
+      const GwRange kr = gw_range(p, s);
+        const int k0 = kr.k0, k1 = kr.k1;
       // ---- column sums of this CTA's dS boxes while the UMMAs run ----
       float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       for (int k = k0; k < k1; ++k) {
@@ -418,14 +431,16 @@ dw2_wide_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
 // (24.7 / 25.1 against 24.3 / 24.8 ms in the same call): the chip sits at its power cap, the extra SMs only
 // lower the clock of everything else; alone, 1.455 against 1.431 ms.
 struct GwSplit { int splits, ks_per_split; bool wide; };
-static GwSplit gw_split(long long rows, int V, int H) {
+static GwSplit gw_split(long long rows, int V, int H, int sm_pairs) {
   GwSplit g;
   g.wide = (H == 512) && rnnt_tune_int("RNNT_B200_DW2_WIDE", 1) != 0;  // the 256 x 256 kernel at H = 512: A/B only
   const int Vds = rnnt_b200_ds_pitch(V);
   const int nvt = (Vds + 255) / 256;
   const int nj = g.wide ? 1 : H / (H >= 256 ? 256 : 128);
   const int ksteps = (int)(rows / 64);
-  int sw = (sm_count() / 2) / (nvt * nj);
+  const int all_pairs = sm_count() / 2;
+  const int pairs = (sm_pairs > 0 && sm_pairs < all_pairs) ? sm_pairs : all_pairs;
+  int sw = pairs / (nvt * nj);
   if (sw < 1) sw = 1;
   { const int e = rnnt_tune_int("RNNT_B200_DW2_SPLITS", 0); if (e >= 1) sw = e; }
   if (sw > ksteps) sw = ksteps;
@@ -437,13 +452,13 @@ static GwSplit gw_split(long long rows, int V, int H) {
   return g;
 }
 
-extern "C" int rnnt_b200_dw2_splits(long long rows, int V, int H) {
+extern "C" int rnnt_b200_dw2_splits(long long rows, int V, int H, int sm_pairs) {
   if (rows <= 0 || (rows & 63) || V <= 0 || !(H == 128 || H == 256 || H == 512)) return 0;
-  return gw_split(rows, V, H).splits;
+  return gw_split(rows, V, H, sm_pairs).splits;
 }
 
 extern "C" int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long long rows, int V, int H,
-                                  float* dw2_parts, float* db2_parts, void* stream) {
+                                  int sm_pairs, float* dw2_parts, float* db2_parts, void* stream) {
   if (!ds_bf16 || !h_rows || !dw2_parts || !db2_parts) return RNNT_B200_E_NULL;
   if (rows < 0 || (rows & 63) || V <= 0 || !(H == 128 || H == 256 || H == 512)) return RNNT_B200_E_SHAPE;
   if ((reinterpret_cast<uintptr_t>(ds_bf16) & 127u) || (reinterpret_cast<uintptr_t>(h_rows) & 15u) ||
@@ -460,7 +475,7 @@ extern "C" int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long 
   rc = make_map_bf16(&mh, h_rows, (uint64_t)rows, (uint64_t)H, (uint64_t)rnnt_hp(H), 64, 64,
                      CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc != RNNT_B200_OK) return rc;
-  const GwSplit g = gw_split(rows, V, H);
+  const GwSplit g = gw_split(rows, V, H, sm_pairs);
   GwParams p;
   p.dw2 = dw2_parts; p.db2 = db2_parts; p.Vds = Vds; p.H = H;
   p.nvt = (Vds + 255) / 256;
@@ -471,7 +486,11 @@ extern "C" int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long 
   p.ks_per_split = g.ks_per_split;
   p.debug = rnnt_tune_int("RNNT_B200_DW2_DEBUG", 0);
   const bool wide = g.wide;
-  const int pairs = sm_count() / 2;
+  const int all_pairs = sm_count() / 2;
+  const int pairs = (sm_pairs > 0 && sm_pairs < all_pairs) ? sm_pairs : all_pairs;
+  // interleaved K splits: all units of a launch walk the chunk's rows front to back together (h boxes shared
+  // through L2 by every unit, and the dS rows by a dh GEMM that runs beside this kernel: DESIGN.md 3.4)
+  p.interleave = (wide && rnnt_tune_int("RNNT_B200_DW2_INTERLEAVE", 1)) ? 1 : 0;
   const int units = wide ? p.splits * p.nvt : p.splits * p.nvt * p.nj;
   const int grid = 2 * (units < pairs ? units : pairs);
   cudaError_t e = wide ? cudaFuncSetAttribute(dw2_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GWW_SMEM)

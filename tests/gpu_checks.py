@@ -245,15 +245,15 @@ def full_size_properties(B=32, T=500, U=100, E=320, D=320, H=512, V=4232, seed=2
     return out
 
 
-def _dw2_run(L, ds, h, rows, V, H, Vds):
+def _dw2_run(L, ds, h, rows, V, H, Vds, sm_pairs=0):
     """One chunk through rnnt_b200_dw2_gemm + the ordered sum of its K-split partials."""
-    ns = L.rnnt_b200_dw2_splits(rows, V, H)
+    ns = L.rnnt_b200_dw2_splits(rows, V, H, sm_pairs)
     parts = torch.empty(ns, Vds, H, device=DEV)
     bparts = torch.zeros(ns, Vds, device=DEV)
     dw2 = torch.empty(Vds, H, device=DEV)
     db2 = torch.empty(Vds, device=DEV)
     st = torch.cuda.current_stream().cuda_stream
-    rc = L.rnnt_b200_dw2_gemm(ds.data_ptr(), h.data_ptr(), rows, V, H, parts.data_ptr(), bparts.data_ptr(), st)
+    rc = L.rnnt_b200_dw2_gemm(ds.data_ptr(), h.data_ptr(), rows, V, H, sm_pairs, parts.data_ptr(), bparts.data_ptr(), st)
     assert rc == 0, rc
     assert L.rnnt_b200_sum_partials(parts.data_ptr(), ns, Vds * H, dw2.data_ptr(), st) == 0
     assert L.rnnt_b200_sum_partials(bparts.data_ptr(), ns, Vds, db2.data_ptr(), st) == 0
@@ -261,7 +261,7 @@ def _dw2_run(L, ds, h, rows, V, H, Vds):
     return dw2, db2, ns
 
 
-def dw2_gemm_vs_torch(rows, V, H, seed=0):
+def dw2_gemm_vs_torch(rows, V, H, seed=0, sm_pairs=0):
     """rnnt_b200_dw2_gemm (tcgen05, MN-major operands, K-split partials added in slot order) against float64 torch
     products of the same bf16 operands; run twice: the two results must be bit-identical (deterministic)."""
     from rnnt_transducer_b200 import _lib
@@ -270,15 +270,15 @@ def dw2_gemm_vs_torch(rows, V, H, seed=0):
     g = torch.Generator().manual_seed(seed)
     ds = (torch.randn(rows, Vds, generator=g) * 0.05).to(torch.bfloat16).to(DEV)
     h = torch.tanh(torch.randn(rows, hp, generator=g)).to(torch.bfloat16).to(DEV)
-    dw2, db2, ns = _dw2_run(L, ds, h, rows, V, H, Vds)
-    dw2b, db2b, _ = _dw2_run(L, ds, h, rows, V, H, Vds)
+    dw2, db2, ns = _dw2_run(L, ds, h, rows, V, H, Vds, sm_pairs)
+    dw2b, db2b, _ = _dw2_run(L, ds, h, rows, V, H, Vds, sm_pairs)
     ref = ds.double().t() @ h[:, :H].double()
     refb = ds.double().sum(0)
     return {"dw2_rel_l2": rel_l2(dw2.cpu(), ref.cpu()), "db2_rel_l2": rel_l2(db2.cpu(), refb.cpu()), "splits": ns,
             "bit_identical": bool(torch.equal(dw2, dw2b) and torch.equal(db2, db2b))}
 
 
-def dh_gemm_vs_torch(tiles, V, H, lo=0, hi=None, seed=0):
+def dh_gemm_vs_torch(tiles, V, H, lo=0, hi=None, seed=0, sm_pairs=0):
     """rnnt_b200_dh_gemm on its own: dpre = (dS . W2q) * (1 - h^2) for tiles [lo, hi) of a stash of ``tiles`` tiles,
     against the float64 product of the same bf16 operands; rows outside [lo, hi) must stay untouched."""
     from rnnt_transducer_b200 import _lib
@@ -295,7 +295,7 @@ def dh_gemm_vs_torch(tiles, V, H, lo=0, hi=None, seed=0):
     dsd, w2d, hd = ds.to(DEV), w2q.t().contiguous().to(DEV), h.to(DEV)   # the kernel takes W2 transposed (H, Vpad)
     dpre = torch.full((tiles * 128, H), 7.0, dtype=torch.bfloat16, device=DEV)
     st = torch.cuda.current_stream().cuda_stream
-    rc = L.rnnt_b200_dh_gemm(dsd.data_ptr(), w2d.data_ptr(), hd.data_ptr(), V, H, tiles, lo, hi, dpre.data_ptr(), st)
+    rc = L.rnnt_b200_dh_gemm(dsd.data_ptr(), w2d.data_ptr(), hd.data_ptr(), V, H, tiles, lo, hi, sm_pairs, dpre.data_ptr(), st)
     torch.cuda.synchronize()
     assert rc == 0, rc
     hs = h[lo * 128: hi * 128].double()
@@ -462,13 +462,13 @@ def dw2_gemm_guard_bands(rows=192, V=300, H=128):
     g = torch.Generator().manual_seed(1)
     ds = (torch.randn(rows, Vds, generator=g) * 0.05).to(torch.bfloat16).to(DEV)
     h = torch.tanh(torch.randn(rows, hp, generator=g)).to(torch.bfloat16).to(DEV)
-    ns = L.rnnt_b200_dw2_splits(rows, V, H)
+    ns = L.rnnt_b200_dw2_splits(rows, V, H, 0)
     pad = 4096
     big = torch.full((pad + ns * Vds * H + pad,), 7.0, device=DEV)
     bigb = torch.full((pad + ns * Vds + pad,), 7.0, device=DEV)
     bigb[pad:pad + ns * Vds] = 0
     st = torch.cuda.current_stream().cuda_stream
-    rc = L.rnnt_b200_dw2_gemm(ds.data_ptr(), h.data_ptr(), rows, V, H, big.data_ptr() + pad * 4,
+    rc = L.rnnt_b200_dw2_gemm(ds.data_ptr(), h.data_ptr(), rows, V, H, 0, big.data_ptr() + pad * 4,
                               bigb.data_ptr() + pad * 4, st)
     torch.cuda.synchronize()
     ok = bool((big[:pad] == 7).all() and (big[pad + ns * Vds * H:] == 7).all() and

@@ -108,6 +108,15 @@ def test_dw2_gemm_matches_torch(rows, V, H):
     assert m["bit_identical"], m
 
 
+@pytest.mark.parametrize("pairs", [1, 5, 37])
+def test_gemms_on_a_share_of_the_sms(pairs):
+    # sm_pairs: the two consumers of a dS chunk run side by side on half of the CTA pairs each
+    m = G.dw2_gemm_vs_torch(8192, 4232, 512, sm_pairs=pairs)
+    assert m["dw2_rel_l2"] < 1e-5 and m["db2_rel_l2"] < 1e-5 and m["bit_identical"], m
+    m = G.dh_gemm_vs_torch(90, 777, 512, 3, 88, sm_pairs=pairs)
+    assert m["rel_l2"] < 4e-3 and m["outside_untouched"], m
+
+
 @pytest.mark.parametrize("tiles,V,H,lo,hi", [
     (2, 200, 512, 0, 2), (1, 64, 128, 0, 1), (3, 300, 256, 0, 3),
     (5, 4232, 512, 1, 4),       # AISHELL vocabulary, odd chunk (dead peer tile), rows outside the chunk untouched

@@ -127,24 +127,24 @@ def test_fold_output_projections_algebra():
 def test_dw2_gemm_rejects_bad_arguments():
     L = _lib.lib()
     a = 256  # aligned fake pointer: argument checks run before anything is dereferenced
-    assert L.rnnt_b200_dw2_gemm(None, a, 128, 100, 512, a, a, None) == -1
-    assert L.rnnt_b200_dw2_gemm(a, a, 100, 100, 512, a, a, None) == -2      # rows % 64
-    assert L.rnnt_b200_dw2_gemm(a, a, 128, 100, 192, a, a, None) == -2      # H not in {128, 256, 512}
-    assert L.rnnt_b200_dw2_gemm(a + 2, a, 128, 100, 512, a, a, None) == -4  # alignment
-    assert L.rnnt_b200_dw2_gemm(a, a, 0, 100, 512, a, a, None) == 0         # nothing to do
-    assert L.rnnt_b200_dw2_splits(100, 100, 512) == 0 and L.rnnt_b200_dw2_splits(128, 100, 192) == 0
-    assert L.rnnt_b200_dw2_splits(64, 100, 512) == 1                        # one K block: one split
+    assert L.rnnt_b200_dw2_gemm(None, a, 128, 100, 512, 0, a, a, None) == -1
+    assert L.rnnt_b200_dw2_gemm(a, a, 100, 100, 512, 0, a, a, None) == -2      # rows % 64
+    assert L.rnnt_b200_dw2_gemm(a, a, 128, 100, 192, 0, a, a, None) == -2      # H not in {128, 256, 512}
+    assert L.rnnt_b200_dw2_gemm(a + 2, a, 128, 100, 512, 0, a, a, None) == -4  # alignment
+    assert L.rnnt_b200_dw2_gemm(a, a, 0, 100, 512, 0, a, a, None) == 0         # nothing to do
+    assert L.rnnt_b200_dw2_splits(100, 100, 512, 0) == 0 and L.rnnt_b200_dw2_splits(128, 100, 192, 0) == 0
+    assert L.rnnt_b200_dw2_splits(64, 100, 512, 0) == 1 and L.rnnt_b200_dw2_splits(64000, 4232, 512, 37) == 2                       # one K block: one split
 
 
 def test_dh_gemm_and_reduce_reject_bad_arguments():
     L = _lib.lib()
     a = 256
     assert L.rnnt_b200_dh_gemm_supported(512) == 1 and L.rnnt_b200_dh_gemm_supported(192) == 0
-    assert L.rnnt_b200_dh_gemm(None, a, a, 100, 512, 4, 0, 4, a, None) == -1
-    assert L.rnnt_b200_dh_gemm(a, a, a, 100, 192, 4, 0, 4, a, None) == -2      # H not in {128, 256, 512}
-    assert L.rnnt_b200_dh_gemm(a, a, a, 100, 512, 4, 2, 5, a, None) == -2      # tile_hi > tile_cap
-    assert L.rnnt_b200_dh_gemm(a + 16, a, a, 100, 512, 4, 0, 4, a, None) == -4  # alignment
-    assert L.rnnt_b200_dh_gemm(a, a, a, 100, 512, 4, 2, 2, a, None) == 0       # nothing to do
+    assert L.rnnt_b200_dh_gemm(None, a, a, 100, 512, 4, 0, 4, 0, a, None) == -1
+    assert L.rnnt_b200_dh_gemm(a, a, a, 100, 192, 4, 0, 4, 0, a, None) == -2      # H not in {128, 256, 512}
+    assert L.rnnt_b200_dh_gemm(a, a, a, 100, 512, 4, 2, 5, 0, a, None) == -2      # tile_hi > tile_cap
+    assert L.rnnt_b200_dh_gemm(a + 16, a, a, 100, 512, 4, 0, 4, 0, a, None) == -4  # alignment
+    assert L.rnnt_b200_dh_gemm(a, a, a, 100, 512, 4, 2, 2, 0, a, None) == 0       # nothing to do
     assert L.rnnt_b200_dpre_reduce_scratch_elems(32, 500, 101, 512) == 32 * 63 * 101 * 512
     assert L.rnnt_b200_dpre_reduce(a, a, a, 1, 4, 2, 100, a, a, a, None) == -2   # H % 64
     assert L.rnnt_b200_dpre_reduce(a, None, a, 1, 4, 2, 128, a, a, a, None) == -1

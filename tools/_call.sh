@@ -1,5 +1,7 @@
-O=gpurun_out/d5; mkdir -p $O
-timeout 600 python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; echo "smoke rc=$?" >> $O/smoke.log; tail -3 $O/smoke.log | cut -c1-600
-timeout 1500 python -m pytest tests -x -q -m gpu > $O/gpu_tests.log 2>&1; echo "gpu tests rc=$?" >> $O/gpu_tests.log; tail -4 $O/gpu_tests.log
-timeout 600 python bench.py --impl reference --gpus 1 --steps 20 --warmup 5 > $O/bench_ref.json 2> $O/bench_ref.err; tail -c 500 $O/bench_ref.json
-timeout 600 python bench.py --gpus 1 --steps 20 --warmup 5 > $O/bench_cfg3.json 2> $O/bench_cfg3.err; tail -c 300 $O/bench_cfg3.json
+O=gpurun_out/d8; mkdir -p $O
+M=dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum
+timeout 300 python tools/profile_range.py > $O/plain.log 2>&1 && \
+timeout 900 ncu --replay-mode app-range --metrics $M --clock-control none --csv --log-file $O/range_overlap.csv python tools/profile_range.py > $O/ncu_overlap.log 2>&1
+tail -3 $O/ncu_overlap.log; cat $O/range_overlap.csv | tail -8
+RNNT_B200_BWD_OVERLAP=0 timeout 900 ncu --replay-mode app-range --metrics $M --clock-control none --csv --log-file $O/range_serial.csv python tools/profile_range.py > $O/ncu_serial.log 2>&1
+tail -3 $O/ncu_serial.log; cat $O/range_serial.csv | tail -8

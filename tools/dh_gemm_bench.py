@@ -20,7 +20,7 @@ for tiles in [int(a) for a in sys.argv[1:]] or [3256, 3108, 2960]:
     dpre = torch.empty(rows, H, dtype=torch.bfloat16, device=dev)
 
     def own():
-        rc = L.rnnt_b200_dh_gemm(ds.data_ptr(), w2t.data_ptr(), h.data_ptr(), V, H, tiles, 0, tiles, dpre.data_ptr(), st)
+        rc = L.rnnt_b200_dh_gemm(ds.data_ptr(), w2t.data_ptr(), h.data_ptr(), V, H, tiles, 0, tiles, 0, dpre.data_ptr(), st)
         assert rc == 0, rc
 
     def lib():

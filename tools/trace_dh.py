@@ -19,7 +19,7 @@ h = torch.tanh(torch.randn(rows, H, device=dev)).to(torch.bfloat16)
 dpre = torch.empty(rows, H, dtype=torch.bfloat16, device=dev)
 st = torch.cuda.current_stream().cuda_stream
 for _ in range(3):
-    assert L.rnnt_b200_dh_gemm(ds.data_ptr(), w2t.data_ptr(), h.data_ptr(), V, H, tiles, 0, tiles, dpre.data_ptr(), st) == 0
+    assert L.rnnt_b200_dh_gemm(ds.data_ptr(), w2t.data_ptr(), h.data_ptr(), V, H, tiles, 0, tiles, 0, dpre.data_ptr(), st) == 0
 torch.cuda.synchronize()
 a = np.fromfile(os.environ["RNNT_B200_DH_TRACE"], dtype=np.int64).reshape(3, 4096, 3)
 NK = Vds // 64
