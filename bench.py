@@ -456,7 +456,15 @@ def run_joint(args, wl, c):
     path["breakdown_pass_ms_per_step"] = ms_break
     path["step_ms_per_rank"] = [round(x, 4) for x in ms_ranks]
     if world > 1:
-        path["allreduce_ms"] = round(sum(a.elapsed_time(b) for a, b in ar_events) / max(len(ar_events), 1), 4)
+        # time between a rank's last backward kernel and the end of the all-reduce: mostly the wait for the slowest
+        # rank (the GPUs sit at different clocks under their power caps); the rank that waits least is the limiter
+        ar = sum(a.elapsed_time(b) for a, b in ar_events) / max(len(ar_events), 1)
+        t = torch.tensor([ar], device=dev)
+        allr = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allr, t)
+        path["allreduce_ms"] = round(ar, 4)
+        path["allreduce_ms_per_rank"] = [round(float(x), 4) for x in allr]
+        path["compute_ms_per_rank (breakdown pass: step - all-reduce wait)"] = [round(ms_break - float(x), 4) for x in allr]
         path["allreduce_bytes"] = 4 * (n_flat + 1)
 
     cfg = make_config(args, wl, world)
