@@ -23,7 +23,7 @@ import torch.nn.functional as F
 from . import _lib
 from ._shard import allreduce_grads_and_loss, global_mean_loss, shard_batch
 
-__all__ = ["RNNTLoss", "rnnt_loss", "JointNet", "JointRNNTLoss", "joint_rnnt_loss",
+__all__ = ["RNNTLoss", "rnnt_loss", "JointNet", "JointRNNTLoss", "GraphedJointRNNTLoss", "joint_rnnt_loss",
            "fold_output_projections", "ProjectedJointRNNTLoss", "greedy_decode", "GreedyDecoder",
            "build_extension", "extension_path", "selftest_gemm", "KernelTimer",
            "shard_batch", "global_mean_loss", "allreduce_grads_and_loss"]
@@ -596,6 +596,79 @@ class JointRNNTLoss(nn.Module):
         return joint_rnnt_loss(enc_state, dec_state, j.forward_layer.weight, j.forward_layer.bias,
                                j.project_layer.weight, j.project_layer.bias, labels, act_lens,
                                label_lens, self.blank, self.reduction, host_lens)
+
+
+class _ReplayFn(torch.autograd.Function):
+    """Autograd glue of GraphedJointRNNTLoss: the graph has already produced the loss and the gradients of
+    sum_b loss_b; backward hands them out scaled by the incoming (scalar) gradient."""
+
+    @staticmethod
+    def forward(ctx, loss_sum, grads, *leaves):
+        ctx.grads = grads
+        return loss_sum.clone()
+
+    @staticmethod
+    def backward(ctx, g):
+        scale = g.reshape(()).to(torch.float32)
+        return (None, None) + tuple(gr * scale for gr in ctx.grads)
+
+
+class GraphedJointRNNTLoss(nn.Module):
+    """``JointRNNTLoss`` with forward AND backward of the fused path captured once per input shape in a CUDA graph
+    and replayed (the launch overhead around the path). The fused step is ~50 launches; at
+    the small BASELINE shapes (configs[0], configs[1]: 0.6-0.8 ms of kernels) the eager path is launch bound, at the
+    AISHELL sweep shape it is not. Lengths are read on the device (the tile loops are sized for the padded
+    (B,T,U+1) bound), so one graph serves every batch of the same padded shape. The joint's parameters are read at
+    replay time. ``reduction`` is 'mean' or 'sum' (the gradients of the parameters are summed over the batch inside
+    the graph, so a per-utterance ``grad_output`` cannot be applied afterwards; the scalar one multiplies the finished
+    gradients, whereas the eager path feeds it into the dS epilogue ahead of the bf16 rounding: identical bits for
+    powers of two, bf16-rounding-level differences otherwise). The returned loss and gradients are fresh tensors."""
+
+    def __init__(self, joint: nn.Module, blank: int = 0, reduction: str = "mean"):
+        super().__init__()
+        if reduction not in ("mean", "sum"):
+            raise ValueError("GraphedJointRNNTLoss supports reduction 'mean' or 'sum'")
+        self.joint, self.blank, self.reduction = joint, blank, reduction
+        self._graphs = {}
+
+    def _params(self):
+        j = self.joint
+        return [j.forward_layer.weight, j.forward_layer.bias, j.project_layer.weight, j.project_layer.bias]
+
+    def _run(self, ent):
+        enc_s, dec_s, y_s, tl_s, ul_s = ent["inputs"]
+        # fresh leaves created on the current (capturing) stream: aliases of the static inputs and of the
+        # parameters' storage (a replay reads the parameters' current values). Differentiating with respect to the
+        # parameters themselves would tie the capture to the stream their grad accumulators were created on.
+        leaves = [t.detach().requires_grad_(True) for t in [enc_s, dec_s] + self._params()]
+        loss_b = joint_rnnt_loss(*leaves, y_s, tl_s, ul_s, self.blank, "none")
+        total = loss_b.sum()
+        grads = torch.autograd.grad(total, leaves)
+        return total.detach(), grads
+
+    def forward(self, enc_state, dec_state, labels, act_lens, label_lens):
+        dev = enc_state.device
+        key = (tuple(enc_state.shape), tuple(dec_state.shape), dev)
+        ent = self._graphs.get(key)
+        if ent is None:
+            ent = {"inputs": (enc_state.detach().clone(), dec_state.detach().clone(),
+                              labels.clone(), act_lens.clone(), label_lens.clone())}
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):          # warm-up off the capture (lazy library initialisation)
+                self._run(ent)
+            torch.cuda.current_stream(dev).wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                ent["total"], ent["grads"] = self._run(ent)
+            ent["graph"] = graph
+            self._graphs[key] = ent
+        for dst, src in zip(ent["inputs"], (enc_state, dec_state, labels, act_lens, label_lens)):
+            dst.copy_(src.detach())
+        ent["graph"].replay()
+        coeff = 1.0 / enc_state.shape[0] if self.reduction == "mean" else 1.0
+        out = _ReplayFn.apply(ent["total"], ent["grads"], enc_state, dec_state, *self._params())
+        return (out * coeff).reshape(1)
 
 
 @torch.no_grad()

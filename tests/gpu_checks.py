@@ -383,6 +383,57 @@ def fused_is_deterministic(B, T, U, E, D, H, V, mode="ragged", seed=3, repeats=3
     return {n: all(torch.equal(runs[0][i], r[i]) for r in runs[1:]) for i, n in enumerate(names)}
 
 
+def graphed_matches_eager(B, T, U, E, D, H, V, seed=6):
+    """GraphedJointRNNTLoss (fused fwd+bwd captured in a CUDA graph, replayed) against the eager JointRNNTLoss on the
+    same module: capture + two replays with different inputs and lengths (one graph per padded shape; lengths are
+    read on the device). reduction 'sum' with grad_output 1: the same kernels see the same numbers, and they are
+    deterministic, so loss and gradients must be bit-identical. reduction 'mean' with grad_output 2: the eager path
+    feeds grad_output / B into the dS epilogue (through a log2f) ahead of the bf16 rounding, the graph scales the
+    finished gradients, so single dS entries round differently: rel-L2 is reported."""
+    import time
+    torch.manual_seed(seed)
+    joint = R.JointNet(E + D, H, V).to(DEV)
+    params = list(joint.parameters())
+    out = {"equal_sum": True, "mean_rel_l2": 0.0}
+    forms = {"sum": (R.JointRNNTLoss(joint, reduction="sum"), R.GraphedJointRNNTLoss(joint, reduction="sum"), 1.0),
+             "mean": (R.JointRNNTLoss(joint), R.GraphedJointRNNTLoss(joint), 2.0)}
+    for rep, mode in enumerate(["full", "ragged", "edge"]):
+        g = torch.Generator().manual_seed(seed + rep)
+        tl, ul = synth_lengths(B, T, U, mode, g)
+        y = synth_labels(B, U, V, ul, g).to(DEV)
+        tl, ul = tl.to(DEV), ul.to(DEV)
+        enc = torch.randn(B, T, E, generator=g).to(DEV)
+        dec = torch.randn(B, U + 1, D, generator=g).to(DEV)
+        for red, (eager, graphed, factor) in forms.items():
+            res = []
+            for fn in (eager, graphed):
+                e, d = enc.clone().requires_grad_(True), dec.clone().requires_grad_(True)
+                for p_ in params:
+                    p_.grad = None
+                loss = fn(e, d, y, tl, ul)
+                (loss * factor).backward()
+                torch.cuda.synchronize()
+                res.append([loss.detach().clone(), e.grad.clone(), d.grad.clone()] + [p_.grad.clone() for p_ in params])
+            for a, b in zip(*res):
+                if red == "sum":
+                    out["equal_sum"] = out["equal_sum"] and bool(torch.equal(a, b))
+                else:
+                    out["mean_rel_l2"] = max(out["mean_rel_l2"], rel_l2(a, b))
+    out["n_graphs"] = len(forms["sum"][1]._graphs)
+    # timing: ms per fwd+bwd of both forms at this shape (host-launch bound at small shapes)
+    for name, fn in (("eager_ms", forms["mean"][0]), ("graphed_ms", forms["mean"][1])):
+        e, d = enc.clone().requires_grad_(True), dec.clone().requires_grad_(True)
+        for _ in range(3):
+            fn(e, d, y, tl, ul).backward()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(20):
+            fn(e, d, y, tl, ul).backward()
+        torch.cuda.synchronize()
+        out[name] = (time.perf_counter() - t0) / 20 * 1e3
+    return out
+
+
 def shared_embedding_grads(seed=4):
     """rnnt/model.py:55-57 (share_embedding): decoder.embedding.weight IS joint.project_layer.weight. The fused
     loss's dW2 and the embedding's own gradient must both land in the one shared tensor: compared with the float64
