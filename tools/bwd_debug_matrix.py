@@ -1,5 +1,10 @@
 """joint_bwd_ds time under RNNT_B200_DEBUG bits (1 no epilogue math, 4 no MMA issue, 16 no dS stores) for
 environment variants given as "NAME=VAL,..." arguments ("-" = none): which side bounds a kernel variant."""
+# NOTE: the RNNT_B200_* kernel knobs and clock64 traces exist only in the tuning build
+# (make -C rnnt-transducer_b200/csrc tune); this tool selects it through RNNT_B200_LIB.
+import os as _os
+_os.environ.setdefault("RNNT_B200_LIB", _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))),
+                                                      "rnnt-transducer_b200", "librnnt_b200_tune.so"))
 import os, sys, subprocess
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CODE = r'''

@@ -1,6 +1,11 @@
 """Soak run of boundary 2 against the float64 oracle on randomly drawn shapes (GPU box only).
 Usage: python tools/soak_fused.py [N=60] [seed=0]. Prints one line per failing case and a summary;
 exit code 1 when any case misses the tolerances of tests/test_fused_gpu.py."""
+# NOTE: the RNNT_B200_* kernel knobs and clock64 traces exist only in the tuning build
+# (make -C rnnt-transducer_b200/csrc tune); this tool selects it through RNNT_B200_LIB.
+import os as _os
+_os.environ.setdefault("RNNT_B200_LIB", _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))),
+                                                      "rnnt-transducer_b200", "librnnt_b200_tune.so"))
 import os, random, sys, traceback
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from tests import gpu_checks as G

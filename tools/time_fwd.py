@@ -1,4 +1,9 @@
 """Times the fused forward kernel alone (no grad) under RNNT_B200_DEBUG variants."""
+# NOTE: the RNNT_B200_* kernel knobs and clock64 traces exist only in the tuning build
+# (make -C rnnt-transducer_b200/csrc tune); this tool selects it through RNNT_B200_LIB.
+import os as _os
+_os.environ.setdefault("RNNT_B200_LIB", _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))),
+                                                      "rnnt-transducer_b200", "librnnt_b200_tune.so"))
 import os, sys, subprocess
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CODE = r'''

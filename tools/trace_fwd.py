@@ -1,5 +1,10 @@
 """Runs one fused forward (or, with argv[1] == "bwd", forward+backward: the LAST dS chunk is traced) at
 cfg3 with RNNT_B200_TRACE and summarises the per-stage clock stamps."""
+# NOTE: the RNNT_B200_* kernel knobs and clock64 traces exist only in the tuning build
+# (make -C rnnt-transducer_b200/csrc tune); this tool selects it through RNNT_B200_LIB.
+import os as _os
+_os.environ.setdefault("RNNT_B200_LIB", _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))),
+                                                      "rnnt-transducer_b200", "librnnt_b200_tune.so"))
 import os, sys, struct
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 os.environ["RNNT_B200_TRACE"] = "gpurun_out/trace_fwd.bin"
