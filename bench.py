@@ -360,11 +360,7 @@ def run_joint(args, wl, c):
     # one flat gradient buffer: the parameters' .grad are views of it, the loss sum rides in the last element,
     # so the step ends in ONE all-reduce with no concatenation and no copy-back
     n_flat = sum(p_.numel() for p_ in params)
-    flat = torch.zeros(n_flat + 1, device=dev)
-    off = 0
-    for p_ in params:
-        p_.grad = flat[off:off + p_.numel()].view_as(p_)
-        off += p_.numel()
+    flat = R.bind_flat_grads(params, extra=1)
     fused_none = R.JointRNNTLoss(joint, reduction="none")
     ar_events = []
 

@@ -9,7 +9,7 @@ from typing import List, Sequence
 import torch
 import torch.distributed as dist
 
-__all__ = ["shard_batch", "global_mean_loss", "allreduce_grads_and_loss"]
+__all__ = ["shard_batch", "global_mean_loss", "allreduce_grads_and_loss", "bind_flat_grads"]
 
 
 def shard_batch(act_lens: Sequence[int], label_lens: Sequence[int], world_size: int) -> List[List[int]]:
@@ -52,3 +52,18 @@ def allreduce_grads_and_loss(params, loss_sum: torch.Tensor) -> torch.Tensor:
         p.grad.copy_(flat[off:off + n].view_as(p.grad))
         off += n
     return flat[-1]
+
+
+def bind_flat_grads(params, extra: int = 1) -> torch.Tensor:
+    """One flat buffer behind every parameter gradient: each ``p.grad`` becomes a view of it, ``extra`` trailing
+    elements are free for scalars that ride along (the loss sum). A step then ends in ONE all-reduce of the flat
+    buffer -- no concatenation before it, no copy-back after it (``allreduce_grads_and_loss`` does both). Zero the
+    buffer (``flat.zero_()``) instead of setting ``p.grad = None`` between steps: autograd accumulates into the views."""
+    params = list(params)
+    n = sum(p.numel() for p in params)
+    flat = torch.zeros(n + extra, dtype=params[0].dtype, device=params[0].device)
+    off = 0
+    for p in params:
+        p.grad = flat[off:off + p.numel()].view_as(p)
+        off += p.numel()
+    return flat

@@ -54,6 +54,41 @@ def _worker(rank, world, port, out):
     dist.destroy_process_group()
 
 
+def _worker_flat(rank, world, port, out):
+    """bench.py's step: gradients are views of one flat buffer whose last element carries the loss sum."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    enc, dec, w1, b1, w2, b2, y, tl, ul = _inputs()
+    params = [t.clone().requires_grad_(True) for t in (w1, b1, w2, b2)]
+    flat = R.bind_flat_grads(params, extra=1)
+    idx = torch.tensor(R.shard_batch(tl.tolist(), ul.tolist(), world)[rank])
+    for _ in range(2):                      # two steps: the buffer is zeroed, not re-bound
+        flat.zero_()
+        loss_b = O.joint_rnnt_loss(enc[idx], dec[idx], *params, y[idx], tl[idx], ul[idx], reduction="none")
+        (loss_b.sum() / enc.shape[0]).backward()
+        flat[-1] = loss_b.sum().detach()
+        dist.all_reduce(flat)
+    assert all(p.grad.data_ptr() >= flat.data_ptr() for p in params)   # still views of the flat buffer
+    if rank == 0:
+        torch.save({"total": flat[-1].clone(), "grads": [p.grad.clone() for p in params]}, out)
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_two_rank_flat_gradient_buffer_matches_single_process(tmp_path):
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_worker_flat, args=(2, _free_port(), out), nprocs=2, join=True)
+    got = torch.load(out)
+    enc, dec, w1, b1, w2, b2, y, tl, ul = _inputs()
+    params = [t.clone().requires_grad_(True) for t in (w1, b1, w2, b2)]
+    ref = O.joint_rnnt_loss(enc, dec, *params, y, tl, ul, reduction="mean")
+    ref.backward()
+    assert abs(float(got["total"]) - float(ref) * enc.shape[0]) < 1e-10
+    for g, p in zip(got["grads"], params):
+        assert torch.allclose(g, p.grad, atol=1e-12)
+
+
 def test_shard_batch_is_a_balanced_partition():
     tl = [50, 10, 40, 30, 20, 60, 5]
     ul = [5, 1, 4, 3, 2, 6, 0]
