@@ -62,6 +62,27 @@ def test_synthetic(dims, mode):
     _assert_fused(G.fused_synth(*dims, mode=mode))
 
 
+def test_hypothesis_random_shapes_against_the_oracle():
+    # SURVEY.md section 4 item (4) for the fused boundary: randomly drawn dims and ragged lengths through every
+    # own kernel (joint fwd / bwd, dh, dW2, the ordered reductions; H = 64 takes the library fall-backs). This test
+    # hunts indexing errors (which are O(1)), so it uses corner-case tolerances: the draw reaches single lattice
+    # cells over 3-word vocabularies, where ONE bf16 rounding flip of an h entry (the kernel's tanh and the oracle's
+    # differ by 1e-7, enough to round a borderline value the other way) is the whole error -- 4e-5 on the loss,
+    # and nothing averages the rounding of dS / dpre (measured worst over the draw: loss 4.0e-5 / 5.1e-4, w2 2.6e-3).
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=25, deadline=None, derandomize=True)
+    @given(st.integers(1, 4), st.integers(1, 26), st.integers(0, 21), st.sampled_from([16, 48, 64]),
+           st.sampled_from([64, 128, 256, 512]), st.sampled_from([3, 17, 64, 65, 130, 300, 515, 777]),
+           st.sampled_from(["ragged", "edge", "full"]), st.booleans(), st.integers(0, 2 ** 16))
+    def check(B, T, U, E, H, V, mode, host_lens, seed):
+        m = G.fused_synth(B, T, U, E, E, H, V, mode=mode, seed=seed, host_lens=host_lens)
+        assert m["loss_rel_q"] < 1e-4 and m["loss_rel_full"] < 1e-3, m
+        for n in GRADS:
+            assert m[f"d{n}_rel_l2_q"] < 1e-2 and m[f"d{n}_rel_l2_full"] < 1.5e-2, (n, m)
+    check()
+
+
 def test_host_length_hint_gives_same_result():
     # exact tile count from host lengths (no padded tiles, odd pair tails) vs the padded bound
     _assert_fused(G.fused_synth(3, 23, 9, 64, 64, 128, 300, mode="edge", host_lens=True))
