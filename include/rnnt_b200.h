@@ -218,8 +218,8 @@ int rnnt_b200_dpre_reduce(const void* dpre_bf16, const int32_t* act_lens, const 
 /* Fused backward, weight/bias gradient of project_layer for one staged dS chunk (rnnt/model.py:16,35):
  *   dw2_parts[s][v, j] = sum_{r in K split s} dS[r, v] * h[r, j]      (v < ds_pitch(V), j < H)
  *   db2_parts[s][v]   += sum_{r in K split s} dS[r, v]
- * for the s < rnnt_b200_dw2_splits(rows, V, H, sm_pairs) K splits of the chunk (split s takes the 64-row blocks
- * s, s + splits, ...). dw2_parts (splits, ds_pitch(V), H) float32 is
+ * for the s < rnnt_b200_dw2_splits(rows, V, H, sm_pairs) K splits of the chunk (H = 512: split s takes the 64-row
+ * blocks s, s + splits, ...; H = 128, 256: contiguous ranges of blocks). dw2_parts (splits, ds_pitch(V), H) float32 is
  * stored (every element exactly once, no zeroing needed); db2_parts (splits, ds_pitch(V)) float32 must be zeroed
  * by the caller. The caller adds the partials of all chunks in slot order with rnnt_b200_sum_partials: the
  * result does not depend on the order in which CTAs finish (DETERMINISTIC).
