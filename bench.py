@@ -337,25 +337,28 @@ def run_joint(args, wl, c):
     else:
         gtl = torch.full((GB,), T, dtype=torch.int32)
         gul = torch.full((GB,), U, dtype=torch.int32)
-    mine = torch.tensor(R.shard_batch(gtl.tolist(), gul.tolist(), world)[rank])
-    assert len(mine) == B
-    gen_r = torch.Generator().manual_seed(2019 + 1000 * (rank + 1))
-    tl, ul = gtl[mine].contiguous(), gul[mine].contiguous()
-    Tm, Um = int(tl.max()), int(ul.max())                # a rank pads to its own longest utterance
-    h_enc = torch.randn(B, Tm, E, generator=gen_r).pin_memory()
-    h_dec = torch.randn(B, Um + 1, D, generator=gen_r).pin_memory()
-    y = torch.randint(1, V, (B, Um), generator=gen_r, dtype=torch.int32)
-    for b in range(B):
-        y[b, int(ul[b]):] = 0
-    h_y, h_tl, h_ul = y.pin_memory(), tl.pin_memory(), ul.pin_memory()
-    cells = int((tl.long() * (ul.long() + 1)).sum())
-    cells_btu = int((tl.long() * ul.long()).sum())
-    if world > 1:
-        tot = torch.tensor([cells, cells_btu], device=dev, dtype=torch.int64)
-        dist.all_reduce(tot)
-        cells_all, cells_btu_all = int(tot[0]), int(tot[1])
-    else:
-        cells_all, cells_btu_all = cells, cells_btu
+    class S:    # this rank's share of the global batch (rebuilt once if the ranks' speeds differ, see below)
+        pass
+
+    def deal(shares):
+        mine = torch.tensor(shares[rank])
+        gen_r = torch.Generator().manual_seed(2019 + 1000 * (rank + 1))
+        S.n = len(mine)
+        S.tl, S.ul = gtl[mine].contiguous(), gul[mine].contiguous()
+        Tm, Um = int(S.tl.max()), int(S.ul.max())            # a rank pads to its own longest utterance
+        S.h_enc = torch.randn(S.n, Tm, E, generator=gen_r).pin_memory()
+        S.h_dec = torch.randn(S.n, Um + 1, D, generator=gen_r).pin_memory()
+        y = torch.randint(1, V, (S.n, Um), generator=gen_r, dtype=torch.int32)
+        for b in range(S.n):
+            y[b, int(S.ul[b]):] = 0
+        S.h_y, S.h_tl, S.h_ul = y.pin_memory(), S.tl.pin_memory(), S.ul.pin_memory()
+        S.cells = int((S.tl.long() * (S.ul.long() + 1)).sum())
+        S.cells_btu = int((S.tl.long() * S.ul.long()).sum())
+        S.d_enc, S.d_dec = S.h_enc.to(dev), S.h_dec.to(dev)
+        S.d_y, S.d_tl, S.d_ul = S.h_y.to(dev), S.h_tl.to(dev), S.h_ul.to(dev)
+
+    deal(R.shard_batch(gtl.tolist(), gul.tolist(), world))
+    assert S.n == B
     params = list(joint.parameters())
     # one flat gradient buffer: the parameters' .grad are views of it, the loss sum rides in the last element,
     # so the step ends in ONE all-reduce with no concatenation and no copy-back
@@ -364,16 +367,16 @@ def run_joint(args, wl, c):
     fused_none = R.JointRNNTLoss(joint, reduction="none")
     ar_events = []
 
-    def step(enc, dec, yy, tll, ull, time_ar=False):
+    def step(enc, dec, yy, tll, ull, time_ar=False, allreduce=True):
         """fwd + bwd (+ NCCL all-reduce of joint grads and the loss sum at N>1)."""
         enc.requires_grad_(True)
         dec.requires_grad_(True)
         flat.zero_()
-        loss_b = fused_none(enc, dec, yy, tll, ull, host_lens=(tl, ul))
+        loss_b = fused_none(enc, dec, yy, tll, ull, host_lens=(S.tl, S.ul))
         loss_sum = loss_b.sum()
         (loss_sum / GB).backward()
         flat[-1] = loss_sum.detach()
-        if world > 1:
+        if world > 1 and allreduce:
             if time_ar:
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
@@ -384,13 +387,51 @@ def run_joint(args, wl, c):
                 dist.all_reduce(flat)
         return flat[-1] / GB
 
-    d_enc, d_dec = h_enc.to(dev), h_dec.to(dev)
-    d_y, d_tl, d_ul = h_y.to(dev), h_tl.to(dev), h_ul.to(dev)
-
     # ---------------- device-resident (value) ----------------
-    def step_resident():
-        return step(d_enc.detach(), d_dec.detach(), d_y, d_tl, d_ul)
+    def step_resident(**kw):
+        return step(S.d_enc.detach(), S.d_dec.detach(), S.d_y, S.d_tl, S.d_ul, **kw)
 
+    # Speed-weighted sharding (N > 1, --balance only): the GPUs of a box run at different clocks under their power
+    # caps and a synchronous step waits for the slowest, so the global batch can be dealt in proportion to each
+    # rank's measured speed (untimed local steps without the all-reduce; half of the measured difference is
+    # corrected, see shard_batch_weighted). The global batch and the loss / gradient normalisation do not change;
+    # utterances per rank are reported in `config`. OFF by default: on the boxes measured, which rank is slow
+    # changes from run to run and the dealt batch changed nothing (profiles/r02_notes.md).
+    balance = None
+    CAL_WARM, CAL_STEPS = 8, 10
+    if world > 1 and args.balance:
+        try:
+            for _ in range(CAL_WARM):
+                step_resident(allreduce=False)
+            torch.cuda.synchronize()
+            dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(CAL_STEPS):
+                step_resident(allreduce=False)
+            e1.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([S.cells / (e0.elapsed_time(e1) / CAL_STEPS)], device=dev, dtype=torch.float64)
+            rates = [torch.zeros_like(t) for _ in range(world)]
+            dist.all_gather(rates, t)
+            rates = [float(x) for x in rates]
+            shares = R.shard_batch_weighted(gtl.tolist(), gul.tolist(), rates, damping=0.5)
+            balance = {"cells_per_ms_per_rank": [round(x, 1) for x in rates],
+                       "utterances_per_rank": [len(s_) for s_ in shares], "damping": 0.5,
+                       "calibration": f"{CAL_WARM}+{CAL_STEPS} untimed local steps"}
+            if len(shares[rank]) != S.n or sorted(shares[rank]) != sorted(R.shard_batch(gtl.tolist(), gul.tolist(), world)[rank]):
+                deal(shares)
+        except Exception as exc:      # never let the balancing take the measurement down: keep the equal split
+            balance = {"error": repr(exc)[:200]}
+            deal(R.shard_batch(gtl.tolist(), gul.tolist(), world))
+
+    cells, cells_btu = S.cells, S.cells_btu
+    if world > 1:
+        tot = torch.tensor([cells, cells_btu], device=dev, dtype=torch.int64)
+        dist.all_reduce(tot)
+        cells_all, cells_btu_all = int(tot[0]), int(tot[1])
+    else:
+        cells_all, cells_btu_all = cells, cells_btu
     sampler = ClockSampler(c.local_rank) if rank == 0 else None
     if sampler:
         sampler.start()      # started ahead of the warm-up so that it is polling when the timed region begins
@@ -415,7 +456,7 @@ def run_joint(args, wl, c):
 
     def stage_inputs():
         with torch.cuda.stream(copy_stream):
-            ts = [t.to(dev, non_blocking=True) for t in (h_enc, h_dec, h_y, h_tl, h_ul)]
+            ts = [t.to(dev, non_blocking=True) for t in (S.h_enc, S.h_dec, S.h_y, S.h_tl, S.h_ul)]
             ev = torch.cuda.Event()
             ev.record(copy_stream)
         pending.append((ts, ev))
@@ -441,11 +482,11 @@ def run_joint(args, wl, c):
     if sampler:
         sampler.window_end()
     clocks = sampler.stop() if sampler else None
-    h2d = sum(t.numel() * t.element_size() for t in (h_enc, h_dec, h_y, h_tl, h_ul))
+    h2d = sum(t.numel() * t.element_size() for t in (S.h_enc, S.h_dec, S.h_y, S.h_tl, S.h_ul))
 
     # ---------------- per-kernel breakdown: a separate pass with CUDA events around every own kernel ----------------
     with R.KernelTimer() as kt:
-        ms_break, _, _ = timed(c, lambda: step(d_enc.detach(), d_dec.detach(), d_y, d_tl, d_ul, time_ar=True), args.steps)
+        ms_break, _, _ = timed(c, lambda: step_resident(time_ar=True), args.steps)
     ks = kt.summary()
     kern_ms = {k: sum(v) / args.steps for k, v in ks.items()}      # ms per step, per C-ABI call site
     roofline, roofline_fwd, path = roofline_objects(R, wl, cells, ks, kern_ms, ms_break, args.steps, args.workload)
@@ -464,7 +505,8 @@ def run_joint(args, wl, c):
         path["allreduce_bytes"] = 4 * (n_flat + 1)
 
     cfg = make_config(args, wl, world)
-    cfg["cells_per_gpu"] = cells
+    if balance is not None:
+        cfg["speed_weighted_sharding"] = balance
     line = {
         "metric": METRIC, "value": cells_all / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
@@ -613,6 +655,9 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ragged", action="store_true", help="ragged lengths instead of full (parity-style inputs)")
+    ap.add_argument("--balance", action="store_true",
+                    help="N > 1: speed-weighted sharding of the global batch (off by default: measured to change "
+                         "nothing, profiles/r02_notes.md)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     args.warmup = max(args.warmup, 3)

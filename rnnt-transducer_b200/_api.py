@@ -21,12 +21,13 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from . import _lib
-from ._shard import allreduce_grads_and_loss, bind_flat_grads, global_mean_loss, shard_batch
+from ._shard import (allreduce_grads_and_loss, bind_flat_grads, global_mean_loss, shard_batch,
+                     shard_batch_weighted)
 
 __all__ = ["RNNTLoss", "rnnt_loss", "JointNet", "JointRNNTLoss", "GraphedJointRNNTLoss", "joint_rnnt_loss",
            "fold_output_projections", "ProjectedJointRNNTLoss", "greedy_decode", "GreedyDecoder",
            "build_extension", "extension_path", "selftest_gemm", "KernelTimer",
-           "shard_batch", "global_mean_loss", "allreduce_grads_and_loss", "bind_flat_grads"]
+           "shard_batch", "shard_batch_weighted", "global_mean_loss", "allreduce_grads_and_loss", "bind_flat_grads"]
 
 
 def build_extension(verbose: bool = False) -> str:

@@ -9,7 +9,7 @@ from typing import List, Sequence
 import torch
 import torch.distributed as dist
 
-__all__ = ["shard_batch", "global_mean_loss", "allreduce_grads_and_loss", "bind_flat_grads"]
+__all__ = ["shard_batch", "shard_batch_weighted", "global_mean_loss", "allreduce_grads_and_loss", "bind_flat_grads"]
 
 
 def shard_batch(act_lens: Sequence[int], label_lens: Sequence[int], world_size: int) -> List[List[int]]:
@@ -24,6 +24,34 @@ def shard_batch(act_lens: Sequence[int], label_lens: Sequence[int], world_size: 
         if (j // world_size) & 1:
             r = world_size - 1 - r
         shards[r].append(idx)
+    return shards
+
+
+def shard_batch_weighted(act_lens: Sequence[int], label_lens: Sequence[int], rates: Sequence[float],
+                         min_spread: float = 0.015, damping: float = 1.0) -> List[List[int]]:
+    """Utterances to ranks in proportion to the ranks' measured speeds (``rates[r]``: lattice cells per unit time of
+    rank r, e.g. from a few untimed steps): the GPUs of one box settle at different clocks under their power caps
+    (8 % apart on an 8-GPU box), and a synchronous step waits for the slowest. Longest-processing-time greedy: the
+    utterances in descending cell count, each to the rank whose finishing time (load + cells) / rate stays
+    smallest. With rates closer than ``min_spread`` the equal split of ``shard_batch`` is returned. ``damping`` < 1
+    corrects only part of the measured difference (rates ** damping): a power-capped GPU that is given less work
+    idles in the step's all-reduce and regains clock headroom, one that is given more loses it. Deterministic: every
+    rank computes the same assignment from the same (all-gathered) rates."""
+    world = len(rates)
+    lo, hi = min(rates), max(rates)
+    if world == 1 or lo <= 0 or (hi - lo) / hi < min_spread:
+        return shard_batch(act_lens, label_lens, world)
+    rates = [float(r) ** damping for r in rates]
+    cells = [int(t) * (int(u) + 1) for t, u in zip(act_lens, label_lens)]
+    order = sorted(range(len(cells)), key=lambda i: (-cells[i], i))
+    load = [0.0] * world
+    shards: List[List[int]] = [[] for _ in range(world)]
+    for idx in order:
+        r = min(range(world), key=lambda q: ((load[q] + cells[idx]) / rates[q], q))
+        shards[r].append(idx)
+        load[r] += cells[idx]
+    if any(not s_ for s_ in shards):      # never leave a rank without work
+        return shard_batch(act_lens, label_lens, world)
     return shards
 
 

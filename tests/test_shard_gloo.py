@@ -103,6 +103,30 @@ def test_shard_batch_is_a_balanced_partition():
 
 
 @pytest.mark.timeout(120)
+def test_speed_weighted_shards_follow_the_ranks_rates():
+    """shard_batch_weighted: a partition of the batch, more cells to faster ranks, the equal split when the rates
+    are close, never an empty rank, the same answer from the same rates (every rank computes it by itself)."""
+    g = torch.Generator().manual_seed(3)
+    tl, ul = synth_lengths(64, 500, 100, "ragged", g)
+    tl, ul = tl.tolist(), ul.tolist()
+    cells = [t * (u + 1) for t, u in zip(tl, ul)]
+    rates = [1.0, 0.9, 1.05, 0.8]
+    sh = R.shard_batch_weighted(tl, ul, rates)
+    assert sorted(i for s_ in sh for i in s_) == list(range(64))
+    load = [sum(cells[i] for i in s_) for s_ in sh]
+    finish = [l / r for l, r in zip(load, rates)]
+    assert max(finish) / min(finish) < 1.06                       # finishing times level, not the loads
+    assert load[3] < load[1] < load[0] < load[2]
+    assert sh == R.shard_batch_weighted(tl, ul, list(rates))
+    equal = R.shard_batch(tl, ul, 4)
+    assert R.shard_batch_weighted(tl, ul, [1.0, 0.99, 1.0, 0.995]) == equal      # inside the 1.5 % dead band
+    assert R.shard_batch_weighted(tl, ul, [1.0, 0.0, 1.0, 1.0]) == equal          # a nonsense rate: equal split
+    assert R.shard_batch_weighted(tl[:2], ul[:2], [1.0, 1e-6]) == R.shard_batch(tl[:2], ul[:2], 2)   # no empty rank
+    # identical utterances (bench.py's default batch): counts follow the rates to within one utterance
+    sh = R.shard_batch_weighted([500] * 256, [100] * 256, [1, 1, .92, 1, .97, 1, 1.02, .95])
+    assert [len(s_) for s_ in sh] == [33, 33, 30, 32, 32, 32, 33, 31]
+
+
 def test_two_rank_gloo_matches_single_process(tmp_path):
     out = str(tmp_path / "r0.pt")
     mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
