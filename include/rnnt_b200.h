@@ -230,6 +230,48 @@ int rnnt_b200_dw2_splits(long long rows, int V, int H, int sm_pairs);
 int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long long rows, int V, int H, int sm_pairs,
                        float* dw2_parts, float* db2_parts, void* stream);
 
+/* ---- The backward WITHOUT the second vocabulary GEMM: the forward stores its exponentials -------------------------
+ * (the backward of rnnt/model.py:35 + :70 entered from train.py:45; same results as joint_bwd_ds -> dh_gemm / dw2_gemm
+ * to bf16 rounding, one of the four vocabulary-sized GEMMs of a training step gone.)
+ *
+ * rnnt_b200_joint_fwd_store: rnnt_b200_joint_fwd that also writes
+ *   e_out[row, v] = bf16( exp2(z[row, v] log2 e - kref[cell]) )    (tile_cap*128 rows, pitch rnnt_b200_ds_pitch(V),
+ *                                                                   16-byte aligned; rows without a cell: zeros)
+ * and the plane kref (an integer-valued float per cell, laid out like lse: the exponent reference, 64 above the
+ * largest of the first 16 logits the cell's row sees, so that later logits may exceed those by 190 (log2 units)
+ * before fp32 overflows; an overflow shows as an infinite lse / loss). lse is formed from the fp32 sum of the same
+ * exponentials (fixed reference instead of a running maximum).
+ *
+ * rnnt_b200_patch_scale (after rnnt_b200_lattice): with g[row] = scale_b (c_blank + c_label) exp2(kref - lse log2 e),
+ *   dS[row, v] = g[row] * e[row, v]  in every column but the row's two one-hot columns: those two entries of e are
+ *   overwritten with (their dS, formed from lp_blank / lp_label as in joint_bwd_ds) / g[row], so that afterwards
+ *   dS = diag(g) . e everywhere. Writes row_scale[tile*128 + r] = g (float32, tile_cap*128; 0 for rows without a cell
+ *   and for cells with scale (c_blank + c_label) below 1e-30) and h_scaled = bf16(g * h) (same shape as h_stash).
+ *   H in {128, 256, 512} (no tail columns in the stash). scale may have either sign.
+ *
+ * rnnt_b200_dh_gemm_scaled: rnnt_b200_dh_gemm with A = e (chunk rows [tile_lo*128, tile_hi*128) at e_bf16) and
+ *   dpre[row, j] = bf16( row_scale[row] * (sum_v e[row, v] W2[v, j]) * (1 - h[row, j]^2) ); row_scale is indexed by
+ *   the row of ALL tiles (like h_stash / dpre).
+ * rnnt_b200_dw2_gemm_weighted: rnnt_b200_dw2_gemm with A = e, B = the chunk's rows of h_scaled, and
+ *   db2_parts[s][v] = sum_r row_weight[r] e[r, v]; row_weight points at the chunk's first row. H = 512 only. */
+int rnnt_b200_joint_fwd_store(const void* h_stash, const void* w2_bf16, const float* b2_log2,
+                              const int32_t* labels, const int32_t* act_lens, const int32_t* label_lens,
+                              const int32_t* tile_utt, const int32_t* tile_cell0, const int32_t* n_tiles,
+                              int B, int T, int U1, int V, int H, int blank, int tile_cap,
+                              float* lse, float* lp_blank, float* lp_label, float* kref, void* e_out, void* stream);
+int rnnt_b200_patch_scale(const void* h_stash, const int32_t* labels, const int32_t* act_lens,
+                          const int32_t* label_lens, const int32_t* tile_utt, const int32_t* tile_cell0,
+                          const int32_t* n_tiles, const float* lse, const float* lp_blank, const float* lp_label,
+                          const float* kref, const float* c_blank, const float* c_label, const float* scale,
+                          int B, int T, int U1, int V, int H, int blank, int tile_cap,
+                          void* e_inout, float* row_scale, void* h_scaled, void* stream);
+int rnnt_b200_dh_gemm_scaled(const void* e_bf16, const void* w2t_bf16, const void* h_stash, const float* row_scale,
+                             int V, int H, int tile_cap, int tile_lo, int tile_hi, int sm_pairs, void* dpre_bf16,
+                             void* stream);
+int rnnt_b200_dw2_gemm_weighted(const void* e_bf16, const void* h_scaled_rows, const float* row_weight,
+                                long long rows, int V, int H, int sm_pairs, float* dw2_parts, float* db2_parts,
+                                void* stream);
+
 /* out[i] = parts[0][i] + parts[1][i] + ... + parts[nparts-1][i], i < n, in that order. */
 int rnnt_b200_sum_partials(const float* parts, int nparts, long long n, float* out, void* stream);
 

@@ -51,7 +51,8 @@ class KernelTimer:
     # kernels launched per C-ABI call
     KERNELS = {"logits_to_planes": 1, "lattice": 2, "planes_to_dlogits": 1, "build_tiles": 1,
                "pack_vocab": 2, "joint_hidden": 1, "joint_fwd": 1, "joint_bwd_ds": 1, "dh_gemm": 1,
-               "dpre_reduce": 2, "sum_partials": 1, "joint_step_argmax": 1, "dw2_gemm": 1}
+               "dpre_reduce": 2, "sum_partials": 1, "joint_step_argmax": 1, "dw2_gemm": 1,
+               "joint_fwd_store": 1, "patch_scale": 1, "dh_gemm_scaled": 1, "dw2_gemm_weighted": 1}
 
     def __init__(self, events: bool = True):
         self.events = events
@@ -267,6 +268,20 @@ class RNNTLoss(nn.Module):
 
 # --------------------------------------------------------------------------- boundary 2
 _DS_BUDGET_BYTES = int(os.environ.get("RNNT_B200_DS_BYTES", str(4 << 30)))
+# Backward without the second vocabulary GEMM: the forward keeps E = bf16(exp2(z - kref)) for every cell
+# (cells x ds_pitch(V) x 2 bytes, alive from forward to backward) when that fits this budget and the joint has the
+# shape the stored path's kernels cover (H = 512); else the backward recomputes the logits chunk by chunk.
+# RNNT_B200_BWD = "stored" | "recompute" forces one (stored: still only where the kernels cover the shape).
+_E_BUDGET_BYTES = int(os.environ.get("RNNT_B200_E_BYTES", str(48 << 30)))
+
+
+def _store_exponentials(H: int, max_tiles: int, Vds: int) -> bool:
+    mode = os.environ.get("RNNT_B200_BWD", "auto")
+    if mode == "recompute" or H != 512 or os.environ.get("RNNT_B200_DH_LIB", "0") == "1":
+        return False
+    return mode == "stored" or max_tiles * 128 * Vds * 2 <= _E_BUDGET_BYTES
+
+
 _SPLIT_K = int(os.environ.get("RNNT_B200_SPLIT_K", "4"))   # of the dW2 library GEMM (rows are a multiple of 256)
 
 
@@ -309,21 +324,32 @@ class _JointLossFn(torch.autograd.Function):
             h_stash = torch.empty(max_tiles * 128, L.rnnt_b200_h_pitch(H), dtype=torch.bfloat16, device=dev)
             _call("joint_hidden", L.rnnt_b200_joint_hidden, _ptr(pe), _ptr(pd), _ptr(act_lens), _ptr(label_lens),
                   _ptr(tile_utt), _ptr(tile_cell0), _ptr(n_tiles), B, T, U1, H, max_tiles, _ptr(h_stash), st)
-            _call("joint_fwd", L.rnnt_b200_joint_fwd, _ptr(h_stash), _ptr(w2q), _ptr(b2l), _ptr(labels),
-                                             _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt),
-                                             _ptr(tile_cell0), _ptr(n_tiles), B, T, U1, V, H, blank, max_tiles,
-                                             _ptr(lse), _ptr(lpb), _ptr(lpl), st)
+            Vds = L.rnnt_b200_ds_pitch(V)
+            e_st = kref = None
+            if need_grad and _store_exponentials(H, max_tiles, Vds):
+                e_st = torch.empty(max_tiles * 128, Vds, dtype=torch.bfloat16, device=dev)
+                kref = torch.empty(n, dtype=torch.float32, device=dev)
+                _call("joint_fwd_store", L.rnnt_b200_joint_fwd_store, _ptr(h_stash), _ptr(w2q), _ptr(b2l),
+                      _ptr(labels), _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt), _ptr(tile_cell0),
+                      _ptr(n_tiles), B, T, U1, V, H, blank, max_tiles, _ptr(lse), _ptr(lpb), _ptr(lpl),
+                      _ptr(kref), _ptr(e_st), st)
+            else:
+                _call("joint_fwd", L.rnnt_b200_joint_fwd, _ptr(h_stash), _ptr(w2q), _ptr(b2l), _ptr(labels),
+                                                 _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt),
+                                                 _ptr(tile_cell0), _ptr(n_tiles), B, T, U1, V, H, blank, max_tiles,
+                                                 _ptr(lse), _ptr(lpb), _ptr(lpl), st)
             loss, cb, cl = _lattice(lpb, lpl, act_lens, label_lens, B, T, U1)
         if need_grad:
             ctx.save_for_backward(labels, act_lens, label_lens, tile_utt, tile_cell0, n_tiles, w2q, b2l,
-                                  lse, lpb, lpl, cb, cl, h_stash, w2t)
+                                  lse, lpb, lpl, cb, cl, h_stash, w2t, e_st, kref)
         ctx.dims = (B, T, U1, V, H, L.rnnt_b200_ds_pitch(V), max_tiles, blank)
         return loss
 
     @staticmethod
     def backward(ctx, grad_out):
         (labels, act_lens, label_lens, tile_utt, tile_cell0, n_tiles, w2q, b2l, lse, lpb, lpl, cb, cl,
-         h_stash, w2t) = ctx.saved_tensors
+         h_stash, w2t, e_st, kref) = ctx.saved_tensors
+        stored = e_st is not None
         B, T, U1, V, H, Vds, max_tiles, blank = ctx.dims
         L = _lib.lib()
         dev = lse.device
@@ -354,7 +380,17 @@ class _JointLossFn(torch.autograd.Function):
                 if up * 128 * Vds * 2 <= max(_DS_BUDGET_BYTES, chunk * 128 * Vds * 2):
                     chunk = up
             bounds = [(lo, min(max_tiles, lo + chunk)) for lo in range(0, max_tiles, chunk)]
-            ds = torch.empty(chunk * 128, Vds, dtype=torch.bfloat16, device=dev)
+            if stored:
+                # dS = diag(row_scale) . E once the two one-hot entries of every row are patched (csrc/joint_tc.cu,
+                # patch_scale_kernel): no second vocabulary GEMM, the consumers read E chunk by chunk
+                row_scale = torch.empty(max_tiles * 128, dtype=torch.float32, device=dev)
+                h_scaled = torch.empty_like(h_stash)
+                _call("patch_scale", L.rnnt_b200_patch_scale, _ptr(h_stash), _ptr(labels), _ptr(act_lens),
+                      _ptr(label_lens), _ptr(tile_utt), _ptr(tile_cell0), _ptr(n_tiles), _ptr(lse), _ptr(lpb),
+                      _ptr(lpl), _ptr(kref), _ptr(cb), _ptr(cl), _ptr(scale), B, T, U1, V, H, blank, max_tiles,
+                      _ptr(e_st), _ptr(row_scale), _ptr(h_scaled), st)
+            else:
+                ds = torch.empty(chunk * 128, Vds, dtype=torch.bfloat16, device=dev)
             # dpre = dh * (1 - h^2), bf16, all M rows (M x H, never M x V): written chunk by chunk, reduced once
             dpre = torch.empty(max_tiles * 128, H, dtype=torch.bfloat16, device=dev)
             if own_gemm:
@@ -368,12 +404,15 @@ class _JointLossFn(torch.autograd.Function):
             slot = 0
             for ci, (lo, hi) in enumerate(bounds):
                 rows = (hi - lo) * 128
-                dsc = ds[:rows]
-                _call("joint_bwd_ds", L.rnnt_b200_joint_bwd_ds, _ptr(h_stash), _ptr(w2q), _ptr(b2l), _ptr(labels),
-                                                    _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt),
-                                                    _ptr(tile_cell0), _ptr(n_tiles), _ptr(lse), _ptr(lpb),
-                                                    _ptr(lpl), _ptr(cb), _ptr(cl), _ptr(scale), B, T, U1, V, H, blank, max_tiles, lo, hi,
-                                                    _ptr(dsc), st)
+                if stored:
+                    dsc = e_st[lo * 128: hi * 128]
+                else:
+                    dsc = ds[:rows]
+                    _call("joint_bwd_ds", L.rnnt_b200_joint_bwd_ds, _ptr(h_stash), _ptr(w2q), _ptr(b2l), _ptr(labels),
+                                                        _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt),
+                                                        _ptr(tile_cell0), _ptr(n_tiles), _ptr(lse), _ptr(lpb),
+                                                        _ptr(lpl), _ptr(cb), _ptr(cl), _ptr(scale), B, T, U1, V, H, blank, max_tiles, lo, hi,
+                                                        _ptr(dsc), st)
                 if lib_dh:
                     with _region("lib_gemm_dh"):
                         dh = torch.mm(dsc, w2v)                                        # (rows, H) bf16
@@ -389,12 +428,22 @@ class _JointLossFn(torch.autograd.Function):
                         fork = torch.cuda.Event()
                         fork.record()
                         side.wait_event(fork)
-                    _call("dh_gemm", L.rnnt_b200_dh_gemm, _ptr(dsc), _ptr(w2t), _ptr(h_stash), V, H, max_tiles, lo, hi,
-                          half, _ptr(dpre), st)
+                    if stored:
+                        _call("dh_gemm_scaled", L.rnnt_b200_dh_gemm_scaled, _ptr(dsc), _ptr(w2t), _ptr(h_stash),
+                              _ptr(row_scale), V, H, max_tiles, lo, hi, half, _ptr(dpre), st)
+                    else:
+                        _call("dh_gemm", L.rnnt_b200_dh_gemm, _ptr(dsc), _ptr(w2t), _ptr(h_stash), V, H, max_tiles,
+                              lo, hi, half, _ptr(dpre), st)
                 if own_gemm:
-                    _call("dw2_gemm", L.rnnt_b200_dw2_gemm, _ptr(dsc), h_stash.data_ptr() + lo * 128 * hp * 2,
-                          rows, V, H, half, dw2_parts.data_ptr() + slot * Vds * H * 4,
-                          db2_parts.data_ptr() + slot * Vds * 4, side.cuda_stream if overlap else st)
+                    if stored:
+                        _call("dw2_gemm_weighted", L.rnnt_b200_dw2_gemm_weighted, _ptr(dsc),
+                              h_scaled.data_ptr() + lo * 128 * hp * 2, row_scale.data_ptr() + lo * 128 * 4,
+                              rows, V, H, half, dw2_parts.data_ptr() + slot * Vds * H * 4,
+                              db2_parts.data_ptr() + slot * Vds * 4, side.cuda_stream if overlap else st)
+                    else:
+                        _call("dw2_gemm", L.rnnt_b200_dw2_gemm, _ptr(dsc), h_stash.data_ptr() + lo * 128 * hp * 2,
+                              rows, V, H, half, dw2_parts.data_ptr() + slot * Vds * H * 4,
+                              db2_parts.data_ptr() + slot * Vds * 4, side.cuda_stream if overlap else st)
                     slot += nsplit[ci]
                     if overlap:   # the next chunk's dS overwrites the staging buffer: join first
                         join = torch.cuda.Event()

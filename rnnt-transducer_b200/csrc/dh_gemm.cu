@@ -81,6 +81,7 @@ struct DhParams {
   int tile_lo, tile_hi;   // tiles of this chunk; dS row 0 is row 0 of tile_lo
   int debug;              // tuning build only
   long long* trace;       // tuning build only: 3 roles x 4096 x 3 clock64 stamps
+  const float* row_scale; // optional: the product's row r (of ALL tiles' rows) is multiplied by row_scale[r]
 };
 
 // Position in the ring's item sequence. bit s of kpar / hpar: parity of the number of K / H items that
@@ -301,6 +302,12 @@ dh_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constant
     for (int u = cid; u < n_units; u += ncl, ++it) {
       for (int kb = 0; kb < p.NK; ++kb) rw.next_k();
       const long long tr0 = RNNT_DH_TRACE(p) ? clock64() : 0;
+      // (stored-E backward: the A operand is E, the row factor g of dS = diag(g) . E comes in here)
+      float gr = 1.f;
+      if (p.row_scale) {
+        const int tile = p.tile_lo + 2 * u + (int)rank;
+        gr = tile < p.tile_hi ? __ldg(p.row_scale + (size_t)tile * RNNT_TILE_M + row) : 0.f;
+      }
       mbar_wait(&ctl->acc_full, it & 1);
       const long long tr1 = RNNT_DH_TRACE(p) ? clock64() : 0;
       tc_fence_after();
@@ -337,7 +344,7 @@ dh_gemm_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constant
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const float h0 = __uint_as_float(hw[j] << 16), h1 = __uint_as_float(hw[j] & 0xffff0000u);
-            o[j] = pack2_bf16(zc[c * 8 + 2 * j] * fmaf(-h0, h0, 1.f), zc[c * 8 + 2 * j + 1] * fmaf(-h1, h1, 1.f));
+            o[j] = pack2_bf16(zc[c * 8 + 2 * j] * (gr * fmaf(-h0, h0, 1.f)), zc[c * 8 + 2 * j + 1] * (gr * fmaf(-h1, h1, 1.f)));
           }
           *reinterpret_cast<uint4*>(hrow + ((((g & 1) * 4 + c) ^ (row & 7)) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
         }
@@ -501,8 +508,9 @@ dpd_final_kernel(const float* __restrict__ part_dec, const int32_t* __restrict__
 
 extern "C" int rnnt_b200_dh_gemm_supported(int H) { return (H == 128 || H == 256 || H == 512) ? 1 : 0; }
 
-extern "C" int rnnt_b200_dh_gemm(const void* ds_bf16, const void* w2t_bf16, const void* h_stash, int V, int H,
-                                 int tile_cap, int tile_lo, int tile_hi, int sm_pairs, void* dpre_bf16, void* stream) {
+static int dh_gemm_launch(const void* ds_bf16, const void* w2t_bf16, const void* h_stash, const float* row_scale,
+                          int V, int H, int tile_cap, int tile_lo, int tile_hi, int sm_pairs, void* dpre_bf16,
+                          void* stream) {
   if (!ds_bf16 || !w2t_bf16 || !h_stash || !dpre_bf16) return RNNT_B200_E_NULL;
   if (V <= 0 || !rnnt_b200_dh_gemm_supported(H)) return RNNT_B200_E_SHAPE;
   if (tile_cap < 1 || tile_lo < 0 || tile_hi < tile_lo || tile_hi > tile_cap) return RNNT_B200_E_SHAPE;
@@ -532,6 +540,7 @@ extern "C" int rnnt_b200_dh_gemm(const void* ds_bf16, const void* w2t_bf16, cons
   p.tile_lo = tile_lo;
   p.tile_hi = tile_hi;
   p.debug = rnnt_tune_int("RNNT_B200_DH_DEBUG", 0);
+  p.row_scale = row_scale;
   const int n_units = (tile_hi - tile_lo + 1) / 2;
   const int all_pairs = sm_count() / 2;
   const int pairs = (sm_pairs > 0 && sm_pairs < all_pairs) ? sm_pairs : all_pairs;
@@ -568,6 +577,20 @@ extern "C" int rnnt_b200_dh_gemm(const void* ds_bf16, const void* w2t_bf16, cons
   }
 #endif
   return RNNT_B200_OK;
+}
+
+extern "C" int rnnt_b200_dh_gemm(const void* ds_bf16, const void* w2t_bf16, const void* h_stash, int V, int H,
+                                 int tile_cap, int tile_lo, int tile_hi, int sm_pairs, void* dpre_bf16, void* stream) {
+  return dh_gemm_launch(ds_bf16, w2t_bf16, h_stash, nullptr, V, H, tile_cap, tile_lo, tile_hi, sm_pairs, dpre_bf16,
+                        stream);
+}
+
+extern "C" int rnnt_b200_dh_gemm_scaled(const void* e_bf16, const void* w2t_bf16, const void* h_stash,
+                                        const float* row_scale, int V, int H, int tile_cap, int tile_lo,
+                                        int tile_hi, int sm_pairs, void* dpre_bf16, void* stream) {
+  if (!row_scale) return RNNT_B200_E_NULL;
+  return dh_gemm_launch(e_bf16, w2t_bf16, h_stash, row_scale, V, H, tile_cap, tile_lo, tile_hi, sm_pairs, dpre_bf16,
+                        stream);
 }
 
 extern "C" size_t rnnt_b200_dpre_reduce_scratch_elems(int B, int T, int U1, int H) {

@@ -48,6 +48,7 @@ struct GwParams {
   int ksteps;      // 64-row K blocks in the chunk
   int splits, ks_per_split;
   int interleave;  // dw2_wide_kernel: K split s takes the 64-row blocks s, s + splits, ... instead of a contiguous range
+  const float* row_weight;  // dw2_wide_kernel, optional: db2 = sum over rows of row_weight[row] * dS[row, :]
   int debug;  // RNNT_B200_DW2_DEBUG (timing experiments): 1 no ones-MMA, 2 no main MMA, 4 no epilogue adds, 8 no TMA loads, 16 no A reuse through the collector
 };
 
@@ -363,6 +364,16 @@ dw2_wide_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
       // ---- column sums of this CTA's dS boxes while the UMMAs run ----
       float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       for (int k = k0; k < k1; ++k) {
+        // (stored-E backward: the operand is E and db2 = E^T g, so each row enters with its weight g; the eight
+        // weights of this thread's rows are fetched before the wait and have landed when the stage is taken)
+        float wr[8] = {1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f};
+        if (p.row_weight) {
+          const int kc = kr.base + (k - kr.k0) * kr.stride;
+          const float4* wp = reinterpret_cast<const float4*>(p.row_weight + (size_t)kc * 64 + rg * 8);
+          const float4 w0 = __ldg(wp), w1 = __ldg(wp + 1);
+          wr[0] = w0.x; wr[1] = w0.y; wr[2] = w0.z; wr[3] = w0.w;
+          wr[4] = w1.x; wr[5] = w1.y; wr[6] = w1.z; wr[7] = w1.w;
+        }
         // The full barrier exists only in the leader CTA, so the column-sum warps of both CTAs take the
         // stage behind its UMMAs (commit multicast) and hand it back to the producers themselves.
         mbar_wait(&ctl->mma_done[stage], phase);
@@ -374,8 +385,8 @@ dw2_wide_kernel(const __grid_constant__ CUtensorMap map_ds, const __grid_constan
           const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            cs[2 * j] += __uint_as_float(ww[j] << 16);
-            cs[2 * j + 1] += __uint_as_float(ww[j] & 0xffff0000u);
+            cs[2 * j] = fmaf(wr[i], __uint_as_float(ww[j] << 16), cs[2 * j]);
+            cs[2 * j + 1] = fmaf(wr[i], __uint_as_float(ww[j] & 0xffff0000u), cs[2 * j + 1]);
           }
         }
         __syncwarp();
@@ -457,8 +468,8 @@ extern "C" int rnnt_b200_dw2_splits(long long rows, int V, int H, int sm_pairs) 
   return gw_split(rows, V, H, sm_pairs).splits;
 }
 
-extern "C" int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long long rows, int V, int H,
-                                  int sm_pairs, float* dw2_parts, float* db2_parts, void* stream) {
+static int dw2_gemm_launch(const void* ds_bf16, const void* h_rows, const float* row_weight, long long rows, int V,
+                           int H, int sm_pairs, float* dw2_parts, float* db2_parts, void* stream) {
   if (!ds_bf16 || !h_rows || !dw2_parts || !db2_parts) return RNNT_B200_E_NULL;
   if (rows < 0 || (rows & 63) || V <= 0 || !(H == 128 || H == 256 || H == 512)) return RNNT_B200_E_SHAPE;
   if ((reinterpret_cast<uintptr_t>(ds_bf16) & 127u) || (reinterpret_cast<uintptr_t>(h_rows) & 15u) ||
@@ -476,7 +487,9 @@ extern "C" int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long 
                      CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc != RNNT_B200_OK) return rc;
   const GwSplit g = gw_split(rows, V, H, sm_pairs);
+  if (row_weight && (!g.wide || (reinterpret_cast<uintptr_t>(row_weight) & 15u))) return RNNT_B200_E_SHAPE;
   GwParams p;
+  p.row_weight = row_weight;
   p.dw2 = dw2_parts; p.db2 = db2_parts; p.Vds = Vds; p.H = H;
   p.nvt = (Vds + 255) / 256;
   p.N = H >= 256 ? 256 : 128;
@@ -509,4 +522,17 @@ extern "C" int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long 
   e = wide ? cudaLaunchKernelEx(&cfg, dw2_wide_kernel, mds, mh, p) : cudaLaunchKernelEx(&cfg, dw2_gemm_kernel, mds, mh, p);
   if (e != cudaSuccess) return (int)e;
   return RNNT_B200_OK;
+}
+
+extern "C" int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long long rows, int V, int H,
+                                  int sm_pairs, float* dw2_parts, float* db2_parts, void* stream) {
+  return dw2_gemm_launch(ds_bf16, h_rows, nullptr, rows, V, H, sm_pairs, dw2_parts, db2_parts, stream);
+}
+
+extern "C" int rnnt_b200_dw2_gemm_weighted(const void* e_bf16, const void* h_scaled_rows, const float* row_weight,
+                                           long long rows, int V, int H, int sm_pairs, float* dw2_parts,
+                                           float* db2_parts, void* stream) {
+  if (!row_weight) return RNNT_B200_E_NULL;
+  if (H != 512) return RNNT_B200_E_SHAPE;  // the 256 x 512 kernel only
+  return dw2_gemm_launch(e_bf16, h_scaled_rows, row_weight, rows, V, H, sm_pairs, dw2_parts, db2_parts, stream);
 }

@@ -82,6 +82,7 @@ struct JointParams {
   float* lse;
   float* lpb;
   float* lpl;
+  float* kref;   // MODE 2: the per-cell exponent reference of the stored exponentials (a plane like lse)
   __nv_bfloat16* h_stash;
   // backward inputs/outputs
   const float* cb;
@@ -100,16 +101,22 @@ struct JointParams {
 
 // Shared memory of joint_kernel:
 //   [h tile: H/64 K blocks x 16 KB | W2 ring: slots x (BN/2 rows x 64 k) |
-//    MODE 1: dS staging, 2 KB per epilogue warp | ctl |
-//    MODE 0: red4, the cross-half (m, s, zb, zl) merge | bias ring: 2 halves x 2 buffers x BN/2 floats]
+//    MODE 1, 2: dS / E staging, 2 KB per epilogue warp | ctl |
+//    MODE 0: red4, the cross-half (m, s, zb, zl) merge; MODE 2: kref_s, one exponent reference per row (its
+//    cross-half merge goes through the staging tiles: 227 KB leave no room for red4 next to five W2 slots) |
+//    bias ring: 2 halves x 2 buffers x BN/2 floats]
 constexpr int kDsStageBytes = kEpiWarps * 2048;  // one 2 KB (32 cells x 32 columns) tile per epilogue warp  // one 2 KB (32 cells x 32 columns) tile per epilogue warp
 constexpr int kRedBytes = RNNT_TILE_M * 16;
+constexpr int kKrefBytes = RNNT_TILE_M * 4;
+__host__ __device__ inline int mode_extra_bytes(int mode) {
+  return mode == 0 ? kRedBytes : mode == 1 ? kDsStageBytes : kDsStageBytes + kKrefBytes;
+}
 // The MMA issuer consumes ksub(H) consecutive ring slots per loop iteration (two when H allows:
 // one wait/fence/elect round per 8 MMAs -- the one-slot loop spent ~620 clk per K block against
 // 512 clk of MMA); the slots themselves are filled and released one K block at a time.
 __host__ __device__ inline int ksub_for(int H) { return (H % 128 == 0) ? 2 : 1; }
 __host__ __device__ inline int smem_bytes_for(int H, int BN, int slots, int mode, int kslot = 1) {
-  return (H / kKBlock) * kABlockBytes + slots * kslot * (BN / 2) * 128 + (mode == 1 ? kDsStageBytes : kRedBytes) +
+  return (H / kKBlock) * kABlockBytes + slots * kslot * (BN / 2) * 128 + mode_extra_bytes(mode) +
          (int)sizeof(SharedCtl) + 2 * 2 * (BN / 2) * 4;
 }
 
@@ -162,7 +169,13 @@ __device__ __forceinline__ RowCoord locate_row(const JointParams& p, int tile, i
 }
 
 // ---------------------------------------------------------------------------------------
-// MODE 0 = forward (online LSE epilogue), MODE 1 = backward dS.
+// MODE 0 = forward (online LSE epilogue), MODE 1 = backward dS (recomputed logits),
+// MODE 2 = forward that also STORES the exponentials: E[cell, v] = bf16(exp2(z - kref[cell])) with kref an
+// integer near the row's largest logit (from the first 16 columns the row sees, + 64: every later logit may
+// exceed them by 190 in log2 units before fp32 overflows, and what underflows is below 2^-62 of them), and
+// sum(E) in fp32 gives the LSE with that same fixed reference. The backward then needs no second GEMM:
+// dS = diag(g) . E with g = scale (c_blank + c_label) exp2(kref - lse log2 e) per cell, after patch_scale_kernel
+// has overwritten the two one-hot entries of every row (csrc comment there).
 // V2 (experiment, RNNT_B200_V2=<kts>; backward only, BN = 128): the first `kts` K blocks of the h
 // tile are copied shared -> TMEM once per lattice tile (tcgen05.cp) and multiplied from there (TS
 // form: no shared-memory read of A for them); the accumulator is `nacc` buffers of 128 columns next
@@ -188,10 +201,13 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
   constexpr int kSlotBytes = KSLOT * kSubBytes;
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + KB * kABlockBytes;
-  uint8_t* smem_ds = smem_b + p.slots * kSlotBytes;  // MODE 1: 8 warps x 2 x 2 KB dS staging tiles
-  SharedCtl* ctl = reinterpret_cast<SharedCtl*>(smem_ds + (MODE == 1 ? kDsStageBytes : 0));
+  uint8_t* smem_ds = smem_b + p.slots * kSlotBytes;  // MODE 1, 2: 8 warps x 2 KB dS / E staging tiles
+  SharedCtl* ctl = reinterpret_cast<SharedCtl*>(smem_ds + (MODE != 0 ? kDsStageBytes : 0));
   float4* red4 = reinterpret_cast<float4*>(ctl + 1);  // MODE 0 only
-  float* bias_r = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ctl + 1) + (MODE == 0 ? kRedBytes : 0));
+  float* kref_s = reinterpret_cast<float*>(ctl + 1);  // MODE 2 only
+  (void)red4; (void)kref_s;
+  float* bias_r = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ctl + 1) +
+                                           (MODE == 0 ? kRedBytes : MODE == 2 ? kKrefBytes : 0));
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -284,14 +300,19 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
       // (Walking this load chain for the next lattice tile during the current one's last
       // vocabulary tiles was tried: the tile switch is not where the time goes, and the extra
       // live registers slowed the steady state.)
-      float nl = RNNT_NEG_BIG;  // invalid rows: exp2(z + nl) == 0 exactly
+      float nl = RNNT_NEG_BIG;  // invalid rows: exp2(z + nl) == 0 exactly (MODE 2: nl = -kref for valid rows)
+      float kref = 0.f;         // MODE 2
+      (void)kref;
       float g_blank = 0.f, g_label = 0.f;
+      uint32_t sgn = 0u;  // MODE 1: a negative upstream gradient flips the sign bits of the packed exponentials
+      (void)sgn;
       if (MODE == 1 && rc.valid) {
         const float sc = p.scale[rc.b];
         const float cbs = p.cb[pidx] * sc;
         const float cls = (rc.u < rc.Ub) ? p.cl[pidx] * sc : 0.f;
         const float c0 = cbs + cls;
-        nl = (c0 > 0.f) ? log2f(c0) - p.lse[pidx] * RNNT_LOG2E : RNNT_NEG_BIG;
+        nl = (c0 != 0.f) ? log2f(fabsf(c0)) - p.lse[pidx] * RNNT_LOG2E : RNNT_NEG_BIG;
+        sgn = (c0 < 0.f) ? 0x80008000u : 0u;
         g_blank = c0 * __expf(p.lpb[pidx]) - cbs;
         if (label >= 0) g_label = c0 * __expf(p.lpl[pidx]) - cls;
         if (label == p.blank) { g_blank -= cls; g_label = g_blank; }
@@ -316,6 +337,27 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         const int ncol = min(HALF, max(0, ((vt == NV - 1) ? n_last : BN) - half * HALF));
         const int nch = (RNNT_DBG(p) & 1) ? 0 : ncol >> 4;
         const int colbase = vt * BN + half * HALF;
+        if (MODE == 2 && vi == 0) {
+          // The row's exponent reference, from the first 16 columns of column half 0 of the first vocabulary tile
+          // this pair sweeps (one extra TMEM load per lattice tile), handed to the other half's thread of the row.
+          if (half == 0) {
+            float z0[16];
+            tmem_ld_32x16(taddr0, z0);
+            tmem_ld_wait();
+            float cm = -INFINITY;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) cm = fmaxf(cm, fmaf(z0[j], RNNT_LOG2E, bias_c[j]));
+            // NaN / infinite logits: any reference will do, the sum carries them into the loss
+            kref = (cm > -1.0e29f && cm < 1.0e29f) ? ceilf(cm) + 64.f : 0.f;
+            kref_s[row] = kref;
+            __threadfence_block();
+            named_bar_arrive(4 + q, 64);
+          } else {
+            named_bar_sync(4 + q, 64);
+            kref = kref_s[row];
+          }
+          nl = rc.valid ? -kref : RNNT_NEG_BIG;
+        }
         auto release_acc = [&]() {
           tc_fence_before();
           __syncwarp();
@@ -366,11 +408,36 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
             }
           } else {
             uint32_t gp[8];
+            if (MODE == 1) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {  // softmax * (c_blank + c_label) * scale, two columns per word
-              float d0, d1;
-              fadd2(d0, d1, zc[2 * j], zc[2 * j + 1], nl, nl);
-              gp[j] = pack_bf16x2(ex2_approx(d0), ex2_approx(d1));
+              for (int j = 0; j < 8; ++j) {  // softmax * (c_blank + c_label) * scale, two columns per word
+                float d0, d1;
+                fadd2(d0, d1, zc[2 * j], zc[2 * j + 1], nl, nl);
+                gp[j] = pack_bf16x2(ex2_approx(d0), ex2_approx(d1)) ^ sgn;
+              }
+            } else {
+              // exp2(z - kref): summed in fp32 (the LSE with a fixed reference), stored as bf16
+              float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+              for (int j = 0; j < 8; j += 2) {
+                float d0, d1, d2, d3;
+                fadd2(d0, d1, zc[2 * j], zc[2 * j + 1], nl, nl);
+                fadd2(d2, d3, zc[2 * j + 2], zc[2 * j + 3], nl, nl);
+                const float e0 = ex2_approx(d0), e1 = ex2_approx(d1), e2 = ex2_approx(d2), e3 = ex2_approx(d3);
+                fadd2(a0, a1, a0, a1, e0, e1);
+                fadd2(a2, a3, a2, a3, e2, e3);
+                gp[j] = pack_bf16x2(e0, e1);
+                gp[j + 1] = pack_bf16x2(e2, e3);
+              }
+              s += (a0 + a1) + (a2 + a3);
+              const bool hit_b = (unsigned)(p.blank - col0) < 16u, hit_l = (unsigned)(label - col0) < 16u;
+              if (hit_b || hit_l) {
+                float tmp[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) tmp[j] = zc[j];
+                if (hit_b) zb = tmp[(p.blank - col0) & 15];
+                if (hit_l) zl = tmp[(label - col0) & 15];
+              }
             }
             // 32 cells x 32 columns of bf16 (two chunks) -> this warp's 2 KB staging tile (64-byte
             // rows, SWIZZLE_64B: conflict-free 16-byte stores) -> one TMA store (full-sector
@@ -398,11 +465,11 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
               *reinterpret_cast<uint4*>(srow + (((2 * (c & 1) + 1) ^ swz) << 4)) = make_uint4(gp[4], gp[5], gp[6], gp[7]);
               // the row's one-hot entries: exact values over the staged ones (same thread, program order)
               const int ncols = 16 + (c & 1) * 16;
-              if ((unsigned)(p.blank - cbase) < (unsigned)ncols && rc.valid) {
+              if (MODE == 1 && (unsigned)(p.blank - cbase) < (unsigned)ncols && rc.valid) {
                 const int off = (p.blank - cbase) * 2;
                 *reinterpret_cast<__nv_bfloat16*>(srow + (((off >> 4) ^ swz) << 4) + (off & 15)) = __float2bfloat16_rn(g_blank);
               }
-              if ((unsigned)(label - cbase) < (unsigned)ncols) {
+              if (MODE == 1 && (unsigned)(label - cbase) < (unsigned)ncols) {
                 const int off = (label - cbase) * 2;
                 *reinterpret_cast<__nv_bfloat16*>(srow + (((off >> 4) ^ swz) << 4) + (off & 15)) = __float2bfloat16_rn(g_label);
               }
@@ -475,9 +542,27 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         }
         named_bar_sync(1, kEpiWarps * 32);  // red4[] is free again
       }
+      if (MODE == 2) {
+        // merge the two column halves through the staging tile of the half-1 warp (its last store has read it)
+        if (half == 1) {
+          if (lane == 0) bulk_wait_group_read0();
+          __syncwarp();
+          reinterpret_cast<float4*>(stage_w)[lane] = make_float4(0.f, s, zb, zl);
+        }
+        named_bar_sync(1, kEpiWarps * 32);
+        if (half == 0 && rc.valid) {
+          const float4 o = reinterpret_cast<const float4*>(smem_ds + (warp + 4) * 2048)[lane];
+          const float lg = log2f(s + o.y);
+          p.lse[pidx] = (kref + lg) * RNNT_LN2;
+          p.lpb[pidx] = ((zb + o.z - kref) - lg) * RNNT_LN2;
+          p.lpl[pidx] = (label >= 0) ? ((zl + o.w - kref) - lg) * RNNT_LN2 : -INFINITY;
+          p.kref[pidx] = kref;
+        }
+        named_bar_sync(1, kEpiWarps * 32);  // the staging tile goes back to the next lattice tile's stores
+      }
     }
-    if (MODE == 1) {
-      if (lane == 0) bulk_wait_group0();  // all of this warp's dS stores have landed
+    if (MODE != 0) {
+      if (lane == 0) bulk_wait_group0();  // all of this warp's dS / E stores have landed
       // tiles of this launch past the end of the tile table: dS rows are defined as zero
       const int first_dead = max(n_tiles, p.tile_lo);
       const int epi_tid = threadIdx.x;  // 0..255
@@ -696,6 +781,81 @@ hidden_kernel(const JointParams p, int max_tiles) {
 }
 
 // ---------------------------------------------------------------------------------------
+// Between the lattice and the two backward GEMMs when the forward stored E (joint_kernel MODE 2):
+//   dS[row, v] = c0 softmax[row, v] - [v = blank] scale c_blank - [v = label] scale c_label,   c0 = scale (c_blank + c_label)
+//             = g E[row, v]   with g = c0 exp2(kref - lse log2 e)   except in the two one-hot columns,
+// so those two entries of every row are overwritten with (their exact dS) / g, from the forward's fp32 lp_blank /
+// lp_label -- the value the recomputing backward stages there as well -- and from then on dS = diag(g) . E:
+//   dh = diag(g) (E . W2)      -> row_scale[row] = g, applied in the dh GEMM's epilogue
+//   dW2 = E^T (diag(g) h)      -> h_scaled = bf16(g h), the dW2 GEMM's B operand
+//   db2 = E^T g                -> the dW2 kernel's column sums, weighted with row_scale
+// One CTA per tile: 128 threads take a row each (g, the two patches), then all 256 scale the tile's h rows.
+// A row whose c0 is below 1e-30 (or whose g leaves the fp32 range) contributes nothing: g = 0, no patch.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+patch_scale_kernel(const JointParams p, float* __restrict__ row_scale, __nv_bfloat16* __restrict__ h_scaled,
+                   int max_tiles) {
+  __shared__ float gs[RNNT_TILE_M];
+  const int n_tiles = min(p.n_tiles[0], max_tiles);
+  const int cpr = p.H / 8;              // 16-byte chunks per row
+  const int rows_per_pass = 256 / cpr;  // H = 512: 4 rows per pass
+  const int chunk = threadIdx.x % cpr, rsub = threadIdx.x / cpr;
+  for (int tile = blockIdx.x; tile < max_tiles; tile += gridDim.x) {
+    const bool dead = tile >= n_tiles;
+    if (threadIdx.x < RNNT_TILE_M) {
+      const int r = threadIdx.x;
+      const RowCoord rc = locate_row(p, tile, r, dead);
+      float g = 0.f;
+      if (rc.valid) {
+        const size_t pidx = plane_index(rc.b, rc.t, rc.u, p.T, p.U1);
+        const float sc = p.scale[rc.b];
+        const float cbs = p.cb[pidx] * sc;
+        const float cls = (rc.u < rc.Ub) ? p.cl[pidx] * sc : 0.f;
+        const float c0 = cbs + cls;
+        if (fabsf(c0) > 1.0e-30f) {
+          g = c0 * exp2f(p.kref[pidx] - p.lse[pidx] * RNNT_LOG2E);
+          if (!(fabsf(g) > 1.0e-36f && fabsf(g) < 1.0e36f)) g = 0.f;
+        }
+        if (g != 0.f) {
+          int label = -1;
+          if (rc.u < rc.Ub) label = clamp_int(p.labels[(size_t)rc.b * (p.U1 - 1) + rc.u], 0, p.V - 1);
+          float g_blank = c0 * __expf(p.lpb[pidx]) - cbs, g_label = 0.f;
+          if (label >= 0) g_label = c0 * __expf(p.lpl[pidx]) - cls;
+          if (label == p.blank) { g_blank -= cls; g_label = g_blank; }
+          __nv_bfloat16* erow = p.ds + ((size_t)tile * RNNT_TILE_M + r) * p.Vds;
+          const float inv = 1.f / g;
+          erow[p.blank] = __float2bfloat16_rn(g_blank * inv);
+          if (label >= 0) erow[label] = __float2bfloat16_rn(g_label * inv);
+        }
+      }
+      gs[r] = g;
+      row_scale[(size_t)tile * RNNT_TILE_M + r] = g;
+    }
+    __syncthreads();
+    if (rsub < rows_per_pass) {
+      const uint4* src = reinterpret_cast<const uint4*>(p.h_stash + (size_t)tile * RNNT_TILE_M * p.H) + chunk;
+      uint4* dst = reinterpret_cast<uint4*>(h_scaled + (size_t)tile * RNNT_TILE_M * p.H) + chunk;
+#pragma unroll 4
+      for (int row = rsub; row < RNNT_TILE_M; row += rows_per_pass) {
+        const float g = gs[row];
+        uint4 o = make_uint4(0u, 0u, 0u, 0u);
+        if (g != 0.f) {
+          const uint4 w = ld_stream_u4(src + (size_t)row * cpr);
+          const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+          uint32_t oo[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            oo[j] = pack_bf16x2(g * __uint_as_float(ww[j] << 16), g * __uint_as_float(ww[j] & 0xffff0000u));
+          o = make_uint4(oo[0], oo[1], oo[2], oo[3]);
+        }
+        dst[(size_t)row * cpr] = o;
+      }
+    }
+    __syncthreads();  // gs[] is free again
+  }
+}
+
+// ---------------------------------------------------------------------------------------
 // Plain C = A . B^T (bf16 in, fp32 out): exercises exactly the descriptors, swizzles, TMA
 // maps, TMEM addressing and barrier protocol used above, with nothing else in the way.
 // One CTA per 128 x BN output tile. 6 warps: 0 TMA, 1 MMA, 2-5 epilogue (+TMEM alloc).
@@ -899,7 +1059,7 @@ int dispatch_joint(JointParams& p, const void* w2q, const void* h_stash, int max
                      CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
   CUtensorMap md = mw;
-  if (MODE == 1) {  // dS chunk (rows x Vpad): 32 x 32 store boxes out of 64-byte-swizzled staging tiles
+  if (MODE != 0) {  // dS chunk / E (rows x Vds): 32 x 32 store boxes out of 64-byte-swizzled staging tiles
     rc = make_map_bf16(&md, p.ds, (uint64_t)(p.tile_hi - p.tile_lo) * RNNT_TILE_M, p.Vds, p.Vds, 32, 32,
                        CU_TENSOR_MAP_SWIZZLE_64B);
     if (rc) return rc;
@@ -973,6 +1133,69 @@ extern "C" int rnnt_b200_joint_fwd(const void* h_stash, const void* w2_bf16,
   if (tile_cap < 1 || tile_cap > rnnt_b200_max_tiles(B, T, U1)) return RNNT_B200_E_SHAPE;
   p.tile_lo = 0; p.tile_hi = tile_cap;
   return dispatch_joint<0>(p, w2_bf16, h_stash, p.tile_hi, (cudaStream_t)stream);
+}
+
+extern "C" int rnnt_b200_joint_fwd_store(const void* h_stash, const void* w2_bf16, const float* b2_log2,
+                                         const int32_t* labels, const int32_t* act_lens,
+                                         const int32_t* label_lens, const int32_t* tile_utt,
+                                         const int32_t* tile_cell0, const int32_t* n_tiles, int B, int T, int U1,
+                                         int V, int H, int blank, int tile_cap, float* lse, float* lp_blank,
+                                         float* lp_label, float* kref, void* e_out, void* stream) {
+  if (!h_stash || !w2_bf16 || !b2_log2 || !act_lens || !label_lens || !tile_utt || !tile_cell0 ||
+      !n_tiles || !lse || !lp_blank || !lp_label || !kref || !e_out)
+    return RNNT_B200_E_NULL;
+  if (U1 > 1 && !labels) return RNNT_B200_E_NULL;
+  int rc = check_common(B, T, U1, V, H, blank);
+  if (rc) return rc;
+  if (((uintptr_t)w2_bf16 & 127) || ((uintptr_t)b2_log2 & 15) || ((uintptr_t)h_stash & 127) ||
+      ((uintptr_t)e_out & 15))
+    return RNNT_B200_E_ALIGN;
+  if (tile_cap < 1 || tile_cap > rnnt_b200_max_tiles(B, T, U1)) return RNNT_B200_E_SHAPE;
+  JointParams p = {};
+  p.w2q = (const __nv_bfloat16*)w2_bf16; p.b2l = b2_log2; p.labels = labels; p.act_lens = act_lens;
+  p.label_lens = label_lens; p.tile_utt = tile_utt; p.tile_cell0 = tile_cell0; p.n_tiles = n_tiles;
+  p.lse = lse; p.lpb = lp_blank; p.lpl = lp_label; p.kref = kref;
+  p.h_stash = (__nv_bfloat16*)const_cast<void*>(h_stash);
+  p.ds = (__nv_bfloat16*)e_out;
+  p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vpad = rnnt_b200_vocab_pad(V); p.Vds = rnnt_b200_ds_pitch(V); p.H = H; p.blank = blank;
+  p.tile_lo = 0; p.tile_hi = tile_cap;
+  return dispatch_joint<2>(p, w2_bf16, h_stash, p.tile_hi, (cudaStream_t)stream);
+}
+
+// g = scale (c_blank + c_label) exp2(kref - lse log2 e) per tile row (0 for rows without a cell and for cells the
+// lattice does not reach), the row's two one-hot entries of E overwritten so that g . E is dS there too, and the
+// hidden rows scaled by g for the dW2 GEMM (E^T . diag(g) . h = E^T . h_scaled).
+extern "C" int rnnt_b200_patch_scale(const void* h_stash, const int32_t* labels, const int32_t* act_lens,
+                                     const int32_t* label_lens, const int32_t* tile_utt,
+                                     const int32_t* tile_cell0, const int32_t* n_tiles, const float* lse,
+                                     const float* lp_blank, const float* lp_label, const float* kref,
+                                     const float* c_blank, const float* c_label, const float* scale, int B,
+                                     int T, int U1, int V, int H, int blank, int tile_cap, void* e_inout,
+                                     float* row_scale, void* h_scaled, void* stream) {
+  if (!h_stash || !act_lens || !label_lens || !tile_utt || !tile_cell0 || !n_tiles || !lse || !lp_blank ||
+      !lp_label || !kref || !c_blank || !c_label || !scale || !e_inout || !row_scale || !h_scaled)
+    return RNNT_B200_E_NULL;
+  if (U1 > 1 && !labels) return RNNT_B200_E_NULL;
+  int rc = check_common(B, T, U1, V, H, blank);
+  if (rc) return rc;
+  if (rnnt_hp(H) != H) return RNNT_B200_E_SHAPE;  // H in {128, 256, 512}: the stash has no tail columns
+  if (tile_cap < 1 || tile_cap > rnnt_b200_max_tiles(B, T, U1)) return RNNT_B200_E_SHAPE;
+  if (((uintptr_t)h_stash & 15) || ((uintptr_t)h_scaled & 15) || ((uintptr_t)e_inout & 1)) return RNNT_B200_E_ALIGN;
+  if (const int arch = rnnt_check_arch()) return arch;
+  JointParams p = {};
+  p.labels = labels; p.act_lens = act_lens; p.label_lens = label_lens;
+  p.tile_utt = tile_utt; p.tile_cell0 = tile_cell0; p.n_tiles = n_tiles;
+  p.lse = const_cast<float*>(lse); p.lpb = const_cast<float*>(lp_blank); p.lpl = const_cast<float*>(lp_label);
+  p.kref = const_cast<float*>(kref);
+  p.cb = c_blank; p.cl = c_label; p.scale = scale;
+  p.h_stash = (__nv_bfloat16*)const_cast<void*>(h_stash);
+  p.ds = (__nv_bfloat16*)e_inout;
+  p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vds = rnnt_b200_ds_pitch(V); p.H = H; p.blank = blank;
+  const int sms = sm_count();
+  const int grid = tile_cap < sms * 8 ? tile_cap : sms * 8;
+  patch_scale_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p, row_scale, (__nv_bfloat16*)h_scaled, tile_cap);
+  RNNT_CUDA_RETURN_IF_ERROR();
+  return RNNT_B200_OK;
 }
 
 extern "C" int rnnt_b200_joint_bwd_ds(const void* h_stash, const void* w2_bf16, const float* b2_log2,

@@ -245,15 +245,19 @@ def full_size_properties(B=32, T=500, U=100, E=320, D=320, H=512, V=4232, seed=2
     return out
 
 
-def _dw2_run(L, ds, h, rows, V, H, Vds, sm_pairs=0):
-    """One chunk through rnnt_b200_dw2_gemm + the ordered sum of its K-split partials."""
+def _dw2_run(L, ds, h, rows, V, H, Vds, sm_pairs=0, weight=None):
+    """One chunk through rnnt_b200_dw2_gemm (or _weighted) + the ordered sum of its K-split partials."""
     ns = L.rnnt_b200_dw2_splits(rows, V, H, sm_pairs)
     parts = torch.empty(ns, Vds, H, device=DEV)
     bparts = torch.zeros(ns, Vds, device=DEV)
     dw2 = torch.empty(Vds, H, device=DEV)
     db2 = torch.empty(Vds, device=DEV)
     st = torch.cuda.current_stream().cuda_stream
-    rc = L.rnnt_b200_dw2_gemm(ds.data_ptr(), h.data_ptr(), rows, V, H, sm_pairs, parts.data_ptr(), bparts.data_ptr(), st)
+    if weight is None:
+        rc = L.rnnt_b200_dw2_gemm(ds.data_ptr(), h.data_ptr(), rows, V, H, sm_pairs, parts.data_ptr(), bparts.data_ptr(), st)
+    else:
+        rc = L.rnnt_b200_dw2_gemm_weighted(ds.data_ptr(), h.data_ptr(), weight.data_ptr(), rows, V, H, sm_pairs,
+                                           parts.data_ptr(), bparts.data_ptr(), st)
     assert rc == 0, rc
     assert L.rnnt_b200_sum_partials(parts.data_ptr(), ns, Vds * H, dw2.data_ptr(), st) == 0
     assert L.rnnt_b200_sum_partials(bparts.data_ptr(), ns, Vds, db2.data_ptr(), st) == 0
@@ -261,26 +265,33 @@ def _dw2_run(L, ds, h, rows, V, H, Vds, sm_pairs=0):
     return dw2, db2, ns
 
 
-def dw2_gemm_vs_torch(rows, V, H, seed=0, sm_pairs=0):
+def dw2_gemm_vs_torch(rows, V, H, seed=0, sm_pairs=0, weighted=False):
     """rnnt_b200_dw2_gemm (tcgen05, MN-major operands, K-split partials added in slot order) against float64 torch
-    products of the same bf16 operands; run twice: the two results must be bit-identical (deterministic)."""
+    products of the same bf16 operands; run twice: the two results must be bit-identical (deterministic).
+    ``weighted``: rnnt_b200_dw2_gemm_weighted, db2 = sum_r w[r] dS[r, :] (the stored-E backward)."""
     from rnnt_transducer_b200 import _lib
     L = _lib.lib()
     Vds, hp = L.rnnt_b200_ds_pitch(V), L.rnnt_b200_h_pitch(H)
     g = torch.Generator().manual_seed(seed)
     ds = (torch.randn(rows, Vds, generator=g) * 0.05).to(torch.bfloat16).to(DEV)
     h = torch.tanh(torch.randn(rows, hp, generator=g)).to(torch.bfloat16).to(DEV)
-    dw2, db2, ns = _dw2_run(L, ds, h, rows, V, H, Vds, sm_pairs)
-    dw2b, db2b, _ = _dw2_run(L, ds, h, rows, V, H, Vds, sm_pairs)
+    w = None
+    if weighted:
+        w = torch.randn(rows, generator=g)
+        w[::7] = 0.0
+        w = w.to(DEV)
+    dw2, db2, ns = _dw2_run(L, ds, h, rows, V, H, Vds, sm_pairs, w)
+    dw2b, db2b, _ = _dw2_run(L, ds, h, rows, V, H, Vds, sm_pairs, w)
     ref = ds.double().t() @ h[:, :H].double()
-    refb = ds.double().sum(0)
+    refb = ds.double().sum(0) if w is None else (ds.double() * w.double()[:, None]).sum(0)
     return {"dw2_rel_l2": rel_l2(dw2.cpu(), ref.cpu()), "db2_rel_l2": rel_l2(db2.cpu(), refb.cpu()), "splits": ns,
             "bit_identical": bool(torch.equal(dw2, dw2b) and torch.equal(db2, db2b))}
 
 
-def dh_gemm_vs_torch(tiles, V, H, lo=0, hi=None, seed=0, sm_pairs=0):
+def dh_gemm_vs_torch(tiles, V, H, lo=0, hi=None, seed=0, sm_pairs=0, scaled=False):
     """rnnt_b200_dh_gemm on its own: dpre = (dS . W2q) * (1 - h^2) for tiles [lo, hi) of a stash of ``tiles`` tiles,
-    against the float64 product of the same bf16 operands; rows outside [lo, hi) must stay untouched."""
+    against the float64 product of the same bf16 operands; rows outside [lo, hi) must stay untouched.
+    ``scaled``: rnnt_b200_dh_gemm_scaled, every row times row_scale[row] (the stored-E backward)."""
     from rnnt_transducer_b200 import _lib
     L = _lib.lib()
     hi = tiles if hi is None else hi
@@ -295,11 +306,20 @@ def dh_gemm_vs_torch(tiles, V, H, lo=0, hi=None, seed=0, sm_pairs=0):
     dsd, w2d, hd = ds.to(DEV), w2q.t().contiguous().to(DEV), h.to(DEV)   # the kernel takes W2 transposed (H, Vpad)
     dpre = torch.full((tiles * 128, H), 7.0, dtype=torch.bfloat16, device=DEV)
     st = torch.cuda.current_stream().cuda_stream
-    rc = L.rnnt_b200_dh_gemm(dsd.data_ptr(), w2d.data_ptr(), hd.data_ptr(), V, H, tiles, lo, hi, sm_pairs, dpre.data_ptr(), st)
+    if scaled:
+        rs = torch.randn(tiles * 128, generator=g) * 3.0
+        rs[::5] = 0.0
+        rsd = rs.to(DEV)
+        rc = L.rnnt_b200_dh_gemm_scaled(dsd.data_ptr(), w2d.data_ptr(), hd.data_ptr(), rsd.data_ptr(), V, H, tiles,
+                                        lo, hi, sm_pairs, dpre.data_ptr(), st)
+    else:
+        rc = L.rnnt_b200_dh_gemm(dsd.data_ptr(), w2d.data_ptr(), hd.data_ptr(), V, H, tiles, lo, hi, sm_pairs, dpre.data_ptr(), st)
     torch.cuda.synchronize()
     assert rc == 0, rc
     hs = h[lo * 128: hi * 128].double()
     ref = (ds.double() @ w2q[:Vds].double()) * (1.0 - hs * hs)
+    if scaled:
+        ref = ref * rs[lo * 128: hi * 128].double()[:, None]
     got = dpre.cpu()
     outside = torch.cat((got[:lo * 128], got[hi * 128:]))
     return {"rel_l2": rel_l2(got[lo * 128: hi * 128], ref), "max_abs": max_abs(got[lo * 128: hi * 128], ref),
@@ -366,6 +386,49 @@ def fused_vs_large_oracle(B, T, U, E, D, H, V, mode="ragged", seed=2019, full_gr
                 out[f"d{n}_rel_l2_{tag}"] = rel_l2(a.grad, g[n])
                 out[f"d{n}_max_abs_{tag}"] = max_abs(a.grad, g[n])
     return out
+
+
+def _fused_grads(inputs, y, tl, ul, mode, weight=None):
+    """loss and the six gradients of boundary 2 with the backward forced to ``mode`` (RNNT_B200_BWD)."""
+    import os
+    prev = os.environ.get("RNNT_B200_BWD")
+    os.environ["RNNT_B200_BWD"] = mode
+    try:
+        leaves = [t.to(DEV).requires_grad_(True) for t in inputs]
+        loss = R.joint_rnnt_loss(*leaves, y.to(DEV), tl.to(DEV), ul.to(DEV), reduction="none")
+        (loss if weight is None else loss * weight.to(DEV)).sum().backward()
+        torch.cuda.synchronize()
+    finally:
+        if prev is None:
+            os.environ.pop("RNNT_B200_BWD", None)
+        else:
+            os.environ["RNNT_B200_BWD"] = prev
+    return loss.detach(), [t.grad for t in leaves]
+
+
+def stored_matches_recompute(B, T, U, E, D, H, V, mode="ragged", seed=8):
+    """The two backward paths on the same inputs: E kept by the forward (no second vocabulary GEMM) against the
+    recomputing one. The loss differs only in the LSE's reference (fixed against running maximum), the gradients in
+    where the bf16 roundings fall (E and g h instead of dS)."""
+    enc, dec, w1, b1, w2, b2, y, tl, ul = _joint_inputs(B, T, U, E, D, H, V, mode, seed)
+    la, ga = _fused_grads((enc, dec, w1, b1, w2, b2), y, tl, ul, "stored")
+    lb, gb = _fused_grads((enc, dec, w1, b1, w2, b2), y, tl, ul, "recompute")
+    out = {"loss_rel": float(((la - lb).abs() / lb.abs()).max())}
+    for n, a, b in zip(["enc", "dec", "w1", "b1", "w2", "b2"], ga, gb):
+        out[f"d{n}_rel_l2"] = rel_l2(a, b)
+    return out
+
+
+def negative_upstream_gradient(B, T, U, E, D, H, V, bwd, seed=9):
+    """Per-utterance weights of both signs on the loss (grad_output < 0 for some utterances): the gradients against
+    the float64 oracle's for the same weighted sum."""
+    enc, dec, w1, b1, w2, b2, y, tl, ul = _joint_inputs(B, T, U, E, D, H, V, "ragged", seed)
+    wgt = torch.tensor([(-1.0) ** i * (1.0 + 0.5 * i) for i in range(B)])
+    _, ga = _fused_grads((enc, dec, w1, b1, w2, b2), y, tl, ul, bwd, weight=wgt)
+    ol = [t.double().requires_grad_(True) for t in (enc, dec, w1, b1, w2, b2)]
+    lo = O.joint_rnnt_loss(*ol, y, tl, ul, reduction="none", quantize_bf16=True)
+    (lo * wgt.double()).sum().backward()
+    return {f"d{n}_rel_l2_q": rel_l2(a, b.grad) for n, a, b in zip(["enc", "dec", "w1", "b1", "w2", "b2"], ga, ol)}
 
 
 def fused_is_deterministic(B, T, U, E, D, H, V, mode="ragged", seed=3, repeats=3):

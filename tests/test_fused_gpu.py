@@ -62,6 +62,43 @@ def test_synthetic(dims, mode):
     _assert_fused(G.fused_synth(*dims, mode=mode))
 
 
+@pytest.mark.parametrize("dims,mode", [
+    ((2, 20, 8, 320, 320, 512, 4232), "ragged"),
+    ((3, 9, 130, 64, 64, 512, 515), "edge"),        # BN = 256, narrow last vocabulary tile
+    ((2, 9, 4, 64, 64, 512, 100), "full"),          # BN = 128
+])
+def test_synthetic_with_the_recomputing_backward(dims, mode, monkeypatch):
+    # H = 512 takes the stored-exponentials backward by default (no second vocabulary GEMM); the recomputing one
+    # (what runs when E does not fit its memory budget) against the oracle as well
+    monkeypatch.setenv("RNNT_B200_BWD", "recompute")
+    _assert_fused(G.fused_synth(*dims, mode=mode))
+
+
+@pytest.mark.parametrize("bwd", ["stored", "recompute"])
+def test_backward_in_several_chunks(bwd, monkeypatch):
+    # the backward walks the tiles in chunks (4 GiB of dS each at the BASELINE shapes: four per step); here a budget
+    # of 3 tiles puts about ten chunks (K-split partial slots, stream joins between chunks) under the oracle
+    from rnnt_transducer_b200 import _api
+    monkeypatch.setenv("RNNT_B200_BWD", bwd)
+    monkeypatch.setattr(_api, "_DS_BUDGET_BYTES", 3 * 128 * 4288 * 2)
+    _assert_fused(G.fused_synth(4, 60, 20, 320, 320, 512, 4232, mode="ragged", host_lens=True))
+
+
+@pytest.mark.parametrize("dims", [(4, 60, 20, 320, 320, 512, 4232), (3, 17, 33, 64, 64, 512, 300)])
+def test_stored_backward_agrees_with_the_recomputing_one(dims):
+    m = G.stored_matches_recompute(*dims)
+    assert m["loss_rel"] < 2e-6, m
+    for n in GRADS:      # two independent sets of bf16 roundings around the same float64 value: sqrt(2) x GRAD_Q
+        assert m[f"d{n}_rel_l2"] < 1.5 * GRAD_Q[n], (n, m)
+
+
+@pytest.mark.parametrize("bwd", ["stored", "recompute"])
+def test_upstream_gradients_of_either_sign(bwd):
+    m = G.negative_upstream_gradient(4, 21, 9, 64, 64, 512, 300, bwd)
+    for n in GRADS:
+        assert m[f"d{n}_rel_l2_q"] < GRAD_Q[n], (n, m)
+
+
 def test_hypothesis_random_shapes_against_the_oracle():
     # SURVEY.md section 4 item (4) for the fused boundary: randomly drawn dims and ragged lengths through every
     # own kernel (joint fwd / bwd, dh, dW2, the ordered reductions; H = 64 takes the library fall-backs). This test
@@ -135,6 +172,17 @@ def test_gemms_on_a_share_of_the_sms(pairs):
     m = G.dw2_gemm_vs_torch(8192, 4232, 512, sm_pairs=pairs)
     assert m["dw2_rel_l2"] < 1e-5 and m["db2_rel_l2"] < 1e-5 and m["bit_identical"], m
     m = G.dh_gemm_vs_torch(90, 777, 512, 3, 88, sm_pairs=pairs)
+    assert m["rel_l2"] < 4e-3 and m["outside_untouched"], m
+
+
+@pytest.mark.parametrize("pairs", [0, 37])
+def test_gemms_with_row_factors(pairs):
+    # the stored-exponentials backward: dS = diag(g) . E, so g enters dh in the epilogue and db2 as row weights
+    m = G.dw2_gemm_vs_torch(8192, 4232, 512, sm_pairs=pairs, weighted=True)
+    assert m["dw2_rel_l2"] < 1e-5 and m["db2_rel_l2"] < 1e-5 and m["bit_identical"], m
+    m = G.dh_gemm_vs_torch(90, 777, 512, 3, 88, sm_pairs=pairs, scaled=True)
+    assert m["rel_l2"] < 4e-3 and m["outside_untouched"], m
+    m = G.dh_gemm_vs_torch(5, 4232, 512, 1, 4, scaled=True)
     assert m["rel_l2"] < 4e-3 and m["outside_untouched"], m
 
 

@@ -1,17 +1,16 @@
 #!/bin/bash
 # scratch GPU script of the current call
 mkdir -p gpurun_out
-TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29511"
-for v in nobal1 bal1 nobal2 bal2; do
-  fl=""; case $v in nobal*) fl="--no-balance";; esac
-  timeout 240 $TR bench.py --gpus 8 --steps 20 --warmup 5 $fl > gpurun_out/e2_n8_$v.json 2> gpurun_out/e2_n8_$v.err; echo "$v rc=$?"
+timeout 900 python -m pytest tests/test_fused_gpu.py -x -q -m gpu -k "synthetic or golden or row_factors or stored or either_sign or config or deterministic or chunks or headline or graphed or hypothesis" > gpurun_out/f1_tests.log 2>&1; echo "tests rc=$?"; tail -5 gpurun_out/f1_tests.log
+for v in stored recompute stored2 recompute2; do
+  RNNT_B200_BWD=${v%2} timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/f1_$v.json 2> gpurun_out/f1_$v.err; echo "$v rc=$?"
 done
-for f in nobal1 bal1 nobal2 bal2; do python - <<PY
+for f in stored recompute stored2 recompute2; do python - <<PY
 import json
 try:
-    l=json.loads(open("gpurun_out/e2_n8_$f.json").read().strip().splitlines()[-1])
-    print("$f", round(l["ms_per_step"],3), round(l["value"]/1e6,2), round(l["e2e"]["ms_per_step"],3), l["config"].get("speed_weighted_sharding"), l["path"].get("allreduce_ms_per_rank"))
+    l=json.loads(open("gpurun_out/f1_$f.json").read().strip().splitlines()[-1])
+    print("$f", round(l["ms_per_step"],3), round(l["value"]/1e6,2), "e2e", round(l["e2e"]["ms_per_step"],3), "loss", l["loss"], l["path"]["kernel_ms_one_step"], l["clocks"]["sm_mhz"])
 except Exception as e:
-    print("$f FAILED", e); print(open("gpurun_out/e2_n8_$f.err").read()[-1500:])
+    print("$f FAILED", e); print(open("gpurun_out/f1_$f.err").read()[-1500:])
 PY
 done
