@@ -452,7 +452,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
 #pragma unroll
               for (int j = 0; j < 8; ++j) gp_hold[j] = gp[j];
             } else {
-              if (lane == 0) bulk_wait_group_read0();
+              if (lane == 0 && !(RNNT_DBG(p) & 32)) bulk_wait_group_read0();
               __syncwarp();
               uint8_t* srow = stage_w + lane * 64;
               const int swz = (lane >> 1) & 3;
@@ -473,7 +473,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
                 const int off = (label - cbase) * 2;
                 *reinterpret_cast<__nv_bfloat16*>(srow + (((off >> 4) ^ swz) << 4) + (off & 15)) = __float2bfloat16_rn(g_label);
               }
-              fence_proxy_async_smem();
+              if (!(RNNT_DBG(p) & 64)) fence_proxy_async_smem();
               __syncwarp();
               if (lane == 0 && !dead && !(RNNT_DBG(p) & 16)) {
                 tma_store_2d(&map_ds, stage_w, cbase, (tile - p.tile_lo) * RNNT_TILE_M + q * 32);
@@ -789,23 +789,33 @@ hidden_kernel(const JointParams p, int max_tiles) {
 //   dh = diag(g) (E . W2)      -> row_scale[row] = g, applied in the dh GEMM's epilogue
 //   dW2 = E^T (diag(g) h)      -> h_scaled = bf16(g h), the dW2 GEMM's B operand
 //   db2 = E^T g                -> the dW2 kernel's column sums, weighted with row_scale
-// One CTA per tile: 128 threads take a row each (g, the two patches), then all 256 scale the tile's h rows.
+// One CTA per tile, one warp per 16 rows: the rows' h chunks are requested first (they do not depend on g), lanes
+// 0-15 then work out g and the two patches of one row each, and the factors reach the scaling through shuffles.
 // A row whose c0 is below 1e-30 (or whose g leaves the fp32 range) contributes nothing: g = 0, no patch.
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 patch_scale_kernel(const JointParams p, float* __restrict__ row_scale, __nv_bfloat16* __restrict__ h_scaled,
                    int max_tiles) {
-  __shared__ float gs[RNNT_TILE_M];
   const int n_tiles = min(p.n_tiles[0], max_tiles);
-  const int cpr = p.H / 8;              // 16-byte chunks per row
-  const int rows_per_pass = 256 / cpr;  // H = 512: 4 rows per pass
-  const int chunk = threadIdx.x % cpr, rsub = threadIdx.x / cpr;
+  const int cpr = p.H / 8;  // 16-byte chunks per row (16, 32 or 64)
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r0 = warp * 16;
   for (int tile = blockIdx.x; tile < max_tiles; tile += gridDim.x) {
     const bool dead = tile >= n_tiles;
-    if (threadIdx.x < RNNT_TILE_M) {
-      const int r = threadIdx.x;
+    const uint4* src = reinterpret_cast<const uint4*>(p.h_stash + ((size_t)tile * RNNT_TILE_M + r0) * p.H);
+    uint4* dst = reinterpret_cast<uint4*>(h_scaled + ((size_t)tile * RNNT_TILE_M + r0) * p.H);
+    uint4 hv[8][2];
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = lane + 32 * cc;
+        hv[j][cc] = (c < cpr && !dead) ? ld_stream_u4(src + (size_t)j * cpr + c) : make_uint4(0u, 0u, 0u, 0u);
+      }
+    float g = 0.f;
+    if (lane < 16) {
+      const int r = r0 + lane;
       const RowCoord rc = locate_row(p, tile, r, dead);
-      float g = 0.f;
       if (rc.valid) {
         const size_t pidx = plane_index(rc.b, rc.t, rc.u, p.T, p.U1);
         const float sc = p.scale[rc.b];
@@ -828,30 +838,35 @@ patch_scale_kernel(const JointParams p, float* __restrict__ row_scale, __nv_bflo
           if (label >= 0) erow[label] = __float2bfloat16_rn(g_label * inv);
         }
       }
-      gs[r] = g;
       row_scale[(size_t)tile * RNNT_TILE_M + r] = g;
     }
-    __syncthreads();
-    if (rsub < rows_per_pass) {
-      const uint4* src = reinterpret_cast<const uint4*>(p.h_stash + (size_t)tile * RNNT_TILE_M * p.H) + chunk;
-      uint4* dst = reinterpret_cast<uint4*>(h_scaled + (size_t)tile * RNNT_TILE_M * p.H) + chunk;
-#pragma unroll 4
-      for (int row = rsub; row < RNNT_TILE_M; row += rows_per_pass) {
-        const float g = gs[row];
-        uint4 o = make_uint4(0u, 0u, 0u, 0u);
-        if (g != 0.f) {
-          const uint4 w = ld_stream_u4(src + (size_t)row * cpr);
-          const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
-          uint32_t oo[4];
+    auto scale_rows = [&](int jbase) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            oo[j] = pack_bf16x2(g * __uint_as_float(ww[j] << 16), g * __uint_as_float(ww[j] & 0xffff0000u));
-          o = make_uint4(oo[0], oo[1], oo[2], oo[3]);
+      for (int j = 0; j < 8; ++j) {
+        const float gj = __shfl_sync(0xffffffffu, g, jbase + j);
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+          const int c = lane + 32 * cc;
+          if (c < cpr) {
+            const uint32_t ww[4] = {hv[j][cc].x, hv[j][cc].y, hv[j][cc].z, hv[j][cc].w};
+            uint32_t oo[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              oo[k] = pack_bf16x2(gj * __uint_as_float(ww[k] << 16), gj * __uint_as_float(ww[k] & 0xffff0000u));
+            dst[(size_t)(jbase + j) * cpr + c] = make_uint4(oo[0], oo[1], oo[2], oo[3]);
+          }
         }
-        dst[(size_t)row * cpr] = o;
       }
-    }
-    __syncthreads();  // gs[] is free again
+    };
+    scale_rows(0);
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = lane + 32 * cc;
+        hv[j][cc] = (c < cpr && !dead) ? ld_stream_u4(src + (size_t)(8 + j) * cpr + c) : make_uint4(0u, 0u, 0u, 0u);
+      }
+    scale_rows(8);
   }
 }
 

@@ -152,6 +152,40 @@ def test_dh_gemm_and_reduce_reject_bad_arguments():
     assert L.rnnt_b200_build_tiles(a, a, 1, 4, 2, 99, a, a, a, None) == -2       # tile_cap above the padded bound
 
 
+def test_stored_exponentials_entry_points_reject_bad_arguments():
+    # the backward without the second vocabulary GEMM (include/rnnt_b200.h): argument checks come before any launch
+    L = _lib.lib()
+    a = 256
+    fwd = lambda **kw: L.rnnt_b200_joint_fwd_store(
+        a, a, a, a, a, a, a, a, a, kw.get("B", 2), 8, 5, kw.get("V", 100), kw.get("H", 512), kw.get("blank", 0),
+        kw.get("cap", 2), a, a, a, kw.get("kref", a), kw.get("e", a), None)
+    assert fwd(kref=None) == -1 and fwd(e=None) == -1
+    assert fwd(H=100) == -2 and fwd(cap=999) == -2 and fwd(blank=100) == -3
+    assert fwd(e=a + 2) == -4
+    ps = lambda **kw: L.rnnt_b200_patch_scale(a, a, a, a, a, a, a, a, a, a, a, a, a, a, 2, 8, 5, 100, kw.get("H", 512), 0,
+                                              kw.get("cap", 2), kw.get("e", a), kw.get("rs", a), a, None)
+    assert ps(e=None) == -1 and ps(rs=None) == -1
+    assert ps(H=192) == -2 and ps(H=64) == -2 and ps(cap=0) == -2       # H with tail columns in the stash: unsupported
+    assert L.rnnt_b200_dh_gemm_scaled(a, a, a, None, 100, 512, 4, 0, 4, 0, a, None) == -1
+    assert L.rnnt_b200_dh_gemm_scaled(a, a, a, a, 100, 512, 4, 2, 5, 0, a, None) == -2
+    assert L.rnnt_b200_dh_gemm_scaled(a, a, a, a, 100, 512, 4, 2, 2, 0, a, None) == 0    # nothing to do
+    assert L.rnnt_b200_dw2_gemm_weighted(a, a, None, 128, 100, 512, 0, a, a, None) == -1
+    assert L.rnnt_b200_dw2_gemm_weighted(a, a, a, 128, 100, 256, 0, a, a, None) == -2   # H = 512 only
+    assert L.rnnt_b200_dw2_gemm_weighted(a, a, a, 100, 100, 512, 0, a, a, None) == -2   # rows % 64
+
+
+def test_backward_mode_selection(monkeypatch):
+    from rnnt_transducer_b200 import _api
+    monkeypatch.delenv("RNNT_B200_BWD", raising=False)
+    assert _api._store_exponentials(512, 12625, 4288)             # AISHELL step: 13.9 GB of exponentials
+    assert not _api._store_exponentials(256, 100, 320)            # kernels of the stored path cover H = 512
+    assert not _api._store_exponentials(512, 60000, 4288)         # 65.9 GB: over the default budget -> recompute
+    monkeypatch.setenv("RNNT_B200_BWD", "recompute")
+    assert not _api._store_exponentials(512, 100, 4288)
+    monkeypatch.setenv("RNNT_B200_BWD", "stored")
+    assert _api._store_exponentials(512, 60000, 4288) and not _api._store_exponentials(128, 10, 64)
+
+
 def test_host_tile_count_applies_the_device_clamps():
     from rnnt_transducer_b200._api import _tile_count
     # t = 0 counts as one frame, lengths above the padded dims are cut: same clamps as build_tiles_kernel

@@ -9,7 +9,10 @@ import os, sys, struct
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 os.environ["RNNT_B200_TRACE"] = "gpurun_out/trace_fwd.bin"
 BWD = len(sys.argv) > 1 and sys.argv[1] == "bwd"
-os.environ["RNNT_B200_DEBUG_MODE"] = "1" if BWD else "0"
+STORE = len(sys.argv) > 1 and sys.argv[1] == "store"     # the forward that stores its exponentials (MODE 2)
+os.environ["RNNT_B200_DEBUG_MODE"] = "1" if BWD else "2" if STORE else "0"
+if BWD:
+    os.environ["RNNT_B200_BWD"] = "recompute"
 import numpy as np, torch, rnnt_transducer_b200 as R
 B,T,U,E,D,H,V = 32,500,100,320,320,512,4232
 dev="cuda:0"; g=torch.Generator().manual_seed(0)
@@ -17,7 +20,10 @@ joint=R.JointNet(E+D,H,V).to(dev); f=R.JointRNNTLoss(joint, reduction="none")
 enc=torch.randn(B,T,E,generator=g).to(dev); dec=torch.randn(B,U+1,D,generator=g).to(dev)
 y=torch.randint(1,V,(B,U),generator=g,dtype=torch.int32).to(dev)
 tl=torch.full((B,),T,dtype=torch.int32,device=dev); ul=torch.full((B,),U,dtype=torch.int32,device=dev)
-if BWD:
+if STORE:
+    enc.requires_grad_(True); dec.requires_grad_(True)
+    for _ in range(2): f(enc,dec,y,tl,ul)
+elif BWD:
     enc.requires_grad_(True); dec.requires_grad_(True)
     for _ in range(2): f(enc,dec,y,tl,ul).sum().backward()
 else:
