@@ -72,7 +72,9 @@ def make_config(args, wl, world):
         cfg["model"] = "AISHELL transducer: 4x320 biLSTM encoder, 1x512 LSTM decoder, joint 640->512->4232"
         cfg["l2"] = "working set per step (activations of 32 x 500 frames, h stash 0.84 GB) exceeds the 126 MB L2"
     else:
-        cfg["l2"] = "working set per step (h stash 1.7 GB, dS staging up to 4 GB) exceeds the 126 MB L2"
+        gb = B * T * (U + 1) * 2e-9
+        cfg["l2"] = (f"working set per step (h stash {gb * wl['H']:.2f} GB, exponentials / logit gradients "
+                     f"{gb * wl['V']:.1f} GB) exceeds the 126 MB L2")
     return cfg
 
 
@@ -305,10 +307,15 @@ def roofline_objects(R, wl, cells, ks, kern_ms, ms_step, steps, workload):
                 "traffic": traffic_tab.get(own[k][1]), "traffic_source": f"{traffic_src} (committed ncu capture)",
                 "kernel_ms": ms / n, "launches_per_step": n, "share_of_step": ms / ms_step}
 
+    stored = kern_ms.get("joint_fwd_store", 0.0) > 0    # the backward ran from the forward's stored exponentials
+    if stored:
+        own["dh_dw2_pair"] = (own["dh_dw2_pair"][0], "dh_dw2_pair_stored_dram_bytes_per_chunk", 2)
     # the kernel (or side-by-side pair) with the largest time per 2*H*V flop/cell of work it does
     dominant = max(own, key=lambda k: kern_ms.get(k, 0.0) / own[k][2])
     total_alg = 6.0 * H * V * cells
-    path = {"algorithmic_tflops": total_alg / (ms_step * 1e-3) / 1e12,
+    path = {"backward": ("from the forward's stored exponentials: no second vocabulary GEMM (DESIGN.md 3.7)" if stored
+                         else "logit gradient recomputed in a second GEMM pass"),
+            "algorithmic_tflops": total_alg / (ms_step * 1e-3) / 1e12,
             "frac_of_sustained_peak": total_alg / (ms_step * 1e-3) / 1e12 / peak,
             "kernel_ms_one_step": {k: round(v, 4) for k, v in kern_ms.items()},
             # every vocabulary-sized GEMM of the step against the same peak (2*H*V flop per cell each;

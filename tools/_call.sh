@@ -1,6 +1,6 @@
 #!/bin/bash
 # scratch GPU script of the current call
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -q -m gpu > gpurun_out/h1_tests.log 2>&1; echo "tests rc=$?"; tail -8 gpurun_out/h1_tests.log
-timeout 300 python __graft_entry__.py smoke > gpurun_out/h1_smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/h1_smoke.log | cut -c1-600
-timeout 600 python bench.py > gpurun_out/h1_bench.json 2> gpurun_out/h1_bench.err; echo "bench rc=$?"; cut -c1-1500 gpurun_out/h1_bench.json
+timeout 300 python tools/profile_range.py step > gpurun_out/k1_plain.log 2>&1; echo "plain rc=$?"
+timeout 900 ncu --replay-mode app-range --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/k1_range_step.csv python tools/profile_range.py step > gpurun_out/k1_ncu.log 2>&1; echo "ncu rc=$?"
+cat gpurun_out/k1_range_step.csv | tail -8
