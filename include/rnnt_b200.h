@@ -247,7 +247,9 @@ int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long long rows, 
  *   overwritten with (their dS, formed from lp_blank / lp_label as in joint_bwd_ds) / g[row], so that afterwards
  *   dS = diag(g) . e everywhere. Writes row_scale[tile*128 + r] = g (float32, tile_cap*128; 0 for rows without a cell
  *   and for cells with scale (c_blank + c_label) below 1e-30) and h_scaled = bf16(g * h) (same shape as h_stash).
- *   H in {128, 256, 512} (no tail columns in the stash). scale may have either sign.
+ *   H in {128, 256, 512} (no tail columns in the stash). scale may have either sign. Works on the tiles
+ *   [tile_lo, tile_hi) (pointers are those of tile 0); max_ctas > 0 bounds the grid (a caller that runs it beside
+ *   other kernels; measured beside the two GEMMs of the previous chunk it did not pay: profiles/r02_notes.md).
  *
  * rnnt_b200_dh_gemm_scaled: rnnt_b200_dh_gemm with A = e (chunk rows [tile_lo*128, tile_hi*128) at e_bf16) and
  *   dpre[row, j] = bf16( row_scale[row] * (sum_v e[row, v] W2[v, j]) * (1 - h[row, j]^2) ); row_scale is indexed by
@@ -264,6 +266,7 @@ int rnnt_b200_patch_scale(const void* h_stash, const int32_t* labels, const int3
                           const int32_t* n_tiles, const float* lse, const float* lp_blank, const float* lp_label,
                           const float* kref, const float* c_blank, const float* c_label, const float* scale,
                           int B, int T, int U1, int V, int H, int blank, int tile_cap,
+                          int tile_lo, int tile_hi, int max_ctas,
                           void* e_inout, float* row_scale, void* h_scaled, void* stream);
 int rnnt_b200_dh_gemm_scaled(const void* e_bf16, const void* w2t_bf16, const void* h_stash, const float* row_scale,
                              int V, int H, int tile_cap, int tile_lo, int tile_hi, int sm_pairs, void* dpre_bf16,

@@ -122,10 +122,10 @@ class _region:
 _side_streams = {}
 
 
-def _side_stream(dev):
-    """One side stream per device for the kernels that run beside the current stream (created once: a new stream per
-    backward call would cost a cudaStreamCreate each)."""
-    key = (dev.type, dev.index if dev.index is not None else torch.cuda.current_device())
+def _side_stream(dev, which=0):
+    """Side streams (one per device and role) for the kernels that run beside the current stream (created once: a
+    new stream per backward call would cost a cudaStreamCreate each)."""
+    key = (dev.type, dev.index if dev.index is not None else torch.cuda.current_device(), which)
     s = _side_streams.get(key)
     if s is None:
         s = _side_streams[key] = torch.cuda.Stream(device=dev)
@@ -327,7 +327,15 @@ class _JointLossFn(torch.autograd.Function):
             Vds = L.rnnt_b200_ds_pitch(V)
             e_st = kref = None
             if need_grad and _store_exponentials(H, max_tiles, Vds):
-                e_st = torch.empty(max_tiles * 128, Vds, dtype=torch.bfloat16, device=dev)
+                try:
+                    e_st = torch.empty(max_tiles * 128, Vds, dtype=torch.bfloat16, device=dev)
+                except torch.cuda.OutOfMemoryError:
+                    # within the budget but not free on this device right now: the recomputing backward needs
+                    # 4 GiB of staging instead (still this package's CUDA path, nothing leaves the GPU)
+                    if os.environ.get("RNNT_B200_BWD", "auto") == "stored":
+                        raise
+                    e_st = None
+            if e_st is not None:
                 kref = torch.empty(n, dtype=torch.float32, device=dev)
                 _call("joint_fwd_store", L.rnnt_b200_joint_fwd_store, _ptr(h_stash), _ptr(w2q), _ptr(b2l),
                       _ptr(labels), _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt), _ptr(tile_cell0),
@@ -385,10 +393,12 @@ class _JointLossFn(torch.autograd.Function):
                 # patch_scale_kernel): no second vocabulary GEMM, the consumers read E chunk by chunk
                 row_scale = torch.empty(max_tiles * 128, dtype=torch.float32, device=dev)
                 h_scaled = torch.empty_like(h_stash)
-                _call("patch_scale", L.rnnt_b200_patch_scale, _ptr(h_stash), _ptr(labels), _ptr(act_lens),
-                      _ptr(label_lens), _ptr(tile_utt), _ptr(tile_cell0), _ptr(n_tiles), _ptr(lse), _ptr(lpb),
-                      _ptr(lpl), _ptr(kref), _ptr(cb), _ptr(cl), _ptr(scale), B, T, U1, V, H, blank, max_tiles,
-                      _ptr(e_st), _ptr(row_scale), _ptr(h_scaled), st)
+
+                def patch(lo, hi, max_ctas, stream):
+                    _call("patch_scale", L.rnnt_b200_patch_scale, _ptr(h_stash), _ptr(labels), _ptr(act_lens),
+                          _ptr(label_lens), _ptr(tile_utt), _ptr(tile_cell0), _ptr(n_tiles), _ptr(lse), _ptr(lpb),
+                          _ptr(lpl), _ptr(kref), _ptr(cb), _ptr(cl), _ptr(scale), B, T, U1, V, H, blank, max_tiles,
+                          lo, hi, max_ctas, _ptr(e_st), _ptr(row_scale), _ptr(h_scaled), stream)
             else:
                 ds = torch.empty(chunk * 128, Vds, dtype=torch.bfloat16, device=dev)
             # dpre = dh * (1 - h^2), bf16, all M rows (M x H, never M x V): written chunk by chunk, reduced once
@@ -402,6 +412,8 @@ class _JointLossFn(torch.autograd.Function):
                 dw2x = torch.zeros(hp, Vds, dtype=torch.float32, device=dev)  # [dW2 | db2 | unused rows]^T
             w2v = w2q[:Vds]                          # rows Vds..Vpad of the pack are padding only
             slot = 0
+            if stored:
+                patch(0, max_tiles, 0, st)
             for ci, (lo, hi) in enumerate(bounds):
                 rows = (hi - lo) * 128
                 if stored:

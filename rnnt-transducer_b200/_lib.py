@@ -43,7 +43,7 @@ SIGNATURES = {
     "rnnt_b200_dh_gemm_supported": (_i, [_i]),
     "rnnt_b200_dh_gemm": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p]),
     "rnnt_b200_joint_fwd_store": (_i, [_p] * 9 + [_i] * 7 + [_p] * 6),
-    "rnnt_b200_patch_scale": (_i, [_p] * 14 + [_i] * 7 + [_p] * 4),
+    "rnnt_b200_patch_scale": (_i, [_p] * 14 + [_i] * 10 + [_p] * 4),
     "rnnt_b200_dh_gemm_scaled": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p]),
     "rnnt_b200_dw2_gemm_weighted": (_i, [_p, _p, _p, ctypes.c_longlong, _i, _i, _i, _p, _p, _p]),
     "rnnt_b200_dpre_reduce_scratch_elems": (ctypes.c_size_t, [_i, _i, _i, _i]),

@@ -423,11 +423,25 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
                 float d0, d1, d2, d3;
                 fadd2(d0, d1, zc[2 * j], zc[2 * j + 1], nl, nl);
                 fadd2(d2, d3, zc[2 * j + 2], zc[2 * j + 3], nl, nl);
+#ifdef RNNT_B200_TUNE
+                const bool no_mufu = RNNT_DBG(p) & 256;  // timing experiments: what the MUFU / the conversions cost
+                const float e0 = no_mufu ? d0 : ex2_approx(d0), e1 = no_mufu ? d1 : ex2_approx(d1);
+                const float e2 = no_mufu ? d2 : ex2_approx(d2), e3 = no_mufu ? d3 : ex2_approx(d3);
+#else
                 const float e0 = ex2_approx(d0), e1 = ex2_approx(d1), e2 = ex2_approx(d2), e3 = ex2_approx(d3);
+#endif
                 fadd2(a0, a1, a0, a1, e0, e1);
                 fadd2(a2, a3, a2, a3, e2, e3);
-                gp[j] = pack_bf16x2(e0, e1);
-                gp[j + 1] = pack_bf16x2(e2, e3);
+#ifdef RNNT_B200_TUNE
+                if (RNNT_DBG(p) & 128) {  // truncating pack on the integer pipe instead of cvt.rn.bf16x2
+                  gp[j] = __byte_perm(__float_as_uint(e0), __float_as_uint(e1), 0x7632);
+                  gp[j + 1] = __byte_perm(__float_as_uint(e2), __float_as_uint(e3), 0x7632);
+                } else
+#endif
+                {
+                  gp[j] = pack_bf16x2(e0, e1);
+                  gp[j + 1] = pack_bf16x2(e2, e3);
+                }
               }
               s += (a0 + a1) + (a2 + a3);
               const bool hit_b = (unsigned)(p.blank - col0) < 16u, hit_l = (unsigned)(label - col0) < 16u;
@@ -448,7 +462,8 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
             // st.global from the staged tile, 6.6 ms, and one 32-byte st.global per lane and chunk
             // straight from registers, 8.7 ms, against 5.65 ms.)
             const bool last = c + 1 == nchk;
-            if ((c & 1) == 0 && !last) {
+            if (RNNT_DBG(p) & 512) {  // timing experiments: no staging at all (results invalid)
+            } else if ((c & 1) == 0 && !last) {
 #pragma unroll
               for (int j = 0; j < 8; ++j) gp_hold[j] = gp[j];
             } else {
@@ -794,13 +809,12 @@ hidden_kernel(const JointParams p, int max_tiles) {
 // A row whose c0 is below 1e-30 (or whose g leaves the fp32 range) contributes nothing: g = 0, no patch.
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-patch_scale_kernel(const JointParams p, float* __restrict__ row_scale, __nv_bfloat16* __restrict__ h_scaled,
-                   int max_tiles) {
-  const int n_tiles = min(p.n_tiles[0], max_tiles);
+patch_scale_kernel(const JointParams p, float* __restrict__ row_scale, __nv_bfloat16* __restrict__ h_scaled) {
+  const int n_tiles = min(p.n_tiles[0], p.tile_hi);
   const int cpr = p.H / 8;  // 16-byte chunks per row (16, 32 or 64)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r0 = warp * 16;
-  for (int tile = blockIdx.x; tile < max_tiles; tile += gridDim.x) {
+  for (int tile = p.tile_lo + blockIdx.x; tile < p.tile_hi; tile += gridDim.x) {
     const bool dead = tile >= n_tiles;
     const uint4* src = reinterpret_cast<const uint4*>(p.h_stash + ((size_t)tile * RNNT_TILE_M + r0) * p.H);
     uint4* dst = reinterpret_cast<uint4*>(h_scaled + ((size_t)tile * RNNT_TILE_M + r0) * p.H);
@@ -1185,8 +1199,9 @@ extern "C" int rnnt_b200_patch_scale(const void* h_stash, const int32_t* labels,
                                      const int32_t* tile_cell0, const int32_t* n_tiles, const float* lse,
                                      const float* lp_blank, const float* lp_label, const float* kref,
                                      const float* c_blank, const float* c_label, const float* scale, int B,
-                                     int T, int U1, int V, int H, int blank, int tile_cap, void* e_inout,
-                                     float* row_scale, void* h_scaled, void* stream) {
+                                     int T, int U1, int V, int H, int blank, int tile_cap, int tile_lo,
+                                     int tile_hi, int max_ctas, void* e_inout, float* row_scale, void* h_scaled,
+                                     void* stream) {
   if (!h_stash || !act_lens || !label_lens || !tile_utt || !tile_cell0 || !n_tiles || !lse || !lp_blank ||
       !lp_label || !kref || !c_blank || !c_label || !scale || !e_inout || !row_scale || !h_scaled)
     return RNNT_B200_E_NULL;
@@ -1195,7 +1210,9 @@ extern "C" int rnnt_b200_patch_scale(const void* h_stash, const int32_t* labels,
   if (rc) return rc;
   if (rnnt_hp(H) != H) return RNNT_B200_E_SHAPE;  // H in {128, 256, 512}: the stash has no tail columns
   if (tile_cap < 1 || tile_cap > rnnt_b200_max_tiles(B, T, U1)) return RNNT_B200_E_SHAPE;
+  if (tile_lo < 0 || tile_hi < tile_lo || tile_hi > tile_cap) return RNNT_B200_E_SHAPE;
   if (((uintptr_t)h_stash & 15) || ((uintptr_t)h_scaled & 15) || ((uintptr_t)e_inout & 1)) return RNNT_B200_E_ALIGN;
+  if (tile_hi == tile_lo) return RNNT_B200_OK;
   if (const int arch = rnnt_check_arch()) return arch;
   JointParams p = {};
   p.labels = labels; p.act_lens = act_lens; p.label_lens = label_lens;
@@ -1206,9 +1223,12 @@ extern "C" int rnnt_b200_patch_scale(const void* h_stash, const int32_t* labels,
   p.h_stash = (__nv_bfloat16*)const_cast<void*>(h_stash);
   p.ds = (__nv_bfloat16*)e_inout;
   p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vds = rnnt_b200_ds_pitch(V); p.H = H; p.blank = blank;
-  const int sms = sm_count();
-  const int grid = tile_cap < sms * 8 ? tile_cap : sms * 8;
-  patch_scale_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p, row_scale, (__nv_bfloat16*)h_scaled, tile_cap);
+  p.tile_lo = tile_lo; p.tile_hi = tile_hi;
+  const int ntile = tile_hi - tile_lo;
+  int grid = sm_count() * 2;  // two CTAs of 256 threads per SM (127 registers per thread)
+  if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+  if (ntile < grid) grid = ntile;
+  patch_scale_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p, row_scale, (__nv_bfloat16*)h_scaled);
   RNNT_CUDA_RETURN_IF_ERROR();
   return RNNT_B200_OK;
 }

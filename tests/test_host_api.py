@@ -163,9 +163,11 @@ def test_stored_exponentials_entry_points_reject_bad_arguments():
     assert fwd(H=100) == -2 and fwd(cap=999) == -2 and fwd(blank=100) == -3
     assert fwd(e=a + 2) == -4
     ps = lambda **kw: L.rnnt_b200_patch_scale(a, a, a, a, a, a, a, a, a, a, a, a, a, a, 2, 8, 5, 100, kw.get("H", 512), 0,
-                                              kw.get("cap", 2), kw.get("e", a), kw.get("rs", a), a, None)
+                                              kw.get("cap", 2), kw.get("lo", 0), kw.get("hi", 2), 0,
+                                              kw.get("e", a), kw.get("rs", a), a, None)
     assert ps(e=None) == -1 and ps(rs=None) == -1
     assert ps(H=192) == -2 and ps(H=64) == -2 and ps(cap=0) == -2       # H with tail columns in the stash: unsupported
+    assert ps(lo=1, hi=3) == -2 and ps(lo=2, hi=1) == -2 and ps(lo=1, hi=1) == 0   # tile range; empty: nothing to do
     assert L.rnnt_b200_dh_gemm_scaled(a, a, a, None, 100, 512, 4, 0, 4, 0, a, None) == -1
     assert L.rnnt_b200_dh_gemm_scaled(a, a, a, a, 100, 512, 4, 2, 5, 0, a, None) == -2
     assert L.rnnt_b200_dh_gemm_scaled(a, a, a, a, 100, 512, 4, 2, 2, 0, a, None) == 0    # nothing to do

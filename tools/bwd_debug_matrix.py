@@ -28,7 +28,7 @@ for var in (sys.argv[1:] or ["-"]):
     row = []
     for dbg in os.environ.get("DBGS", "0,1,16,4,5").split(","):
         env = dict(os.environ, RNNT_B200_DEBUG=dbg, RNNT_B200_DEBUG_MODE=os.environ.get("MODE", "1"))
-        if env["RNNT_B200_DEBUG_MODE"] == "1":
+        if env["RNNT_B200_DEBUG_MODE"] in ("0", "1"):
             env["RNNT_B200_BWD"] = "recompute"
         if var != "-":
             for kv in var.split(","):
