@@ -141,6 +141,52 @@ __device__ __forceinline__ void tanh4(const float (&x)[4], float (&y)[4]) {
   y[3] = fmaf(-2.f, r23 * d[2], 1.f);
 }
 
+// z[i & 15] out of a register tile: a four-level select tree inside the rare branch that needs it (a dynamically
+// indexed local array put 16 stores and a dependent load into that branch: the epilogue's stall samples sat there).
+__device__ __forceinline__ float pick16(const float* z, int i) {
+  const bool b0 = i & 1, b1 = i & 2, b2 = i & 4, b3 = i & 8;
+  float a[8], b[4];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) a[j] = b0 ? z[2 * j + 1] : z[2 * j];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) b[j] = b1 ? a[2 * j + 1] : a[2 * j];
+  const float c0 = b2 ? b[1] : b[0], c1 = b2 ? b[3] : b[2];
+  return b3 ? c1 : c0;
+}
+
+// Two such groups of four side by side on the packed f32x2 pipe (element i of group a with element i of group b):
+// the same operations in the same order and rounding as tanh4, in 43 instead of 68 floating-point instructions
+// per eight values (hidden_kernel is issue bound: 77 % issue-active under ncu).
+__device__ __forceinline__ void tanh4x2(const float (&xa)[4], const float (&xb)[4], float (&ya)[4], float (&yb)[4]) {
+  float da[4], db[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float ta, tb;
+    fmul2(ta, tb, xa[i] > 10.f ? 10.f : xa[i], xb[i] > 10.f ? 10.f : xb[i], 2.f * RNNT_LOG2E, 2.f * RNNT_LOG2E);
+    fadd2(da[i], db[i], ex2_approx(ta), ex2_approx(tb), 1.f, 1.f);
+  }
+  float p01a, p01b, p23a, p23b, pa, pb, ra, rb;
+  fmul2(p01a, p01b, da[0], db[0], da[1], db[1]);
+  fmul2(p23a, p23b, da[2], db[2], da[3], db[3]);
+  fmul2(pa, pb, p01a, p01b, p23a, p23b);
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ra) : "f"(pa));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rb) : "f"(pb));
+  float r01a, r01b, r23a, r23b;
+  fmul2(r01a, r01b, ra, rb, p23a, p23b);
+  fmul2(r23a, r23b, ra, rb, p01a, p01b);
+  float qa[4], qb[4];
+  fmul2(qa[0], qb[0], r01a, r01b, da[1], db[1]);
+  fmul2(qa[1], qb[1], r01a, r01b, da[0], db[0]);
+  fmul2(qa[2], qb[2], r23a, r23b, da[3], db[3]);
+  fmul2(qa[3], qb[3], r23a, r23b, da[2], db[2]);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    ya[i] = qa[i];
+    yb[i] = qb[i];
+    ffma2(ya[i], yb[i], -2.f, 1.f, 1.f);
+  }
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
@@ -395,16 +441,13 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
             }
             s = s * ex2_approx(m - mn) + ((a0 + a1) + (a2 + a3));
             m = mn;
-            // the blank / label logits: a dynamically indexed read of the chunk through a small
-            // local array, only in the rare chunk that holds one of them (selecting with 16
-            // compare+select pairs per chunk cost ~7 % of the epilogue's issue slots)
+            // the blank / label logits: picked out of the chunk's registers only in the rare chunk that
+            // holds one of them (selecting with 16 compare+select pairs in EVERY chunk cost ~7 % of the
+            // epilogue's issue slots)
             const bool hit_b = (unsigned)(p.blank - col0) < 16u, hit_l = (unsigned)(label - col0) < 16u;
             if (hit_b || hit_l) {
-              float tmp[16];
-#pragma unroll
-              for (int j = 0; j < 16; ++j) tmp[j] = zc[j];
-              if (hit_b) zb = tmp[(p.blank - col0) & 15];
-              if (hit_l) zl = tmp[(label - col0) & 15];
+              if (hit_b) zb = pick16(zc, p.blank - col0);
+              if (hit_l) zl = pick16(zc, label - col0);
             }
           } else {
             uint32_t gp[8];
@@ -446,11 +489,8 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
               s += (a0 + a1) + (a2 + a3);
               const bool hit_b = (unsigned)(p.blank - col0) < 16u, hit_l = (unsigned)(label - col0) < 16u;
               if (hit_b || hit_l) {
-                float tmp[16];
-#pragma unroll
-                for (int j = 0; j < 16; ++j) tmp[j] = zc[j];
-                if (hit_b) zb = tmp[(p.blank - col0) & 15];
-                if (hit_l) zl = tmp[(label - col0) & 15];
+                if (hit_b) zb = pick16(zc, p.blank - col0);
+                if (hit_l) zl = pick16(zc, label - col0);
               }
             }
             // 32 cells x 32 columns of bf16 (two chunks) -> this warp's 2 KB staging tile (64-byte
@@ -776,11 +816,13 @@ hidden_kernel(const JointParams p, int max_tiles) {
             e1 = __ldg(pe4 + (size_t)t * h4 + 1);
             t_have = t;
           }
-          const float xa[4] = {e0.x + d0.x, e0.y + d0.y, e0.z + d0.z, e0.w + d0.w};
-          const float xb[4] = {e1.x + d1.x, e1.y + d1.y, e1.z + d1.z, e1.w + d1.w};
+          float xa[4], xb[4];
+          fadd2(xa[0], xb[0], e0.x, e1.x, d0.x, d1.x);
+          fadd2(xa[1], xb[1], e0.y, e1.y, d0.y, d1.y);
+          fadd2(xa[2], xb[2], e0.z, e1.z, d0.z, d1.z);
+          fadd2(xa[3], xb[3], e0.w, e1.w, d0.w, d1.w);
           float ya[4], yb[4];
-          tanh4(xa, ya);
-          tanh4(xb, yb);
+          tanh4x2(xa, xb, ya, yb);
           o.x = pack_bf16x2(ya[0], ya[1]);
           o.y = pack_bf16x2(ya[2], ya[3]);
           o.z = pack_bf16x2(yb[0], yb[1]);
@@ -804,16 +846,17 @@ hidden_kernel(const JointParams p, int max_tiles) {
 //   dh = diag(g) (E . W2)      -> row_scale[row] = g, applied in the dh GEMM's epilogue
 //   dW2 = E^T (diag(g) h)      -> h_scaled = bf16(g h), the dW2 GEMM's B operand
 //   db2 = E^T g                -> the dW2 kernel's column sums, weighted with row_scale
-// One CTA per tile, one warp per 16 rows: the rows' h chunks are requested first (they do not depend on g), lanes
-// 0-15 then work out g and the two patches of one row each, and the factors reach the scaling through shuffles.
+// One CTA of four warps per tile, one warp per 32 rows: the first rows' h chunks are requested first (they do not
+// depend on g), every lane then works out g and the two patches of one row, and the factors reach the scaling
+// through shuffles, eight rows at a time. (Four CTAs per SM: four tiles' dependent plane reads in flight.)
 // A row whose c0 is below 1e-30 (or whose g leaves the fp32 range) contributes nothing: g = 0, no patch.
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
 patch_scale_kernel(const JointParams p, float* __restrict__ row_scale, __nv_bfloat16* __restrict__ h_scaled) {
   const int n_tiles = min(p.n_tiles[0], p.tile_hi);
   const int cpr = p.H / 8;  // 16-byte chunks per row (16, 32 or 64)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int r0 = warp * 16;
+  const int r0 = warp * 32;
   for (int tile = p.tile_lo + blockIdx.x; tile < p.tile_hi; tile += gridDim.x) {
     const bool dead = tile >= n_tiles;
     const uint4* src = reinterpret_cast<const uint4*>(p.h_stash + ((size_t)tile * RNNT_TILE_M + r0) * p.H);
@@ -827,7 +870,7 @@ patch_scale_kernel(const JointParams p, float* __restrict__ row_scale, __nv_bflo
         hv[j][cc] = (c < cpr && !dead) ? ld_stream_u4(src + (size_t)j * cpr + c) : make_uint4(0u, 0u, 0u, 0u);
       }
     float g = 0.f;
-    if (lane < 16) {
+    {
       const int r = r0 + lane;
       const RowCoord rc = locate_row(p, tile, r, dead);
       if (rc.valid) {
@@ -873,14 +916,17 @@ patch_scale_kernel(const JointParams p, float* __restrict__ row_scale, __nv_bflo
       }
     };
     scale_rows(0);
+#pragma unroll 1
+    for (int jb = 8; jb < 32; jb += 8) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j)
+      for (int j = 0; j < 8; ++j)
 #pragma unroll
-      for (int cc = 0; cc < 2; ++cc) {
-        const int c = lane + 32 * cc;
-        hv[j][cc] = (c < cpr && !dead) ? ld_stream_u4(src + (size_t)(8 + j) * cpr + c) : make_uint4(0u, 0u, 0u, 0u);
-      }
-    scale_rows(8);
+        for (int cc = 0; cc < 2; ++cc) {
+          const int c = lane + 32 * cc;
+          hv[j][cc] = (c < cpr && !dead) ? ld_stream_u4(src + (size_t)(jb + j) * cpr + c) : make_uint4(0u, 0u, 0u, 0u);
+        }
+      scale_rows(jb);
+    }
   }
 }
 
@@ -1225,10 +1271,10 @@ extern "C" int rnnt_b200_patch_scale(const void* h_stash, const int32_t* labels,
   p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vds = rnnt_b200_ds_pitch(V); p.H = H; p.blank = blank;
   p.tile_lo = tile_lo; p.tile_hi = tile_hi;
   const int ntile = tile_hi - tile_lo;
-  int grid = sm_count() * 2;  // two CTAs of 256 threads per SM (127 registers per thread)
+  int grid = sm_count() * 4;  // four CTAs of 128 threads per SM
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   if (ntile < grid) grid = ntile;
-  patch_scale_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p, row_scale, (__nv_bfloat16*)h_scaled);
+  patch_scale_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(p, row_scale, (__nv_bfloat16*)h_scaled);
   RNNT_CUDA_RETURN_IF_ERROR();
   return RNNT_B200_OK;
 }
