@@ -400,34 +400,37 @@ def run_joint(args, wl, c):
     def step_resident(**kw):
         return step(S.d_enc.detach(), S.d_dec.detach(), S.d_y, S.d_tl, S.d_ul, **kw)
 
-    # Speed-weighted sharding (N > 1, --balance only): the GPUs of a box run at different clocks under their power
-    # caps and a synchronous step waits for the slowest, so the global batch can be dealt in proportion to each
-    # rank's measured speed (untimed local steps without the all-reduce; half of the measured difference is
-    # corrected, see shard_batch_weighted). The global batch and the loss / gradient normalisation do not change;
-    # utterances per rank are reported in `config`. OFF by default: on the boxes measured, which rank is slow
-    # changes from run to run and the dealt batch changed nothing (profiles/r02_notes.md).
+    # Speed-weighted sharding (N > 1, --balance): the GPUs of a box run at different clocks under their power caps
+    # and a synchronous step waits for the slowest, so the global batch is dealt in proportion to each rank's measured
+    # speed. Calibration = untimed steps of the real, synchronous step: a rank's compute time is the step minus its
+    # wait in the all-reduce; half of the measured difference is corrected (a rank that is given less work idles,
+    # regains power headroom and speeds up: shard_batch_weighted). The global batch and the loss / gradient
+    # normalisation do not change; utterances per rank are reported in `path`.
     balance = None
-    CAL_WARM, CAL_STEPS = 8, 10
+    CAL_WARM, CAL_STEPS = 4, 8
     if world > 1 and args.balance:
         try:
             for _ in range(CAL_WARM):
-                step_resident(allreduce=False)
+                step_resident()
             torch.cuda.synchronize()
             dist.barrier()
+            ar_events.clear()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             for _ in range(CAL_STEPS):
-                step_resident(allreduce=False)
+                step_resident(time_ar=True)
             e1.record()
             torch.cuda.synchronize()
-            t = torch.tensor([S.cells / (e0.elapsed_time(e1) / CAL_STEPS)], device=dev, dtype=torch.float64)
+            wait = sum(a.elapsed_time(b) for a, b in ar_events) / CAL_STEPS
+            ar_events.clear()
+            t = torch.tensor([S.cells / (e0.elapsed_time(e1) / CAL_STEPS - wait)], device=dev, dtype=torch.float64)
             rates = [torch.zeros_like(t) for _ in range(world)]
             dist.all_gather(rates, t)
             rates = [float(x) for x in rates]
-            shares = R.shard_batch_weighted(gtl.tolist(), gul.tolist(), rates, damping=0.5)
+            shares = R.shard_batch_weighted(gtl.tolist(), gul.tolist(), rates, min_spread=0.03, damping=0.5)
             balance = {"cells_per_ms_per_rank": [round(x, 1) for x in rates],
                        "utterances_per_rank": [len(s_) for s_ in shares], "damping": 0.5,
-                       "calibration": f"{CAL_WARM}+{CAL_STEPS} untimed local steps"}
+                       "calibration": f"{CAL_WARM}+{CAL_STEPS} untimed synchronous steps (step - all-reduce wait)"}
             if len(shares[rank]) != S.n or sorted(shares[rank]) != sorted(R.shard_batch(gtl.tolist(), gul.tolist(), world)[rank]):
                 deal(shares)
         except Exception as exc:      # never let the balancing take the measurement down: keep the equal split
@@ -526,7 +529,7 @@ def run_joint(args, wl, c):
 
     cfg = make_config(args, wl, world)
     if balance is not None:
-        cfg["speed_weighted_sharding"] = balance
+        path["speed_weighted_sharding"] = balance
     line = {
         "metric": METRIC, "value": cells_all / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
