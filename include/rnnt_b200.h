@@ -237,9 +237,11 @@ int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long long rows, 
  * rnnt_b200_joint_fwd_store: rnnt_b200_joint_fwd that also writes
  *   e_out[row, v] = bf16( exp2(z[row, v] log2 e - kref[cell]) )    (tile_cap*128 rows, pitch rnnt_b200_ds_pitch(V),
  *                                                                   16-byte aligned; rows without a cell: zeros)
- * and the plane kref (an integer-valued float per cell, laid out like lse: the exponent reference, 64 above the
- * largest of the first 16 logits the cell's row sees, so that later logits may exceed those by 190 (log2 units)
- * before fp32 overflows; an overflow shows as an infinite lse / loss). lse is formed from the fp32 sum of the same
+ * and the plane kref (an integer-valued float per cell, laid out like lse: the exponent reference, 86 above the
+ * largest of the first 16 logits the cell's row sees, so that later logits may exceed those by 213 log2 units
+ * (147 nats) before fp32 overflows; an overflow shows as an infinite lse / loss, never as a silently wrong one --
+ * a model whose logits spread wider than that takes rnnt_b200_joint_fwd and the recomputing backward, which use
+ * a running maximum). lse is formed from the fp32 sum of the same
  * exponentials (fixed reference instead of a running maximum).
  *
  * rnnt_b200_patch_scale (after rnnt_b200_lattice): with g[row] = scale_b (c_blank + c_label) exp2(kref - lse log2 e),

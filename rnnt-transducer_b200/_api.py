@@ -347,6 +347,11 @@ class _JointLossFn(torch.autograd.Function):
                                                  _ptr(tile_cell0), _ptr(n_tiles), B, T, U1, V, H, blank, max_tiles,
                                                  _ptr(lse), _ptr(lpb), _ptr(lpl), st)
             loss, cb, cl = _lattice(lpb, lpl, act_lens, label_lens, B, T, U1)
+            if e_st is not None and _validate() and not bool(torch.isfinite(loss).all()):   # opt-in: a device sync
+                raise FloatingPointError(
+                    "rnnt_b200: non-finite loss from the forward that stores its exponentials -- the logits of a "
+                    "lattice cell spread over more than ~147 nats (or the inputs hold NaN / inf); set "
+                    "RNNT_B200_BWD=recompute for such a model (running-maximum log-sum-exp, no range limit)")
         if need_grad:
             ctx.save_for_backward(labels, act_lens, label_lens, tile_utt, tile_cell0, n_tiles, w2q, b2l,
                                   lse, lpb, lpl, cb, cl, h_stash, w2t, e_st, kref)

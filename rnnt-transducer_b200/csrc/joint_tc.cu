@@ -217,8 +217,9 @@ __device__ __forceinline__ RowCoord locate_row(const JointParams& p, int tile, i
 // ---------------------------------------------------------------------------------------
 // MODE 0 = forward (online LSE epilogue), MODE 1 = backward dS (recomputed logits),
 // MODE 2 = forward that also STORES the exponentials: E[cell, v] = bf16(exp2(z - kref[cell])) with kref an
-// integer near the row's largest logit (from the first 16 columns the row sees, + 64: every later logit may
-// exceed them by 190 in log2 units before fp32 overflows, and what underflows is below 2^-62 of them), and
+// integer near the row's largest logit (from the first 16 columns the row sees, + 86: every later logit may
+// exceed them by 213 in log2 units = 147 nats before fp32 overflows -- the loss then comes out infinite, never
+// silently wrong -- and what flushes to zero is below 2^-40 of them, under the fp32 sum's resolution), and
 // sum(E) in fp32 gives the LSE with that same fixed reference. The backward then needs no second GEMM:
 // dS = diag(g) . E with g = scale (c_blank + c_label) exp2(kref - lse log2 e) per cell, after patch_scale_kernel
 // has overwritten the two one-hot entries of every row (csrc comment there).
@@ -394,7 +395,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
 #pragma unroll
             for (int j = 0; j < 16; ++j) cm = fmaxf(cm, fmaf(z0[j], RNNT_LOG2E, bias_c[j]));
             // NaN / infinite logits: any reference will do, the sum carries them into the loss
-            kref = (cm > -1.0e29f && cm < 1.0e29f) ? ceilf(cm) + 64.f : 0.f;
+            kref = (cm > -1.0e29f && cm < 1.0e29f) ? ceilf(cm) + 86.f : 0.f;
             kref_s[row] = kref;
             __threadfence_block();
             named_bar_arrive(4 + q, 64);
@@ -607,10 +608,20 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
         named_bar_sync(1, kEpiWarps * 32);
         if (half == 0 && rc.valid) {
           const float4 o = reinterpret_cast<const float4*>(smem_ds + (warp + 4) * 2048)[lane];
-          const float lg = log2f(s + o.y);
-          p.lse[pidx] = (kref + lg) * RNNT_LN2;
-          p.lpb[pidx] = ((zb + o.z - kref) - lg) * RNNT_LN2;
-          p.lpl[pidx] = (label >= 0) ? ((zl + o.w - kref) - lg) * RNNT_LN2 : -INFINITY;
+          const float st = s + o.y;
+          const float lg = log2f(st);
+          if (st < 3.0e38f) {
+            p.lse[pidx] = (kref + lg) * RNNT_LN2;
+            p.lpb[pidx] = ((zb + o.z - kref) - lg) * RNNT_LN2;
+            p.lpl[pidx] = (label >= 0) ? ((zl + o.w - kref) - lg) * RNNT_LN2 : -INFINITY;
+          } else {
+            // a logit beyond the fixed reference's range (or NaN): log-probabilities of -inf would only close this
+            // cell to the lattice and leave a finite, wrong loss -- +inf makes every path through it, hence the
+            // utterance's loss, infinite
+            p.lse[pidx] = INFINITY;
+            p.lpb[pidx] = INFINITY;
+            p.lpl[pidx] = (label >= 0) ? INFINITY : -INFINITY;
+          }
           p.kref[pidx] = kref;
         }
         named_bar_sync(1, kEpiWarps * 32);  // the staging tile goes back to the next lattice tile's stores

@@ -431,6 +431,40 @@ def negative_upstream_gradient(B, T, U, E, D, H, V, bwd, seed=9):
     return {f"d{n}_rel_l2_q": rel_l2(a, b.grad) for n, a, b in zip(["enc", "dec", "w1", "b1", "w2", "b2"], ga, ol)}
 
 
+def logit_spread_beyond_stored_range(seed=12):
+    """One vocabulary entry's bias 400 nats above the rest (outside the first columns a row sees): the forward that
+    stores exponentials against a fixed reference must come out non-finite (never finite and wrong), raise under
+    RNNT_B200_VALIDATE=1, and the recomputing path (running maximum) must agree with the float64 oracle."""
+    import os
+    B, T, U, E, D, H, V = 2, 9, 4, 64, 64, 512, 600
+    enc, dec, w1, b1, w2, b2, y, tl, ul = _joint_inputs(B, T, U, E, D, H, V, "full", seed)
+    b2 = b2.clone()
+    b2[300] = 400.0
+    ins = (enc, dec, w1, b1, w2, b2)
+    out = {}
+    la, _ = _fused_grads(ins, y, tl, ul, "stored")
+    out["stored_finite"] = bool(torch.isfinite(la).all())
+    prev = os.environ.get("RNNT_B200_VALIDATE")
+    os.environ["RNNT_B200_VALIDATE"] = "1"
+    try:
+        _fused_grads(ins, y, tl, ul, "stored")
+        out["validate_raises"] = False
+    except FloatingPointError:
+        out["validate_raises"] = True
+    finally:
+        if prev is None:
+            del os.environ["RNNT_B200_VALIDATE"]
+        else:
+            os.environ["RNNT_B200_VALIDATE"] = prev
+    lb, gb = _fused_grads(ins, y, tl, ul, "recompute")
+    ol = [t.double().requires_grad_(True) for t in ins]
+    lo = O.joint_rnnt_loss(*ol, y, tl, ul, reduction="none", quantize_bf16=True)
+    lo.sum().backward()
+    out["recompute_loss_rel"] = float(((lb.cpu().double() - lo.detach()).abs() / lo.detach().abs()).max())
+    out["recompute_dw2_rel_l2"] = rel_l2(gb[4], ol[4].grad)
+    return out
+
+
 def fused_is_deterministic(B, T, U, E, D, H, V, mode="ragged", seed=3, repeats=3):
     """Identical calls must give BIT-identical losses and gradients (no order-dependent atomics in the backward)."""
     ins = _joint_inputs(B, T, U, E, D, H, V, mode, seed)

@@ -99,6 +99,14 @@ def test_upstream_gradients_of_either_sign(bwd):
         assert m[f"d{n}_rel_l2_q"] < GRAD_Q[n], (n, m)
 
 
+def test_logit_spread_beyond_the_stored_range_is_loud():
+    # the storing forward keeps exp2(z - k) with k fixed from the first columns a row sees: 147 nats of headroom
+    m = G.logit_spread_beyond_stored_range()
+    assert not m["stored_finite"], m          # infinite loss, not a finite wrong one
+    assert m["validate_raises"], m
+    assert m["recompute_loss_rel"] < LOSS_Q and m["recompute_dw2_rel_l2"] < GRAD_Q["w2"], m
+
+
 def test_hypothesis_random_shapes_against_the_oracle():
     # SURVEY.md section 4 item (4) for the fused boundary: randomly drawn dims and ragged lengths through every
     # own kernel (joint fwd / bwd, dh, dW2, the ordered reductions; H = 64 takes the library fall-backs). This test
