@@ -242,7 +242,9 @@ int rnnt_b200_dw2_gemm(const void* ds_bf16, const void* h_rows, long long rows, 
  * (147 nats) before fp32 overflows; an overflow shows as an infinite lse / loss, never as a silently wrong one --
  * a model whose logits spread wider than that takes rnnt_b200_joint_fwd and the recomputing backward, which use
  * a running maximum). lse is formed from the fp32 sum of the same
- * exponentials (fixed reference instead of a running maximum).
+ * exponentials (fixed reference instead of a running maximum). range_flag (optional, may be NULL): an int32 the kernel
+ * sets to 1 when that happens -- device memory, or pinned host memory mapped into the device's address space, which
+ * the host can then read without synchronising (_api.py switches to the recomputing path for the following calls).
  *
  * rnnt_b200_patch_scale (after rnnt_b200_lattice): with g[row] = scale_b (c_blank + c_label) exp2(kref - lse log2 e),
  *   dS[row, v] = g[row] * e[row, v]  in every column but the row's two one-hot columns: those two entries of e are
@@ -262,7 +264,8 @@ int rnnt_b200_joint_fwd_store(const void* h_stash, const void* w2_bf16, const fl
                               const int32_t* labels, const int32_t* act_lens, const int32_t* label_lens,
                               const int32_t* tile_utt, const int32_t* tile_cell0, const int32_t* n_tiles,
                               int B, int T, int U1, int V, int H, int blank, int tile_cap,
-                              float* lse, float* lp_blank, float* lp_label, float* kref, void* e_out, void* stream);
+                              float* lse, float* lp_blank, float* lp_label, float* kref, void* e_out,
+                              int32_t* range_flag, void* stream);
 int rnnt_b200_patch_scale(const void* h_stash, const int32_t* labels, const int32_t* act_lens,
                           const int32_t* label_lens, const int32_t* tile_utt, const int32_t* tile_cell0,
                           const int32_t* n_tiles, const float* lse, const float* lp_blank, const float* lp_label,

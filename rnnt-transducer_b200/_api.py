@@ -275,11 +275,34 @@ _DS_BUDGET_BYTES = int(os.environ.get("RNNT_B200_DS_BYTES", str(4 << 30)))
 _E_BUDGET_BYTES = int(os.environ.get("RNNT_B200_E_BYTES", str(48 << 30)))
 
 
-def _store_exponentials(H: int, max_tiles: int, Vds: int) -> bool:
+_range_flags = {}     # per device: a pinned int32 the storing forward sets when a cell's logits leave its range
+
+
+def _range_flag(dev) -> torch.Tensor:
+    key = dev.index if dev.index is not None else torch.cuda.current_device()
+    f = _range_flags.get(key)
+    if f is None:
+        f = _range_flags[key] = torch.zeros(1, dtype=torch.int32).pin_memory()
+    return f
+
+
+def _store_exponentials(H: int, max_tiles: int, Vds: int, dev=None) -> bool:
     mode = os.environ.get("RNNT_B200_BWD", "auto")
     if mode == "recompute" or H != 512 or os.environ.get("RNNT_B200_DH_LIB", "0") == "1":
         return False
-    return mode == "stored" or max_tiles * 128 * Vds * 2 <= _E_BUDGET_BYTES
+    if mode == "stored":
+        return True
+    if dev is not None and int(_range_flag(dev)[0]) != 0:
+        # an earlier call on this device produced logits beyond the fixed exponent reference's range (its loss came
+        # out infinite): from then on the recomputing backward, whose running-maximum log-sum-exp has no such limit.
+        # A plain read of pinned host memory the kernel wrote: no synchronisation.
+        if not _range_flags.get("warned"):
+            _range_flags["warned"] = True
+            import warnings
+            warnings.warn("rnnt_b200: logits spread beyond the stored-exponentials range in an earlier step; "
+                          "using the recomputing backward from now on (RNNT_B200_BWD=recompute makes this explicit)")
+        return False
+    return max_tiles * 128 * Vds * 2 <= _E_BUDGET_BYTES
 
 
 _SPLIT_K = int(os.environ.get("RNNT_B200_SPLIT_K", "4"))   # of the dW2 library GEMM (rows are a multiple of 256)
@@ -326,7 +349,7 @@ class _JointLossFn(torch.autograd.Function):
                   _ptr(tile_utt), _ptr(tile_cell0), _ptr(n_tiles), B, T, U1, H, max_tiles, _ptr(h_stash), st)
             Vds = L.rnnt_b200_ds_pitch(V)
             e_st = kref = None
-            if need_grad and _store_exponentials(H, max_tiles, Vds):
+            if need_grad and _store_exponentials(H, max_tiles, Vds, dev):
                 try:
                     e_st = torch.empty(max_tiles * 128, Vds, dtype=torch.bfloat16, device=dev)
                 except torch.cuda.OutOfMemoryError:
@@ -340,7 +363,7 @@ class _JointLossFn(torch.autograd.Function):
                 _call("joint_fwd_store", L.rnnt_b200_joint_fwd_store, _ptr(h_stash), _ptr(w2q), _ptr(b2l),
                       _ptr(labels), _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt), _ptr(tile_cell0),
                       _ptr(n_tiles), B, T, U1, V, H, blank, max_tiles, _ptr(lse), _ptr(lpb), _ptr(lpl),
-                      _ptr(kref), _ptr(e_st), st)
+                      _ptr(kref), _ptr(e_st), _ptr(_range_flag(dev)), st)
             else:
                 _call("joint_fwd", L.rnnt_b200_joint_fwd, _ptr(h_stash), _ptr(w2q), _ptr(b2l), _ptr(labels),
                                                  _ptr(act_lens), _ptr(label_lens), _ptr(tile_utt),

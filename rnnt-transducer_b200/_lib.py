@@ -42,7 +42,7 @@ SIGNATURES = {
     "rnnt_b200_sum_partials": (_i, [_p, _i, ctypes.c_longlong, _p, _p]),
     "rnnt_b200_dh_gemm_supported": (_i, [_i]),
     "rnnt_b200_dh_gemm": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p]),
-    "rnnt_b200_joint_fwd_store": (_i, [_p] * 9 + [_i] * 7 + [_p] * 6),
+    "rnnt_b200_joint_fwd_store": (_i, [_p] * 9 + [_i] * 7 + [_p] * 7),
     "rnnt_b200_patch_scale": (_i, [_p] * 14 + [_i] * 10 + [_p] * 4),
     "rnnt_b200_dh_gemm_scaled": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p]),
     "rnnt_b200_dw2_gemm_weighted": (_i, [_p, _p, _p, ctypes.c_longlong, _i, _i, _i, _p, _p, _p]),

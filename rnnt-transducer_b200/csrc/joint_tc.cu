@@ -83,6 +83,7 @@ struct JointParams {
   float* lpb;
   float* lpl;
   float* kref;   // MODE 2: the per-cell exponent reference of the stored exponentials (a plane like lse)
+  int32_t* range_flag;  // MODE 2, optional: set to 1 when a cell's logits leave the fixed reference's range
   __nv_bfloat16* h_stash;
   // backward inputs/outputs
   const float* cb;
@@ -618,6 +619,7 @@ joint_kernel(const __grid_constant__ CUtensorMap map_w2, const __grid_constant__
             // a logit beyond the fixed reference's range (or NaN): log-probabilities of -inf would only close this
             // cell to the lattice and leave a finite, wrong loss -- +inf makes every path through it, hence the
             // utterance's loss, infinite
+            if (p.range_flag) *p.range_flag = 1;
             p.lse[pidx] = INFINITY;
             p.lpb[pidx] = INFINITY;
             p.lpl[pidx] = (label >= 0) ? INFINITY : -INFINITY;
@@ -1226,7 +1228,8 @@ extern "C" int rnnt_b200_joint_fwd_store(const void* h_stash, const void* w2_bf1
                                          const int32_t* label_lens, const int32_t* tile_utt,
                                          const int32_t* tile_cell0, const int32_t* n_tiles, int B, int T, int U1,
                                          int V, int H, int blank, int tile_cap, float* lse, float* lp_blank,
-                                         float* lp_label, float* kref, void* e_out, void* stream) {
+                                         float* lp_label, float* kref, void* e_out, int32_t* range_flag,
+                                         void* stream) {
   if (!h_stash || !w2_bf16 || !b2_log2 || !act_lens || !label_lens || !tile_utt || !tile_cell0 ||
       !n_tiles || !lse || !lp_blank || !lp_label || !kref || !e_out)
     return RNNT_B200_E_NULL;
@@ -1240,7 +1243,7 @@ extern "C" int rnnt_b200_joint_fwd_store(const void* h_stash, const void* w2_bf1
   JointParams p = {};
   p.w2q = (const __nv_bfloat16*)w2_bf16; p.b2l = b2_log2; p.labels = labels; p.act_lens = act_lens;
   p.label_lens = label_lens; p.tile_utt = tile_utt; p.tile_cell0 = tile_cell0; p.n_tiles = n_tiles;
-  p.lse = lse; p.lpb = lp_blank; p.lpl = lp_label; p.kref = kref;
+  p.lse = lse; p.lpb = lp_blank; p.lpl = lp_label; p.kref = kref; p.range_flag = range_flag;
   p.h_stash = (__nv_bfloat16*)const_cast<void*>(h_stash);
   p.ds = (__nv_bfloat16*)e_out;
   p.B = B; p.T = T; p.U1 = U1; p.V = V; p.Vpad = rnnt_b200_vocab_pad(V); p.Vds = rnnt_b200_ds_pitch(V); p.H = H; p.blank = blank;

@@ -456,7 +456,20 @@ def logit_spread_beyond_stored_range(seed=12):
             del os.environ["RNNT_B200_VALIDATE"]
         else:
             os.environ["RNNT_B200_VALIDATE"] = prev
+    # the kernel has set this device's range flag (pinned host memory): without a forced mode the next call takes
+    # the recomputing path by itself
+    from rnnt_transducer_b200 import _api
+    flag = _api._range_flag(torch.device(DEV))
+    out["flag_set"] = int(flag[0]) == 1
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        lc, _ = _fused_grads(ins, y, tl, ul, "auto")
+    out["auto_after_flag_finite"] = bool(torch.isfinite(lc).all())
+    flag.zero_()
+    _api._range_flags.pop("warned", None)
     lb, gb = _fused_grads(ins, y, tl, ul, "recompute")
+    out["auto_equals_recompute"] = bool(torch.equal(lc, lb))
     ol = [t.double().requires_grad_(True) for t in ins]
     lo = O.joint_rnnt_loss(*ol, y, tl, ul, reduction="none", quantize_bf16=True)
     lo.sum().backward()

@@ -104,6 +104,7 @@ def test_logit_spread_beyond_the_stored_range_is_loud():
     m = G.logit_spread_beyond_stored_range()
     assert not m["stored_finite"], m          # infinite loss, not a finite wrong one
     assert m["validate_raises"], m
+    assert m["flag_set"] and m["auto_after_flag_finite"] and m["auto_equals_recompute"], m   # self-healing from then on
     assert m["recompute_loss_rel"] < LOSS_Q and m["recompute_dw2_rel_l2"] < GRAD_Q["w2"], m
 
 

@@ -158,7 +158,7 @@ def test_stored_exponentials_entry_points_reject_bad_arguments():
     a = 256
     fwd = lambda **kw: L.rnnt_b200_joint_fwd_store(
         a, a, a, a, a, a, a, a, a, kw.get("B", 2), 8, 5, kw.get("V", 100), kw.get("H", 512), kw.get("blank", 0),
-        kw.get("cap", 2), a, a, a, kw.get("kref", a), kw.get("e", a), None)
+        kw.get("cap", 2), a, a, a, kw.get("kref", a), kw.get("e", a), None, None)
     assert fwd(kref=None) == -1 and fwd(e=None) == -1
     assert fwd(H=100) == -2 and fwd(cap=999) == -2 and fwd(blank=100) == -3
     assert fwd(e=a + 2) == -4

@@ -1,3 +1,3 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python tools/parity_report.py > gpurun_out/w1_parity.txt 2>&1; echo "rc=$?"; tail -25 gpurun_out/w1_parity.txt | cut -c1-700
+timeout 900 python -m pytest tests/test_fused_gpu.py -x -q -m gpu -k "spread or synthetic or golden or stored or config or graphed or headline" > gpurun_out/x1_tests.log 2>&1; echo "tests rc=$?"; tail -5 gpurun_out/x1_tests.log
