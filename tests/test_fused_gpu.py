@@ -57,6 +57,10 @@ def test_golden(name):
     ((2, 17, 130, 64, 64, 256, 1000), "ragged"),    # U+1 > 128: a tile spans < 1 lattice row
     ((2, 9, 4, 64, 64, 64, 270), "ragged"),         # last vocabulary tile N = 64: one epilogue half idle
     ((2, 9, 4, 64, 64, 128, 460), "full"),          # last tile N = 192: half 1 sweeps 2 of its 4 chunks
+    # H = 512 takes the stored-exponentials backward: U+1 > 128, narrow last vocabulary tiles, a tiny vocabulary
+    ((2, 17, 130, 64, 64, 512, 1000), "ragged"),
+    ((3, 11, 6, 64, 64, 512, 270), "edge"),         # BN = 256, last (second) tile N = 64: half 1 idle in it
+    ((2, 9, 4, 64, 64, 512, 17), "full"),           # BN = 64
 ])
 def test_synthetic(dims, mode):
     _assert_fused(G.fused_synth(*dims, mode=mode))
