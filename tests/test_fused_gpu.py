@@ -1,15 +1,19 @@
 """Boundary 2 (fused joint + loss, bf16 tensor-core GEMM, logits never materialised).
 
 Stated bf16-path tolerances. Measured first on B200 over every case of this file (tools/parity_report.py ->
-profiles/r02_parity.json), then fixed at about twice the worst case found, per tensor (DESIGN.md section 4 says
-which rounding owns which share):
+profiles/r02_parity.json) and over 300 randomly drawn corner shapes through both backward paths (tools/soak_fused.py ->
+profiles/r02_soak_{stored,recompute}.txt), then fixed at about twice the worst case found, per tensor (DESIGN.md
+section 4 says which rounding owns which share):
   vs the float64 oracle fed the SAME bf16-rounded h and W2 (isolates kernel error):
-      per-utterance loss 5e-6 relative (worst 2.4e-6); gradients rel-L2: enc 7.5e-3, dec 6e-3, w1 / b1 7e-3
-      (worst 3.0e-3 .. 3.7e-3, all at the single-cell case where nothing averages the bf16 rounding of dS and
-      dpre; 2e-3 / 4e-4 at the BASELINE shapes), w2 2.5e-3 (worst 1.1e-3), b2 2e-3 (worst 8.3e-4)
+      per-utterance loss 5e-6 relative (worst 2.4e-6 here; lattices of one or two cells reach 1.5e-5 in the soak, where
+      one bf16 rounding flip of an h entry is the whole error: the hypothesis test below allows for it); gradients
+      rel-L2: enc 7.5e-3, dec 6e-3, w1 / b1 7e-3 (worst 3.3e-3 .. 4.0e-3, at lattices of a single row where nothing
+      averages the bf16 rounding of dS / E and dpre; 2e-3 / 4e-4 at the BASELINE shapes), w2 6.5e-3 (worst 3.1e-3 with
+      the stored-exponentials backward, whose dW2 carries the bf16 rounding of E and of g.h; 1.7e-3 recomputing),
+      b2 5.5e-3 (worst 2.7e-3, a 17-word vocabulary)
   vs the full-precision float64 oracle (kernel + operand quantisation of h and W2):
-      per-utterance loss 4e-4 relative (worst 1.8e-4: a one-frame utterance); gradients rel-L2 8.5e-3 (worst 4.2e-3),
-      w2 6.5e-3 (worst 3.1e-3), b2 2e-3 (worst 8.3e-4)
+      per-utterance loss 4e-4 relative (worst 4.1e-4 in the soak, 1.8e-4 here: a one-frame utterance); gradients
+      rel-L2 8.5e-3 (worst 6.0e-3 in the soak), w2 9e-3 (worst 4.5e-3), b2 5.5e-3 (worst 2.8e-3)
 """
 import pytest
 
@@ -19,8 +23,8 @@ pytestmark = pytest.mark.gpu
 
 GRADS = ["enc", "dec", "w1", "b1", "w2", "b2"]
 LOSS_Q, LOSS_FULL = 5e-6, 4e-4
-GRAD_Q = {"enc": 7.5e-3, "dec": 6e-3, "w1": 7e-3, "b1": 7e-3, "w2": 2.5e-3, "b2": 2e-3}
-GRAD_FULL = {"enc": 8.5e-3, "dec": 8.5e-3, "w1": 8.5e-3, "b1": 8.5e-3, "w2": 6.5e-3, "b2": 2e-3}
+GRAD_Q = {"enc": 7.5e-3, "dec": 6e-3, "w1": 7e-3, "b1": 7e-3, "w2": 6.5e-3, "b2": 5.5e-3}
+GRAD_FULL = {"enc": 8.5e-3, "dec": 8.5e-3, "w1": 8.5e-3, "b1": 8.5e-3, "w2": 9e-3, "b2": 5.5e-3}
 
 
 def _assert_fused(m, full_grads=True):
