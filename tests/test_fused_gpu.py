@@ -12,7 +12,7 @@ section 4 says which rounding owns which share):
       the stored-exponentials backward, whose dW2 carries the bf16 rounding of E and of g.h; 1.7e-3 recomputing),
       b2 5.5e-3 (worst 2.7e-3, a 17-word vocabulary)
   vs the full-precision float64 oracle (kernel + operand quantisation of h and W2):
-      per-utterance loss 4e-4 relative (worst 4.1e-4 in the soak, 1.8e-4 here: a one-frame utterance); gradients
+      per-utterance loss 8e-4 relative (worst 4.1e-4 in the soak, 1.8e-4 here: a one-frame utterance); gradients
       rel-L2 8.5e-3 (worst 6.0e-3 in the soak), w2 9e-3 (worst 4.5e-3), b2 5.5e-3 (worst 2.8e-3)
 """
 import pytest
@@ -22,7 +22,7 @@ from tests import gpu_checks as G
 pytestmark = pytest.mark.gpu
 
 GRADS = ["enc", "dec", "w1", "b1", "w2", "b2"]
-LOSS_Q, LOSS_FULL = 5e-6, 4e-4
+LOSS_Q, LOSS_FULL = 5e-6, 8e-4
 GRAD_Q = {"enc": 7.5e-3, "dec": 6e-3, "w1": 7e-3, "b1": 7e-3, "w2": 6.5e-3, "b2": 5.5e-3}
 GRAD_FULL = {"enc": 8.5e-3, "dec": 8.5e-3, "w1": 8.5e-3, "b1": 8.5e-3, "w2": 9e-3, "b2": 5.5e-3}
 
