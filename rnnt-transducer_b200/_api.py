@@ -309,7 +309,10 @@ _SPLIT_K = int(os.environ.get("RNNT_B200_SPLIT_K", "4"))   # of the dW2 library 
 
 
 class _JointLossFn(torch.autograd.Function):
-    """(P_enc, P_dec, W2, b2) -> per-utterance loss; logits never materialised."""
+    """(P_enc, P_dec, W2, b2) -> per-utterance loss. The fp32 logits are never materialised; where H = 512 and the
+    memory budget allows, the forward keeps bf16 exponentials of them (E, 2 bytes per cell and vocabulary entry) and the
+    backward needs no second vocabulary GEMM; otherwise the backward recomputes the logits
+    chunk by chunk."""
 
     @staticmethod
     def forward(ctx, pe, pd, w2, b2, labels, act_lens, label_lens, blank, tile_cap):
